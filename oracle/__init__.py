@@ -1,0 +1,216 @@
+"""ctypes front end of the CPU oracle (oracle/ccoracle.c).
+
+TEST INFRASTRUCTURE ONLY — "parity unpinned" (see the header of ccoracle.c).  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+package; the product (cloudclean_b200/, adapters/) never does.
+
+Clouds are numpy float32 arrays of shape (n, S) with S >= 3 (x, y, z first) — e.g. S=8 mirrors
+pcl::PointXYZI (32 B), S=12 pcl::PointXYZINormal (48 B), S=4 a packed float4.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libccoracle.so")
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "ccoracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "libccoracle.so"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        vp, i32, f64 = C.c_void_p, C.c_int, C.c_double
+        L.cco_tree_build.restype = vp
+        L.cco_tree_build.argtypes = [vp, i32, i32]
+        L.cco_tree_free.argtypes = [vp]
+        L.cco_knn.argtypes = [vp, i32, i32, i32, vp, vp, i32]
+        L.cco_knn_brute.argtypes = [vp, i32, i32, i32, i32, i32, vp, vp]
+        L.cco_radius.argtypes = [vp, f64, i32, i32, i32, i32, vp, vp, vp, vp, i32]
+        L.cco_pca_lists.argtypes = [vp, i32, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp]
+        L.cco_hist_normalise.argtypes = [vp, i32]
+        L.cco_features.argtypes = [vp, i32, i32, vp]
+        L.cco_eigen_ratio.argtypes = [vp, i32, vp]
+        L.cco_plane_similarity.argtypes = [vp, i32, vp]
+        L.cco_sor.argtypes = [vp, i32, f64, vp, vp, vp, vp, i32]
+        L.cco_radius_outliers.argtypes = [vp, f64, i32, i32, vp, i32]
+        L.cco_grid_normals.restype = i32
+        L.cco_grid_normals.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, vp]
+        L.cco_eig3_f64_export.argtypes = [vp, vp, vp]
+        L.cco_eig3_f32_export.argtypes = [vp, vp]
+        L.cco_max_threads.restype = i32
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _cloud(points):
+    pts = np.ascontiguousarray(points, dtype=np.float32)
+    assert pts.ndim == 2 and pts.shape[1] >= 3
+    return pts
+
+
+def max_threads():
+    return lib().cco_max_threads()
+
+
+class Tree:
+    """Exact single kd-tree over a cloud — stands in for pcl::KdTreeFLANN (cv.h:83-84)."""
+
+    def __init__(self, points):
+        self.pts = _cloud(points)
+        self.n = self.pts.shape[0]
+        self.stride = self.pts.strides[0]
+        self.h = lib().cco_tree_build(_p(self.pts), self.n, self.stride)
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.cco_tree_free(self.h)
+            self.h = None
+
+    def knn(self, k, q_begin=0, q_end=None, threads=0):
+        """a1 — (idx[int32 rows,k], d2[float32 rows,k]) ascending (d2, idx), self included."""
+        q_end = self.n if q_end is None else q_end
+        rows = q_end - q_begin
+        idx = np.empty((rows, k), np.int32)
+        d2 = np.empty((rows, k), np.float32)
+        lib().cco_knn(self.h, k, q_begin, q_end, _p(idx), _p(d2), threads)
+        return idx, d2
+
+    def radius(self, r, cap=0, strict_lt=True, q_begin=0, q_end=None, lists=True, threads=0):
+        """a2/a3 — lists=True (needs cap > 0): dict(count, idx, d2) with the `cap` nearest in radius;
+        lists=False: dict(count, total) where total = every point inside the radius (exact)."""
+        q_end = self.n if q_end is None else q_end
+        rows = q_end - q_begin
+        count = np.empty(rows, np.int32)
+        total = np.empty(rows, np.int32)
+        idx = d2 = None
+        if lists:
+            assert cap > 0, "lists need a cap"
+            idx = np.empty((rows, cap), np.int32)
+            d2 = np.empty((rows, cap), np.float32)
+        lib().cco_radius(self.h, float(r), cap, 1 if strict_lt else 0, q_begin, q_end,
+                         _p(idx), _p(d2), _p(count), _p(total), threads)
+        if lists:
+            return {"count": count, "idx": idx, "d2": d2}
+        return {"count": count, "total": total}
+
+    def sor(self, mean_k, stddev_mul, threads=0):
+        """a11 — (outlier[uint8 n], mean_d[float32 n], mu, sigma)."""
+        out = np.empty(self.n, np.uint8)
+        md = np.empty(self.n, np.float32)
+        mu, sg = C.c_double(), C.c_double()
+        lib().cco_sor(self.h, mean_k, float(stddev_mul), _p(out), _p(md), C.byref(mu), C.byref(sg), threads)
+        return out, md, mu.value, sg.value
+
+    def radius_outliers(self, r, min_neighbours, prefilter=False, threads=0):
+        """a10 — outlier[uint8 n] (outlierfilter.cpp:120-179)."""
+        out = np.empty(self.n, np.uint8)
+        lib().cco_radius_outliers(self.h, float(r), min_neighbours, 1 if prefilter else 0, _p(out), threads)
+        return out
+
+
+def knn_brute(points, k, q_begin=0, q_end=None):
+    pts = _cloud(points)
+    n = pts.shape[0]
+    q_end = n if q_end is None else q_end
+    idx = np.empty((q_end - q_begin, k), np.int32)
+    d2 = np.empty((q_end - q_begin, k), np.float32)
+    lib().cco_knn_brute(_p(pts), n, pts.strides[0], k, q_begin, q_end, _p(idx), _p(d2))
+    return idx, d2
+
+
+def knn_numpy(points, k, queries=None):
+    """Independent numpy restatement (small n only): same fp32 op order, lexsort on (d2, idx)."""
+    pts = _cloud(points)[:, :3]
+    q = pts if queries is None else pts[queries]
+    dx = q[:, None, 0] - pts[None, :, 0]
+    dy = q[:, None, 1] - pts[None, :, 1]
+    dz = q[:, None, 2] - pts[None, :, 2]
+    d2 = ((dx * dx) + (dy * dy)) + (dz * dz)
+    assert d2.dtype == np.float32
+    order = np.argsort(d2, axis=1, kind="stable")[:, :k]      # stable => ties by index
+    return order.astype(np.int32), np.take_along_axis(d2, order, axis=1)
+
+
+def pca_lists(points, nbr, count=None, cov_norm=1, min_pts=3):
+    """a4/a6/a12 — dict(eig32, eig64, nrm64, gap64) for given neighbour lists."""
+    pts = _cloud(points)
+    nbr = np.ascontiguousarray(nbr, np.int32)
+    rows, cap = nbr.shape
+    cnt = None if count is None else np.ascontiguousarray(count, np.int32)
+    eig32 = np.empty((rows, 3), np.float32)
+    eig64 = np.empty((rows, 3), np.float64)
+    nrm64 = np.empty((rows, 4), np.float64)
+    gap64 = np.empty(rows, np.float64)
+    lib().cco_pca_lists(_p(pts), pts.strides[0], _p(nbr), _p(cnt), rows, cap, cov_norm, min_pts,
+                        _p(eig32), _p(eig64), _p(nrm64), _p(gap64))
+    return {"eig32": eig32, "eig64": eig64, "nrm64": nrm64, "gap64": gap64}
+
+
+def hist_normalise(eig):
+    e = np.ascontiguousarray(eig, np.float32).copy()
+    lib().cco_hist_normalise(_p(e), e.shape[0])
+    return e
+
+
+def features(eig3, formula_set=0):
+    e = np.ascontiguousarray(eig3, np.float32)
+    out = np.empty((e.shape[0], 7), np.float32)
+    with np.errstate(all="ignore"):
+        lib().cco_features(_p(e), e.shape[0], formula_set, _p(out))
+    return out
+
+
+def eigen_ratio(eig3):
+    e = np.ascontiguousarray(eig3, np.float32)
+    out = np.empty(e.shape[0], np.float32)
+    lib().cco_eigen_ratio(_p(e), e.shape[0], _p(out))
+    return out
+
+
+def plane_similarity(eig3):
+    e = np.ascontiguousarray(eig3, np.float32)
+    out = np.empty(e.shape[0], np.float32)
+    lib().cco_plane_similarity(_p(e), e.shape[0], _p(out))
+    return out
+
+
+def grid_normals(points, cloud_to_grid, scan_w, scan_h, fallback=True, k_fallback=50):
+    """a7 — (normal4[float32 n,4], still_missing)."""
+    pts = _cloud(points)
+    c2g = np.ascontiguousarray(cloud_to_grid, np.int32)
+    out = np.empty((pts.shape[0], 4), np.float32)
+    still = lib().cco_grid_normals(_p(pts), pts.shape[0], pts.strides[0], _p(c2g), scan_w, scan_h,
+                                   1 if fallback else 0, k_fallback, _p(out))
+    return out, still
+
+
+def eig3_f64(a6):
+    a = np.ascontiguousarray(a6, np.float64)
+    w = np.empty(3, np.float64)
+    v = np.empty(9, np.float64)
+    lib().cco_eig3_f64_export(_p(a), _p(w), _p(v))
+    return w, v.reshape(3, 3)
+
+
+def eig3_f32(a6):
+    a = np.ascontiguousarray(a6, np.float32)
+    w = np.empty(3, np.float32)
+    lib().cco_eig3_f32_export(_p(a), _p(w))
+    return w
