@@ -1,0 +1,272 @@
+"""cloudclean_b200 — B200-native (sm_100a) kNN / radius / PCA / outlier hot path of CloudClean.
+
+The product is `libccgpu.so` (hand-written CUDA behind the C ABI of include/ccgpu.h); the C++ adapters in
+adapters/ keep the reference's call surface (getPCA, getHist, NormalEstimator, OutlierFilter::filter).
+This package is only the ctypes binding used by tests/, bench.py and Python callers: it contains no
+compute and no fallback — if the library or a GPU is missing, it raises.
+
+Arrays: numpy arrays are host buffers; torch CUDA tensors are passed as device pointers (no copies).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libccgpu.so")
+
+COV_SCATTER, COV_NM1, COV_N = 0, 1, 2
+MAX_K = 64
+
+ERRORS = {0: "CCG_OK", -1: "CCG_ERR_INVALID", -2: "CCG_ERR_CUDA", -3: "CCG_ERR_NO_CLOUD", -4: "CCG_ERR_NONFINITE",
+          -5: "CCG_ERR_UNSUPPORTED", -6: "CCG_ERR_CANCELLED"}
+
+# every symbol include/ccgpu.h declares (tests/test_abi.py checks the header against this list and the .so)
+SYMBOLS = [
+    "ccg_create", "ccg_destroy", "ccg_last_error", "ccg_version", "ccg_get_stats", "ccg_set_cancel_flag",
+    "ccg_set_cloud", "ccg_cloud_size", "ccg_get_order", "ccg_knn", "ccg_radius", "ccg_pca_knn", "ccg_pca_radius",
+    "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
+    "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute",
+]
+
+
+class CcgError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{ERRORS.get(code, code)}: {msg}")
+        self.code = code
+
+
+class Stats(C.Structure):
+    _fields_ = [("ms_upload", C.c_float), ("ms_build", C.c_float), ("ms_query", C.c_float), ("ms_download", C.c_float),
+                ("launches", C.c_int32), ("launches_build", C.c_int32), ("n_points", C.c_int64), ("n_leaves", C.c_int64),
+                ("leaves_scanned", C.c_int64), ("deferred_queries", C.c_int64)]
+
+    def as_dict(self):
+        return {f: getattr(self, f) for f, _ in self._fields_}
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libccgpu.so and declare the ABI.  Raises if the library has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `make` (or __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, f64, sz = C.c_void_p, C.c_int, C.c_double, C.c_size_t
+    L.ccg_create.argtypes = [C.POINTER(vp), i32]
+    L.ccg_destroy.argtypes = [vp]
+    L.ccg_destroy.restype = None
+    L.ccg_last_error.argtypes = [vp]
+    L.ccg_last_error.restype = C.c_char_p
+    L.ccg_version.restype = i32
+    L.ccg_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.ccg_set_cancel_flag.argtypes = [vp, vp]
+    L.ccg_set_cloud.argtypes = [vp, vp, sz, sz]
+    L.ccg_cloud_size.argtypes = [vp]
+    L.ccg_cloud_size.restype = C.c_int64
+    L.ccg_get_order.argtypes = [vp, vp]
+    L.ccg_knn.argtypes = [vp, i32, vp, vp]
+    L.ccg_radius.argtypes = [vp, f64, i32, i32, vp, vp, vp]
+    L.ccg_pca_knn.argtypes = [vp, i32, i32, vp, vp, vp]
+    L.ccg_pca_radius.argtypes = [vp, f64, i32, i32, i32, vp, vp, vp, vp]
+    L.ccg_features.argtypes = [vp, vp, sz, i32, vp]
+    L.ccg_eigen_scalar.argtypes = [vp, vp, sz, i32, vp]
+    L.ccg_sor_mask.argtypes = [vp, i32, f64, vp, vp]
+    L.ccg_radius_count_mask.argtypes = [vp, f64, i32, i32, vp]
+    L.ccg_grid_normals.argtypes = [vp, vp, i32, i32, i32, vp, vp]
+    L.ccg_pca_knn_range.argtypes = [vp, i32, i32, vp, sz, sz, vp, vp]
+    L.ccg_sor_mean_range.argtypes = [vp, i32, sz, sz, vp]
+    L.ccg_unpermute.argtypes = [vp, vp, sz, vp]
+    _lib = L
+    return L
+
+
+def _is_torch(a):
+    return a is not None and type(a).__module__.startswith("torch")
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if _is_torch(a):
+        assert a.is_contiguous()
+        return C.c_void_p(a.data_ptr())
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One GPU, one cloud.  Thin wrapper over ccg_ctx; every method is one C-ABI call."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        h = C.c_void_p()
+        rc = self.L.ccg_create(C.byref(h), int(device))
+        if rc != 0:
+            raise CcgError(rc, "ccg_create failed (no usable CUDA device?) — there is no CPU fallback")
+        self.h = h
+        self.device = int(device)
+        self.n = 0
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ccg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc != 0:
+            raise CcgError(rc, self.L.ccg_last_error(self.h).decode())
+
+    def stats(self):
+        s = Stats()
+        self._check(self.L.ccg_get_stats(self.h, C.byref(s)))
+        return s.as_dict()
+
+    def _out(self, like_device, shape, dtype):
+        """allocate an output next to the inputs: torch CUDA tensor if the cloud came from one, else numpy"""
+        if like_device:
+            import torch
+            tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8}[dtype]
+            return torch.empty(shape, dtype=tdt, device=f"cuda:{self.device}")
+        return np.empty(shape, dtype)
+
+    # ---- cloud -------------------------------------------------------------------------------------
+    def set_cloud(self, points):
+        """points: float32 [n, S>=3] (x, y, z first; S=8 mirrors pcl::PointXYZI).  numpy (host) or torch CUDA."""
+        if _is_torch(points):
+            assert points.dtype.is_floating_point and points.element_size() == 4 and points.dim() == 2
+            assert points.is_contiguous() and points.shape[1] >= 3
+            n, stride = points.shape[0], points.shape[1] * 4
+            self.on_device = points.is_cuda
+            if not points.is_cuda:
+                points = points.numpy()
+        else:
+            points = np.ascontiguousarray(points, np.float32)
+            assert points.ndim == 2 and points.shape[1] >= 3
+            n, stride = points.shape[0], points.strides[0]
+            self.on_device = False
+        self._check(self.L.ccg_set_cloud(self.h, _ptr(points), n, stride))
+        self.n = n
+        return self
+
+    def order(self):
+        o = np.empty(self.n, np.int32)
+        self._check(self.L.ccg_get_order(self.h, _ptr(o)))
+        return o
+
+    # ---- a1 ----------------------------------------------------------------------------------------
+    def knn(self, k, want_d2=True, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        idx = self._out(dev, (self.n, k), np.int32)
+        d2 = self._out(dev, (self.n, k), np.float32) if want_d2 else None
+        self._check(self.L.ccg_knn(self.h, k, _ptr(idx), _ptr(d2)))
+        return idx, d2
+
+    # ---- a2 / a3 -----------------------------------------------------------------------------------
+    def radius(self, r, max_nn=0, strict_lt=True, lists=True, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        count = self._out(dev, (self.n,), np.int32)
+        idx = d2 = None
+        if lists:
+            idx = self._out(dev, (self.n, max_nn), np.int32)
+            d2 = self._out(dev, (self.n, max_nn), np.float32)
+        self._check(self.L.ccg_radius(self.h, float(r), max_nn, 1 if strict_lt else 0, _ptr(idx), _ptr(d2), _ptr(count)))
+        return {"count": count, "idx": idx, "d2": d2}
+
+    # ---- a12 ---------------------------------------------------------------------------------------
+    def pca_knn(self, k, cov_norm=COV_NM1, viewpoint=None, want_normals=True, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        eig = self._out(dev, (self.n, 3), np.float32)
+        nrm = self._out(dev, (self.n, 4), np.float32) if want_normals else None
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn(self.h, k, cov_norm, _ptr(vp), _ptr(eig), _ptr(nrm)))
+        return eig, nrm
+
+    def pca_knn_into(self, k, cov_norm, eig, nrm, viewpoint=None):
+        """same, into caller-provided buffers (host numpy or torch CUDA) — what bench.py times"""
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn(self.h, k, cov_norm, _ptr(vp), _ptr(eig), _ptr(nrm)))
+
+    # ---- a4 / a5 -----------------------------------------------------------------------------------
+    def pca_radius(self, r, max_nn=0, cov_norm=COV_NM1, normalise_hist=False, viewpoint=None, want_normals=False,
+                   device_out=None):
+        """getPCA (cv.h:76-116) when normalise_hist=False, getHist (cv.cpp:249-308) when True."""
+        dev = self.on_device if device_out is None else device_out
+        eig = self._out(dev, (self.n, 3), np.float32)
+        nrm = self._out(dev, (self.n, 4), np.float32) if want_normals else None
+        count = self._out(dev, (self.n,), np.int32)
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_radius(self.h, float(r), max_nn, cov_norm, 1 if normalise_hist else 0, _ptr(vp),
+                                          _ptr(eig), _ptr(nrm), _ptr(count)))
+        return eig, nrm, count
+
+    # ---- a9 ----------------------------------------------------------------------------------------
+    def features(self, eig3, formula_set=0):
+        n = eig3.shape[0]
+        out = self._out(_is_torch(eig3) and eig3.is_cuda, (n, 7), np.float32)
+        self._check(self.L.ccg_features(self.h, _ptr(eig3), n, formula_set, _ptr(out)))
+        return out
+
+    def eigen_scalar(self, eig3, which):
+        n = eig3.shape[0]
+        out = self._out(_is_torch(eig3) and eig3.is_cuda, (n,), np.float32)
+        self._check(self.L.ccg_eigen_scalar(self.h, _ptr(eig3), n, which, _ptr(out)))
+        return out
+
+    # ---- a11 / a10 ---------------------------------------------------------------------------------
+    def sor_mask(self, mean_k, stddev_mul, want_mean_d=True, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n,), np.uint8)
+        md = self._out(dev, (self.n,), np.float32) if want_mean_d else None
+        self._check(self.L.ccg_sor_mask(self.h, mean_k, float(stddev_mul), _ptr(out), _ptr(md)))
+        return out, md
+
+    def radius_count_mask(self, r, min_neighbours, prefilter=False, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n,), np.uint8)
+        self._check(self.L.ccg_radius_count_mask(self.h, float(r), min_neighbours, 1 if prefilter else 0, _ptr(out)))
+        return out
+
+    # ---- a7 ----------------------------------------------------------------------------------------
+    def grid_normals(self, cloud_to_grid, scan_w, scan_h, fallback=True, device_out=None):
+        dev = self.on_device if device_out is None else device_out
+        if not _is_torch(cloud_to_grid):
+            cloud_to_grid = np.ascontiguousarray(cloud_to_grid, np.int32)
+        out = self._out(dev, (self.n, 4), np.float32)
+        missing = C.c_int32(0)
+        self._check(self.L.ccg_grid_normals(self.h, _ptr(cloud_to_grid), scan_w, scan_h, 1 if fallback else 0, _ptr(out),
+                                            C.byref(missing)))
+        return out, missing.value
+
+    # ---- sharding ----------------------------------------------------------------------------------
+    def pca_knn_range(self, k, cov_norm, begin, end, eig_sorted, nrm_sorted, viewpoint=None):
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn_range(self.h, k, cov_norm, _ptr(vp), begin, end, _ptr(eig_sorted), _ptr(nrm_sorted)))
+
+    def sor_mean_range(self, mean_k, begin, end, mean_d_sorted):
+        self._check(self.L.ccg_sor_mean_range(self.h, mean_k, begin, end, _ptr(mean_d_sorted)))
+
+    def unpermute(self, rows_sorted, rows_original):
+        row_bytes = rows_sorted.shape[1] * 4 if rows_sorted.ndim == 2 else 4
+        if _is_torch(rows_sorted):
+            row_bytes = (rows_sorted.shape[1] if rows_sorted.dim() == 2 else 1) * rows_sorted.element_size()
+        else:
+            row_bytes = (rows_sorted.shape[1] if rows_sorted.ndim == 2 else 1) * rows_sorted.itemsize
+        self._check(self.L.ccg_unpermute(self.h, _ptr(rows_sorted), row_bytes, _ptr(rows_original)))

@@ -1,0 +1,487 @@
+// api.cu — the extern "C" surface of libccgpu.so (include/ccgpu.h): argument checking, host/device pointer
+// detection, output staging, and the few O(n) glue kernels (SOR mask, voxel prefilter).
+#include "common.cuh"
+#include <cub/device/device_radix_sort.cuh>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <new>
+
+namespace ccg {
+
+int set_error(ccg_ctx *ctx, int code, const char *fmt, ...) {
+    if (ctx) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+static bool is_dev(const ccg_ctx *ctx, const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// An output the caller wants at `user` (host or device, may be NULL): kernels write to dev().
+struct OutBuf {
+    ccg_ctx *ctx; void *user; size_t bytes; void *d; bool staged;
+    OutBuf() : ctx(nullptr), user(nullptr), bytes(0), d(nullptr), staged(false) {}
+    int open(ccg_ctx *c, int slot, void *user_ptr, size_t nbytes) {
+        ctx = c; user = user_ptr; bytes = nbytes; d = nullptr; staged = false;
+        if (!user_ptr || nbytes == 0) return CCG_OK;
+        if (is_dev(c, user_ptr)) { d = user_ptr; return CCG_OK; }
+        CCG_CUDA(c, c->out[slot].reserve(nbytes));
+        d = c->out[slot].p; staged = true;
+        return CCG_OK;
+    }
+    template <class T> T *dev() const { return reinterpret_cast<T *>(d); }
+    int close() {
+        if (staged) CCG_CUDA(ctx, cudaMemcpyAsync(user, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        return CCG_OK;
+    }
+};
+
+static int begin_call(ccg_ctx *ctx, bool need_cloud) {
+    if (!ctx) return CCG_ERR_INVALID;
+    ctx->err[0] = 0;
+    CCG_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (need_cloud && !ctx->has_cloud)
+        return set_error(ctx, CCG_ERR_NO_CLOUD, "no cloud: call ccg_set_cloud first");
+    if (ctx->cancel && *ctx->cancel) return set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller");
+    ctx->stats.launches = 0;
+    ctx->stats.leaves_scanned = 0;
+    return CCG_OK;
+}
+static int query_begin(ccg_ctx *ctx) { CCG_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream)); return CCG_OK; }
+static int query_end(ccg_ctx *ctx) { CCG_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream)); return CCG_OK; }
+static int finish_call(ccg_ctx *ctx) {
+    CCG_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    CCG_CUDA(ctx, cudaGetLastError());
+    cudaEventElapsedTime(&ctx->stats.ms_query, ctx->ev[3], ctx->ev[4]);
+    cudaEventElapsedTime(&ctx->stats.ms_download, ctx->ev[4], ctx->ev[5]);
+    return CCG_OK;
+}
+
+// strict: d2 < (float)(r*r)  <=>  d2 <= pred((float)(r*r));  inclusive: (double)d2 <= r*r  <=>  d2 <= rounddown(r*r)
+static float radius_bound(double r, int strict_lt) {
+    double r2 = r * r;
+    float f = (float)r2;
+    if (strict_lt) return f > 0.f ? nextafterf(f, -INFINITY) : -1.f;
+    if ((double)f > r2) f = nextafterf(f, -INFINITY);
+    return f;
+}
+
+// ---- glue kernels --------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_sor_mask(const float *__restrict__ mean_d, size_t n, double thr, uint8_t *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (double)mean_d[i] > thr ? 1 : 0;
+}
+__global__ void __launch_bounds__(256) k_count_mask(const int32_t *__restrict__ count, const uint8_t *__restrict__ cand, size_t n,
+                                                    int min_neighbours, uint8_t *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ((cand == nullptr || cand[i]) && count[i] < min_neighbours) ? 1 : 0;
+}
+// voxel key of octreeDownsample's lattice (utils.h:29-31 via outlierfilter.cpp:128): first point at a voxel centre
+__global__ void __launch_bounds__(256) k_voxel_keys(const float4 *__restrict__ orig, size_t n, float edge,
+                                                    unsigned long long *__restrict__ keys, unsigned *__restrict__ vals) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 p0 = orig[0], p = orig[i];
+    const float h = __fmul_rn(edge, 0.5f);
+    long long kx = (long long)floorf(__fdiv_rn(__fsub_rn(p.x, __fsub_rn(p0.x, h)), edge));
+    long long ky = (long long)floorf(__fdiv_rn(__fsub_rn(p.y, __fsub_rn(p0.y, h)), edge));
+    long long kz = (long long)floorf(__fdiv_rn(__fsub_rn(p.z, __fsub_rn(p0.z, h)), edge));
+    keys[i] = ((unsigned long long)(kx & 0x1fffff) << 42) | ((unsigned long long)(ky & 0x1fffff) << 21) | (unsigned long long)(kz & 0x1fffff);
+    vals[i] = (unsigned)i;
+}
+// after sorting by voxel key: candidate[i] = (points in i's voxel) < min_neighbours
+__global__ void __launch_bounds__(256) k_voxel_candidates(const unsigned long long *__restrict__ keys, const unsigned *__restrict__ vals,
+                                                          size_t n, int min_neighbours, uint8_t *__restrict__ cand) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long k = keys[i];
+    // a voxel is sparse iff the run of equal keys around i is shorter than min_neighbours: look at most that far
+    int run = 1;
+    for (long long j = (long long)i - 1; j >= 0 && run < min_neighbours && keys[j] == k; --j) ++run;
+    for (size_t j = i + 1; j < n && run < min_neighbours && keys[j] == k; ++j) ++run;
+    cand[vals[i]] = run < min_neighbours ? 1 : 0;
+}
+
+static QueryArgs base_args(ccg_ctx *ctx) {
+    QueryArgs a{};
+    a.rb = INFINITY; a.begin = 0; a.end = ctx->n; a.sorted_rows = 0;
+    a.cov_norm = CCG_COV_NM1; a.min_pts = 3;
+    return a;
+}
+
+}  // namespace ccg
+
+using namespace ccg;
+
+extern "C" {
+
+int ccg_version(void) { return CCG_VERSION; }
+
+int ccg_create(ccg_ctx **out, int device_id) {
+    if (!out) return CCG_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return CCG_ERR_CUDA; }
+    if (device_id < 0 || device_id >= ndev) return CCG_ERR_INVALID;
+    ccg_ctx *ctx = new (std::nothrow) ccg_ctx();
+    if (!ctx) return CCG_ERR_INVALID;
+    ctx->device = device_id;
+    if (cudaSetDevice(device_id) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
+    for (int i = 0; i < 8; ++i) if (cudaEventCreate(&ctx->ev[i]) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
+    const char *cs = getenv("CCG_COLLECT_STATS");
+    ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
+    *out = ctx;
+    return CCG_OK;
+}
+
+void ccg_destroy(ccg_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ctx->raw.release(); ctx->orig.release(); ctx->sorted.release();
+    for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
+    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release();
+    for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
+    for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    delete ctx;
+}
+
+const char *ccg_last_error(const ccg_ctx *ctx) { return ctx ? ctx->err : "invalid context"; }
+
+int ccg_get_stats(const ccg_ctx *ctx, ccg_stats *out) {
+    if (!ctx || !out) return CCG_ERR_INVALID;
+    *out = ctx->stats;
+    return CCG_OK;
+}
+
+int ccg_set_cancel_flag(ccg_ctx *ctx, const volatile int *flag) {
+    if (!ctx) return CCG_ERR_INVALID;
+    ctx->cancel = flag;
+    return CCG_OK;
+}
+
+int ccg_set_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes) {
+    CCG_TRY(begin_call(ctx, false));
+    if (n > 0 && !xyz) return set_error(ctx, CCG_ERR_INVALID, "xyz is NULL");
+    return build_cloud(ctx, xyz, n, stride_bytes);
+}
+
+int64_t ccg_cloud_size(const ccg_ctx *ctx) { return ctx ? (int64_t)ctx->n : -1; }
+
+int ccg_get_order(ccg_ctx *ctx, int32_t *order) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!order) return set_error(ctx, CCG_ERR_INVALID, "order is NULL");
+    if (ctx->n == 0) return CCG_OK;
+    CCG_CUDA(ctx, cudaMemcpyAsync(order, ctx->vals[ctx->order_sel].p, ctx->n * 4, cudaMemcpyDefault, ctx->stream));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return CCG_OK;
+}
+
+int ccg_knn(ccg_ctx *ctx, int k, int32_t *idx, float *d2) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!idx) return set_error(ctx, CCG_ERR_INVALID, "idx is NULL");
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    OutBuf oi, od;
+    CCG_TRY(oi.open(ctx, 0, idx, ctx->n * (size_t)k * 4));
+    CCG_TRY(od.open(ctx, 1, d2, ctx->n * (size_t)k * 4));
+    QueryArgs a = base_args(ctx);
+    a.mode = MODE_KNN; a.k = k; a.idx = oi.dev<int32_t>(); a.d2 = od.dev<float>();
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_query(ctx, a));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oi.close()); CCG_TRY(od.close());
+    return finish_call(ctx);
+}
+
+int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, float *d2, int32_t *count) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+    const bool lists = idx || d2;
+    if (lists && (max_nn < 1 || max_nn > CCG_MAX_K))
+        return set_error(ctx, CCG_ERR_UNSUPPORTED, "neighbour lists need 1 <= max_nn <= %d (got %d)", CCG_MAX_K, max_nn);
+    if (max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "max_nn must be >= 0");
+    OutBuf oi, od, oc;
+    CCG_TRY(oc.open(ctx, 2, count, ctx->n * 4));
+    const float rb = radius_bound(r, strict_lt);
+    CCG_TRY(query_begin(ctx));
+    if (lists) {
+        CCG_TRY(oi.open(ctx, 0, idx, ctx->n * (size_t)max_nn * 4));
+        CCG_TRY(od.open(ctx, 1, d2, ctx->n * (size_t)max_nn * 4));
+        QueryArgs a = base_args(ctx);
+        a.mode = MODE_KNN; a.k = max_nn; a.rb = rb; a.idx = oi.dev<int32_t>(); a.d2 = od.dev<float>(); a.count = oc.dev<int32_t>();
+        CCG_TRY(launch_tile_query(ctx, a));
+    } else {
+        StreamArgs s{};
+        s.mode = 0; s.rb = rb; s.count_cap = max_nn; s.begin = 0; s.end = ctx->n; s.count = oc.dev<int32_t>();
+        CCG_TRY(launch_tile_stream(ctx, s));
+    }
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oi.close()); CCG_TRY(od.close()); CCG_TRY(oc.close());
+    return finish_call(ctx);
+}
+
+static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise_hist, const float *vp, size_t begin, size_t end,
+                      int sorted_rows, float *eig3, float *normal4, int32_t *count, bool uncapped) {
+    if (cov_norm < 0 || cov_norm > 2) return set_error(ctx, CCG_ERR_INVALID, "cov_norm must be 0, 1 or 2");
+    size_t rows = sorted_rows ? (end > begin ? end - begin : 0) : ctx->n;
+    OutBuf oe, on, oc;
+    CCG_TRY(oe.open(ctx, 0, eig3, rows * 12));
+    CCG_TRY(on.open(ctx, 1, normal4, rows * 16));
+    CCG_TRY(oc.open(ctx, 2, count, rows * 4));
+    CCG_TRY(query_begin(ctx));
+    if (!uncapped) {
+        QueryArgs a = base_args(ctx);
+        a.mode = MODE_PCA; a.k = k; a.rb = rb; a.begin = begin; a.end = end; a.sorted_rows = sorted_rows;
+        a.cov_norm = cov_norm; a.min_pts = 3; a.normalise_hist = normalise_hist; a.has_vp = vp ? 1 : 0;
+        if (vp) for (int i = 0; i < 3; ++i) a.vp[i] = vp[i];
+        a.eig3 = oe.dev<float>(); a.normal4 = on.dev<float>(); a.count = oc.dev<int32_t>();
+        CCG_TRY(launch_tile_query(ctx, a));
+    } else {
+        StreamArgs s{};
+        s.mode = 1; s.rb = rb; s.count_cap = 0; s.begin = begin; s.end = end; s.sorted_rows = sorted_rows;
+        s.cov_norm = cov_norm; s.min_pts = 3; s.normalise_hist = normalise_hist; s.has_vp = vp ? 1 : 0;
+        if (vp) for (int i = 0; i < 3; ++i) s.vp[i] = vp[i];
+        s.eig3 = oe.dev<float>(); s.normal4 = on.dev<float>(); s.count = oc.dev<int32_t>();
+        CCG_TRY(launch_tile_stream(ctx, s));
+    }
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oe.close()); CCG_TRY(on.close()); CCG_TRY(oc.close());
+    return finish_call(ctx);
+}
+
+int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, 0, ctx->n, 0, eig3, normal4, nullptr, false);
+}
+
+int ccg_pca_knn_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, size_t begin, size_t end,
+                      float *eig3_sorted, float *normal4_sorted) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    if (begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "begin must be a multiple of 32");
+    if (end > ctx->n) end = ctx->n;
+    return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, begin, end, 1, eig3_sorted, normal4_sorted, nullptr, false);
+}
+
+int ccg_pca_radius(ccg_ctx *ctx, double r, int max_nn, int cov_norm, int normalise_hist, const float *viewpoint3,
+                   float *eig3, float *normal4, int32_t *count) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+    if (max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "max_nn must be >= 0");
+    const float rb = radius_bound(r, 1);
+    // FLANN caps only when 0 < max_nn < n; otherwise every point inside the radius is used
+    bool uncapped = (max_nn == 0) || ((size_t)max_nn >= ctx->n);
+    if (!uncapped && max_nn > CCG_MAX_K) {
+        // a cap this loose only matters for neighbourhoods denser than max_nn: count first, refuse if any is
+        StreamArgs s{};
+        CCG_CUDA(ctx, ctx->tmp[0].reserve(ctx->n * 4 + 16));
+        s.mode = 0; s.rb = rb; s.count_cap = max_nn + 1; s.begin = 0; s.end = ctx->n; s.count = ctx->tmp[0].as<int32_t>();
+        CCG_TRY(launch_tile_stream(ctx, s));
+        CCG_CUDA(ctx, ctx->hpin[0].reserve(ctx->n * 4));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, ctx->tmp[0].p, ctx->n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        const int32_t *c = ctx->hpin[0].as<int32_t>();
+        for (size_t i = 0; i < ctx->n; ++i)
+            if (c[i] > max_nn)
+                return set_error(ctx, CCG_ERR_UNSUPPORTED, "max_nn=%d > %d with neighbourhoods denser than the cap (point %zu)", max_nn, CCG_MAX_K, i);
+        uncapped = true;
+    }
+    return pca_common(ctx, max_nn, rb, cov_norm, normalise_hist, viewpoint3, 0, ctx->n, 0, eig3, normal4, count, uncapped);
+}
+
+int ccg_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out) {
+    CCG_TRY(begin_call(ctx, false));
+    if (n == 0) return CCG_OK;
+    if (!eig3 || !out) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    const float *e = eig3;
+    if (!is_dev(ctx, eig3)) {
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(n * 12));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, eig3, n * 12, cudaMemcpyHostToDevice, ctx->stream));
+        e = ctx->tmp[1].as<float>();
+    }
+    OutBuf o;
+    CCG_TRY(o.open(ctx, 0, out, n * 28));
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_features(ctx, e, n, formula_set, o.dev<float>()));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(o.close());
+    return finish_call(ctx);
+}
+
+int ccg_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out) {
+    CCG_TRY(begin_call(ctx, false));
+    if (n == 0) return CCG_OK;
+    if (!eig3 || !out) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (which < 0 || which > 1) return set_error(ctx, CCG_ERR_INVALID, "which must be 0 or 1");
+    const float *e = eig3;
+    if (!is_dev(ctx, eig3)) {
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(n * 12));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, eig3, n * 12, cudaMemcpyHostToDevice, ctx->stream));
+        e = ctx->tmp[1].as<float>();
+    }
+    OutBuf o;
+    CCG_TRY(o.open(ctx, 0, out, n * 4));
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_eigen_scalar(ctx, e, n, which, o.dev<float>()));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(o.close());
+    return finish_call(ctx);
+}
+
+int ccg_sor_mean_range(ccg_ctx *ctx, int mean_k, size_t begin, size_t end, float *mean_d_sorted) {
+    CCG_TRY(begin_call(ctx, true));
+    if (mean_k < 1 || mean_k + 1 > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "mean_k=%d outside [1,%d]", mean_k, CCG_MAX_K - 1);
+    if (begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "begin must be a multiple of 32");
+    if (end > ctx->n) end = ctx->n;
+    if (!mean_d_sorted) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    OutBuf om;
+    CCG_TRY(om.open(ctx, 0, mean_d_sorted, (end > begin ? end - begin : 0) * 4));
+    QueryArgs a = base_args(ctx);
+    a.mode = MODE_SOR; a.k = mean_k + 1; a.mean_k = mean_k; a.begin = begin; a.end = end; a.sorted_rows = 1; a.mean_d = om.dev<float>();
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_query(ctx, a));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(om.close());
+    return finish_call(ctx);
+}
+
+int ccg_sor_mask(ccg_ctx *ctx, int mean_k, double stddev_mul, uint8_t *outlier, float *mean_d) {
+    CCG_TRY(begin_call(ctx, true));
+    if (mean_k < 1 || mean_k + 1 > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "mean_k=%d outside [1,%d]", mean_k, CCG_MAX_K - 1);
+    if (!outlier) return set_error(ctx, CCG_ERR_INVALID, "outlier is NULL");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    CCG_CUDA(ctx, ctx->tmp[0].reserve(n * 4));
+    float *md = ctx->tmp[0].as<float>();
+    QueryArgs a = base_args(ctx);
+    a.mode = MODE_SOR; a.k = mean_k + 1; a.mean_k = mean_k; a.mean_d = md;
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_query(ctx, a));
+    // The threshold is a sum over all points in INDEX ORDER in fp64 (PCL StatisticalOutlierRemoval); a parallel
+    // reduction would round differently, so the n floats go to the host once and are summed sequentially there.
+    // This is the contract's arithmetic, not a fallback: the per-point work stays on the GPU.
+    CCG_CUDA(ctx, ctx->hpin[0].reserve(n * 4));
+    CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, md, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const float *h = ctx->hpin[0].as<float>();
+    double sum = 0.0, sq = 0.0;
+    for (size_t i = 0; i < n; ++i) { sum += (double)h[i]; sq += (double)h[i] * (double)h[i]; }
+    const double mu = sum / (double)n;
+    const double var = n > 1 ? (sq - sum * sum / (double)n) / ((double)n - 1.0) : 0.0;
+    const double thr = mu + stddev_mul * sqrt(var > 0 ? var : 0.0);
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, outlier, n));
+    k_sor_mask<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(md, n, thr, oo.dev<uint8_t>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    if (mean_d) {
+        if (is_dev(ctx, mean_d)) CCG_CUDA(ctx, cudaMemcpyAsync(mean_d, md, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        else memcpy(mean_d, h, n * 4);
+    }
+    return finish_call(ctx);
+}
+
+int ccg_radius_count_mask(ccg_ctx *ctx, double r, int min_neighbours, int prefilter, uint8_t *outlier) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!(r >= 0.0) || min_neighbours < 1) return set_error(ctx, CCG_ERR_INVALID, "need r >= 0 and min_neighbours >= 1");
+    if (!outlier) return set_error(ctx, CCG_ERR_INVALID, "outlier is NULL");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    cudaStream_t st = ctx->stream;
+    CCG_CUDA(ctx, ctx->tmp[0].reserve(n * 4));
+    int32_t *cnt = ctx->tmp[0].as<int32_t>();
+    uint8_t *cand = nullptr;
+    CCG_TRY(query_begin(ctx));
+    if (prefilter) {
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(n));
+        CCG_CUDA(ctx, ctx->tmp[2].reserve(n * 16 + 64));
+        CCG_CUDA(ctx, ctx->tmp[3].reserve(n * 8 + 64));
+        cand = ctx->tmp[1].as<uint8_t>();
+        unsigned long long *k0 = ctx->tmp[2].as<unsigned long long>(), *k1 = k0 + n;
+        unsigned *v0 = ctx->tmp[3].as<unsigned>(), *v1 = v0 + n;
+        const float edge = (float)(2.0 * r);
+        k_voxel_keys<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx->orig.as<float4>(), n, edge, k0, v0);
+        cub::DoubleBuffer<unsigned long long> dk(k0, k1);
+        cub::DoubleBuffer<unsigned> dv(v0, v1);
+        size_t tmp_bytes = 0;
+        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, st));
+        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, (int)n, 0, 63, st));
+        k_voxel_candidates<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dk.Current(), dv.Current(), n, min_neighbours, cand);
+        ctx->stats.launches += 11;
+    }
+    StreamArgs s{};
+    s.mode = 0; s.rb = radius_bound(r, 0); s.count_cap = min_neighbours; s.begin = 0; s.end = n; s.count = cnt;
+    CCG_TRY(launch_tile_stream(ctx, s));
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, outlier, n));
+    k_count_mask<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(cnt, cand, n, min_neighbours, oo.dev<uint8_t>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
+int ccg_grid_normals(ccg_ctx *ctx, const int32_t *cloud_to_grid, int scan_w, int scan_h, int do_fallback,
+                     float *normal4, int32_t *n_missing) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!cloud_to_grid || !normal4) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (scan_w < 1 || scan_h < 1) return set_error(ctx, CCG_ERR_INVALID, "scan grid must be at least 1 x 1");
+    const size_t n = ctx->n;
+    if (n == 0) { if (n_missing) *n_missing = 0; return CCG_OK; }
+    const int32_t *c2g = cloud_to_grid;
+    if (!is_dev(ctx, cloud_to_grid)) {
+        CCG_CUDA(ctx, ctx->out[3].reserve(n * 4));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->out[3].p, cloud_to_grid, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        c2g = ctx->out[3].as<int32_t>();
+    }
+    OutBuf on;
+    CCG_TRY(on.open(ctx, 1, normal4, n * 16));
+    CCG_TRY(query_begin(ctx));
+    int32_t still = 0;
+    CCG_TRY(launch_grid_normals(ctx, c2g, scan_w, scan_h, do_fallback, on.dev<float>(), &still));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(on.close());
+    if (n_missing) *n_missing = still;
+    return finish_call(ctx);
+}
+
+int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void *rows_original) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!rows_sorted || !rows_original || row_bytes == 0 || (row_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "bad rows");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *in = rows_sorted;
+    if (!is_dev(ctx, rows_sorted)) {
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(n * row_bytes));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, rows_sorted, n * row_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        in = ctx->tmp[1].p;
+    }
+    OutBuf o;
+    CCG_TRY(o.open(ctx, 0, rows_original, n * row_bytes));
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_unpermute(ctx, in, row_bytes, o.d));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(o.close());
+    return finish_call(ctx);
+}
+
+}  // extern "C"

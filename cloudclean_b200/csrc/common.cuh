@@ -1,0 +1,181 @@
+// common.cuh — internals shared by the libccgpu translation units (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include "../../include/ccgpu.h"
+
+namespace ccg {
+
+constexpr int kLeaf = 32;        // points per leaf of the Morton order == one warp-wide float4 load (512 B)
+constexpr int kFan = 32;         // children per inner node == one lane per child
+constexpr int kMaxLevels = 8;    // 32^8 leaves is far beyond any cloud
+constexpr unsigned kFull = 0xffffffffu;
+
+// Device view of the bounding-box hierarchy over the Morton-sorted cloud (passed by value to kernels).
+struct TreeView {
+    const float4 *pts;               // sorted points, npad = nleaf*32; w = original index (int bits); pads = +inf
+    const float4 *orig;              // original-order points (w unused), for the PCA gather
+    const float4 *lo[kMaxLevels];    // per level: box min (w unused)
+    const float4 *hi[kMaxLevels];    // per level: box max
+    int count[kMaxLevels];           // nodes per level; level 0 = leaves
+    int nlevels;                     // count[nlevels-1] == 1
+    int n;                           // valid points
+};
+
+// grow-only device buffer
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct HostBuf {   // grow-only pinned host buffer
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+}  // namespace ccg
+
+struct ccg_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    const volatile int *cancel = nullptr;
+
+    bool has_cloud = false;
+    size_t n = 0;            // points
+    size_t npad = 0;         // nleaf * 32
+    int nleaf = 0;
+    int nlevels = 0;
+    int level_count[ccg::kMaxLevels] = {};
+    size_t level_off[ccg::kMaxLevels] = {};   // offset (in float4) of each level inside boxes_lo / boxes_hi
+
+    ccg::DevBuf raw;         // staged AoS input (host clouds only)
+    ccg::DevBuf orig;        // float4[n]   original order
+    ccg::DevBuf sorted;      // float4[npad] Morton order, w = original index
+    ccg::DevBuf keys[2];     // uint64[n] Morton keys (double buffer)
+    ccg::DevBuf vals[2];     // uint32[n] original index (double buffer); vals[order_sel] is the final order
+    int order_sel = 0;
+    ccg::DevBuf sort_tmp;    // radix sort scratch
+    ccg::DevBuf boxes_lo, boxes_hi;
+    ccg::DevBuf scratch;     // bbox / flags / counters
+    ccg::DevBuf out[4];      // staged outputs for host destinations
+    ccg::DevBuf tmp[4];      // per-call temporaries
+    ccg::HostBuf hpin[2];    // pinned bounce buffers
+    float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};
+
+    ccg_stats stats = {};
+    int collect_stats = 0;
+    char err[512] = "";
+
+    ccg::TreeView view() const {
+        ccg::TreeView t;
+        t.pts = sorted.as<float4>();
+        t.orig = orig.as<float4>();
+        for (int l = 0; l < ccg::kMaxLevels; ++l) {
+            t.lo[l] = boxes_lo.as<float4>() + level_off[l];
+            t.hi[l] = boxes_hi.as<float4>() + level_off[l];
+            t.count[l] = l < nlevels ? level_count[l] : 0;
+        }
+        t.nlevels = nlevels;
+        t.n = (int)n;
+        return t;
+    }
+};
+
+namespace ccg {
+
+int set_error(ccg_ctx *ctx, int code, const char *fmt, ...);
+
+#define CCG_CUDA(ctx, call)                                                                     \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return ccg::set_error((ctx), CCG_ERR_CUDA, "%s failed: %s (%s:%d)", #call,          \
+                                  cudaGetErrorString(e__), __FILE__, __LINE__);                 \
+    } while (0)
+
+#define CCG_TRY(expr)                                   \
+    do {                                                \
+        int rc__ = (expr);                              \
+        if (rc__ != CCG_OK) return rc__;                \
+    } while (0)
+
+// build.cu
+int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes);
+
+// query.cu
+enum TileMode { MODE_KNN = 0, MODE_PCA = 1, MODE_SOR = 2 };
+struct QueryArgs {
+    int mode;
+    int k;                  // list entries wanted (kNN k, or capped max_nn)
+    float rb;               // candidates need d2 <= rb (+inf for pure kNN)
+    size_t begin, end;      // sorted-position range (begin multiple of 32)
+    int sorted_rows;        // 1: output row = pos - begin, 0: output row = original index
+    // MODE_KNN
+    int32_t *idx; float *d2; int32_t *count;
+    // MODE_PCA
+    int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
+    float *eig3; float *normal4;
+    // MODE_SOR
+    int mean_k; float *mean_d;
+};
+int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a);
+
+struct StreamArgs {
+    int mode;               // 0: count (early-out at count_cap when > 0), 1: moments -> PCA
+    float rb;
+    int count_cap;
+    size_t begin, end;
+    int sorted_rows;
+    int32_t *count;
+    int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
+    float *eig3; float *normal4;
+};
+int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a);
+
+// warp-per-query kernel over an explicit list of query points (original indices, device pointer)
+struct PointArgs {
+    const int32_t *queries; int nq;
+    int mode, k; float rb;
+    int list_rows;          // 1: output row = position in the list, 0: row = original index
+    int32_t *idx; float *d2; int32_t *count;
+    int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
+    float *eig3; float *normal4;
+    int mean_k; float *mean_d;
+};
+int launch_point_query(ccg_ctx *ctx, const PointArgs &a);
+
+int launch_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out);
+int launch_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out);
+int launch_unpermute(ccg_ctx *ctx, const void *in, size_t row_bytes, void *out);
+
+// gridnormals.cu
+int launch_grid_normals(ccg_ctx *ctx, const int32_t *c2g_dev, int scan_w, int scan_h, int do_fallback, float *normal4_dev,
+                        int32_t *n_missing_host);
+
+}  // namespace ccg

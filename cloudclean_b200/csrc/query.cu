@@ -1,0 +1,764 @@
+// query.cu — the per-point neighbourhood kernels: exact kNN / fixed-radius search over the Morton box
+// hierarchy with a fused covariance + eigensolve (normals, curvature, eigenvalues) or SOR epilogue.
+//
+// Replaces the serial loops  cv.h:96-113 (getPCA), cv.cpp:271-295 (getHist), normalestimation.cpp:436-459,
+// outlierfilter.cpp:157-173  and the PCL StatisticalOutlierRemoval / NormalEstimation definitions.
+//
+// Mapping: one warp = one TILE = the 32 queries of one leaf (Morton-adjacent, so they share
+// their candidate set).  The warp walks the box hierarchy bottom-up from its own leaf; at inner nodes one
+// lane tests one child box against the tile box; a surviving leaf is re-tested per query, staged once in
+// shared memory (a contiguous 512-byte run) and read back as broadcast LDS.128, so every lane scores the
+// same candidate against its own query.  Each lane keeps its own bounded top-k as 64-bit (d2 bits, index)
+// keys in registers, which makes the (d2, original index) tie-break a single unsigned compare.
+//
+// Exactness: d2 is evaluated with __fmul_rn/__fadd_rn in the contract's order (no fma); a box is pruned
+// only if its fp32 box distance, built from the same monotone operations, is strictly greater than the
+// current k-th d2, so ties at the k-th distance are always visited.
+#include "common.cuh"
+#include <cfloat>
+
+namespace ccg {
+
+// ---------------------------------------------------------------------------------------------------
+// distance primitives (contract: ((dx*dx + dy*dy) + dz*dz), round-to-nearest, never fused)
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float sumsq3(float dx, float dy, float dz) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+__device__ __forceinline__ float d2_point(const float4 &q, const float4 &p) {
+    return sumsq3(__fsub_rn(q.x, p.x), __fsub_rn(q.y, p.y), __fsub_rn(q.z, p.z));
+}
+// lower bound of d2_point(q, p) over all p inside [lo, hi] (monotone in every rounding step)
+__device__ __forceinline__ float d2_point_box(const float4 &q, const float4 &lo, const float4 &hi) {
+    float dx = fmaxf(fmaxf(__fsub_rn(lo.x, q.x), __fsub_rn(q.x, hi.x)), 0.f);
+    float dy = fmaxf(fmaxf(__fsub_rn(lo.y, q.y), __fsub_rn(q.y, hi.y)), 0.f);
+    float dz = fmaxf(fmaxf(__fsub_rn(lo.z, q.z), __fsub_rn(q.z, hi.z)), 0.f);
+    return sumsq3(dx, dy, dz);
+}
+// lower bound over all (q in [alo, ahi], p in [blo, bhi])
+__device__ __forceinline__ float d2_box_box(const float4 &alo, const float4 &ahi, const float4 &blo, const float4 &bhi) {
+    float dx = fmaxf(fmaxf(__fsub_rn(blo.x, ahi.x), __fsub_rn(alo.x, bhi.x)), 0.f);
+    float dy = fmaxf(fmaxf(__fsub_rn(blo.y, ahi.y), __fsub_rn(alo.y, bhi.y)), 0.f);
+    float dz = fmaxf(fmaxf(__fsub_rn(blo.z, ahi.z), __fsub_rn(alo.z, bhi.z)), 0.f);
+    return sumsq3(dx, dy, dz);
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// bounded top-k in registers: K sorted 64-bit keys (d2 bits << 32 | original index)
+// ---------------------------------------------------------------------------------------------------
+typedef unsigned long long u64;
+constexpr u64 kEmptyKey = ((u64)0x7f800000u << 32) | 0x7fffffffu;   // (+inf, INT_MAX): larger than any real key
+
+template <int K>
+struct TopK {
+    u64 key[K];
+    float bound;     // min(radius bound, current k-th d2); -1 for inactive lanes
+    float rb;
+
+    __device__ __forceinline__ void init(int k, float rb_, bool active) {
+#pragma unroll
+        for (int i = 0; i < K; ++i) key[i] = (i < K - k) ? 0ull : kEmptyKey;   // front slots pinned when k < K
+        rb = rb_;
+        bound = active ? rb_ : -1.f;
+    }
+    __device__ __forceinline__ void insert(u64 ck) {
+        // precondition: ck < key[K-1]; keeps key[] ascending
+        bool lt_i = true;
+#pragma unroll
+        for (int i = K - 1; i > 0; --i) {
+            bool lt_p = ck < key[i - 1];
+            key[i] = lt_p ? key[i - 1] : (lt_i ? ck : key[i]);
+            lt_i = lt_p;
+        }
+        key[0] = lt_i ? ck : key[0];
+    }
+    __device__ __forceinline__ void candidate(const float4 &q, const float4 &c) {
+        float d2 = d2_point(q, c);
+        if (d2 <= bound) {
+            u64 ck = ((u64)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(c.w);
+            if (ck < key[K - 1]) {
+                insert(ck);
+                bound = fminf(rb, __uint_as_float((unsigned)(key[K - 1] >> 32)));
+            }
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// streaming visitor (no list): count and shifted moments of everything inside the radius
+// ---------------------------------------------------------------------------------------------------
+struct Stream {
+    float bound, rb;
+    int count, cap;
+    bool moments;
+    float m[9];   // sx sy sz sxx sxy sxz syy syz szz of (p - q)
+    __device__ __forceinline__ void init(float rb_, int cap_, bool moments_, bool active) {
+        rb = rb_; cap = cap_; moments = moments_; count = 0;
+        bound = active ? rb_ : -1.f;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) m[i] = 0.f;
+    }
+    __device__ __forceinline__ void candidate(const float4 &q, const float4 &c) {
+        float d2 = d2_point(q, c);
+        if (d2 <= bound) {
+            ++count;
+            if (moments) {
+                float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
+                m[0] += x; m[1] += y; m[2] += z;
+                m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+            }
+            if (cap > 0 && count >= cap) bound = -1.f;   // enough neighbours seen: this lane is finished
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// tile traversal
+// ---------------------------------------------------------------------------------------------------
+struct WarpScratch {
+    float4 leaf[kLeaf];
+    int base[kMaxLevels];
+    unsigned mask[kMaxLevels];
+};
+
+template <class V>
+__device__ __forceinline__ int traverse_tile(const TreeView &T, int tile, const float4 &q, V &v, WarpScratch &ws) {
+    const int lane = threadIdx.x & 31;
+    const float4 tlo = T.lo[0][tile], thi = T.hi[0][tile];
+    int scanned = 0;
+    int node = tile;       // ancestor of the tile at level L
+    int L = 0;
+    int sp = 1;            // stack depth; entry d holds children at level (top_lv - d), exhausted entries pop lazily
+    int top_lv = 0;
+    if (lane == 0) { ws.base[0] = tile & ~31; ws.mask[0] = 1u << (tile & 31); }
+    __syncwarp();
+    while (true) {
+        if (sp == 0) {
+            // all subtrees below the level-L ancestor are done: test its siblings
+            ++L;
+            if (L >= T.nlevels) break;
+            const int parent = node >> 5;
+            const int first = parent << 5;
+            const int c = first + lane;
+            const bool in = c < T.count[L - 1];
+            const float rmax = warp_max(v.bound);
+            if (rmax < 0.f) break;                           // every lane is finished
+            bool pass = false;
+            if (in) {
+                float4 clo = T.lo[L - 1][c], chi = T.hi[L - 1][c];
+                pass = d2_box_box(tlo, thi, clo, chi) <= rmax;
+            }
+            unsigned m = __ballot_sync(kFull, pass) & ~(1u << (node & 31));
+            node = parent;
+            top_lv = L - 1;
+            if (!m) continue;
+            if (lane == 0) { ws.base[0] = first; ws.mask[0] = m; }
+            __syncwarp();
+            sp = 1;
+        }
+        // take one child off the top entry
+        const int lv = top_lv - (sp - 1);
+        const int base = ws.base[sp - 1];
+        unsigned m = ws.mask[sp - 1];
+        __syncwarp();
+        if (m == 0) { --sp; continue; }
+        const int cbit = __ffs(m) - 1;
+        m &= m - 1;
+        if (lane == 0) ws.mask[sp - 1] = m;
+        const int child = base + cbit;
+        // exact per-query test of the child's box against each lane's current bound
+        const float4 clo = T.lo[lv][child], chi = T.hi[lv][child];
+        const bool want = d2_point_box(q, clo, chi) <= v.bound;
+        if (!__any_sync(kFull, want)) { __syncwarp(); continue; }
+        if (lv == 0) {
+            // stage the leaf (contiguous 512 B) and let every lane score all 32 candidates
+            const float4 mine = T.pts[(size_t)child * kLeaf + lane];
+            __syncwarp();
+            ws.leaf[lane] = mine;
+            __syncwarp();
+#pragma unroll 8
+            for (int j = 0; j < kLeaf; ++j) v.candidate(q, ws.leaf[j]);
+            ++scanned;
+        } else {
+            // expand: one lane per grandchild against the tile box
+            const int first = child << 5;
+            const int c = first + lane;
+            const bool in = c < T.count[lv - 1];
+            const float rmax = warp_max(v.bound);
+            bool pass = false;
+            if (in) {
+                float4 glo = T.lo[lv - 1][c], ghi = T.hi[lv - 1][c];
+                pass = d2_box_box(tlo, thi, glo, ghi) <= rmax;
+            }
+            const unsigned m2 = __ballot_sync(kFull, pass);
+            if (m2) {
+                if (lane == 0) { ws.base[sp] = first; ws.mask[sp] = m2; }
+                ++sp;
+            }
+        }
+        __syncwarp();
+    }
+    return scanned;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fused covariance + symmetric 3x3 eigensolve (fp32 cyclic Jacobi: high relative accuracy on PSD input)
+// ---------------------------------------------------------------------------------------------------
+struct Eig3 {
+    float w[3];      // descending
+    float n[3];      // unit eigenvector of w[2]
+};
+
+__device__ __forceinline__ void jacobi_rot(float &app, float &aqq, float &apq, float &arp, float &arq,
+                                           float &v0p, float &v0q, float &v1p, float &v1q, float &v2p, float &v2q) {
+    if (apq != 0.f) {
+        float theta = (aqq - app) / (2.f * apq);
+        float t = copysignf(1.f, theta) / (fabsf(theta) + sqrtf(fmaf(theta, theta, 1.f)));
+        if (!isfinite(theta)) t = 0.f;
+        float c = rsqrtf(fmaf(t, t, 1.f));
+        float s = t * c;
+        float tau = s / (1.f + c);
+        app -= t * apq;
+        aqq += t * apq;
+        apq = 0.f;
+        float rp = arp, rq = arq;
+        arp = rp - s * (rq + tau * rp);
+        arq = rq + s * (rp - tau * rq);
+        float a, b;
+        a = v0p; b = v0q; v0p = a - s * (b + tau * a); v0q = b + s * (a - tau * b);
+        a = v1p; b = v1q; v1p = a - s * (b + tau * a); v1q = b + s * (a - tau * b);
+        a = v2p; b = v2q; v2p = a - s * (b + tau * a); v2q = b + s * (a - tau * b);
+    }
+}
+
+// a = {xx, xy, xz, yy, yz, zz}
+__device__ __forceinline__ Eig3 eig3_sym(const float a_in[6]) {
+    float a00 = a_in[0], a01 = a_in[1], a02 = a_in[2], a11 = a_in[3], a12 = a_in[4], a22 = a_in[5];
+    float scale = fmaxf(fmaxf(fmaxf(fabsf(a00), fabsf(a11)), fabsf(a22)), fmaxf(fmaxf(fabsf(a01), fabsf(a02)), fabsf(a12)));
+    float inv = scale > 0.f ? 1.f / scale : 0.f;
+    a00 *= inv; a01 *= inv; a02 *= inv; a11 *= inv; a12 *= inv; a22 *= inv;
+    float v00 = 1.f, v01 = 0.f, v02 = 0.f, v10 = 0.f, v11 = 1.f, v12 = 0.f, v20 = 0.f, v21 = 0.f, v22 = 1.f;
+#pragma unroll 1
+    for (int sweep = 0; sweep < 8; ++sweep) {
+        float off = fabsf(a01) + fabsf(a02) + fabsf(a12);
+        if (off <= 1e-10f) break;                     // entries are scaled to max |a_ij| = 1
+        // (p,q,r) = (0,1,2): a_rp = a02, a_rq = a12
+        jacobi_rot(a00, a11, a01, a02, a12, v00, v01, v10, v11, v20, v21);
+        // (0,2,1): a_rp = a01, a_rq = a12
+        jacobi_rot(a00, a22, a02, a01, a12, v00, v02, v10, v12, v20, v22);
+        // (1,2,0): a_rp = a01, a_rq = a02
+        jacobi_rot(a11, a22, a12, a01, a02, v01, v02, v11, v12, v21, v22);
+    }
+    Eig3 r;
+    float w0 = a00 * scale, w1 = a11 * scale, w2 = a22 * scale;
+    // column of the smallest eigenvalue, eigenvalues descending
+    float nx, ny, nz, wmin;
+    if (w0 <= w1 && w0 <= w2) { wmin = w0; nx = v00; ny = v10; nz = v20; r.w[0] = fmaxf(w1, w2); r.w[1] = fminf(w1, w2); }
+    else if (w1 <= w2) { wmin = w1; nx = v01; ny = v11; nz = v21; r.w[0] = fmaxf(w0, w2); r.w[1] = fminf(w0, w2); }
+    else { wmin = w2; nx = v02; ny = v12; nz = v22; r.w[0] = fmaxf(w0, w1); r.w[1] = fminf(w0, w1); }
+    r.w[2] = wmin;
+    float nn = rsqrtf(nx * nx + ny * ny + nz * nz);
+    r.n[0] = nx * nn; r.n[1] = ny * nn; r.n[2] = nz * nn;
+    return r;
+}
+
+struct PcaOut {
+    int cov_norm, min_pts, normalise_hist, has_vp;
+    float vp[3];
+    float *eig3, *normal4;
+};
+
+// moments of (p - q): m = {sx sy sz sxx sxy sxz syy syz szz}, cnt points -> outputs for one row
+__device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, const float m[9], int cnt, size_t row) {
+    float e0 = 0.f, e1 = 0.f, e2 = 1.f;                       // cv.h:105-109 "isolated point" marker
+    float nx = NAN, ny = NAN, nz = NAN, curv = NAN;
+    if (cnt >= o.min_pts) {
+        float invn = 1.f / (float)cnt;
+        float mx = m[0] * invn, my = m[1] * invn, mz = m[2] * invn;
+        float s[6];
+        s[0] = m[3] - m[0] * mx; s[1] = m[4] - m[0] * my; s[2] = m[5] - m[0] * mz;
+        s[3] = m[6] - m[1] * my; s[4] = m[7] - m[1] * mz; s[5] = m[8] - m[2] * mz;
+        float sc = o.cov_norm == CCG_COV_NM1 ? 1.f / (float)(cnt - 1) : (o.cov_norm == CCG_COV_N ? invn : 1.f);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) s[i] *= sc;
+        Eig3 e = eig3_sym(s);
+        e0 = e.w[0]; e1 = e.w[1]; e2 = e.w[2];
+        float tr = e0 + e1 + e2;
+        curv = tr > 0.f ? fabsf(e2 / tr) : 0.f;
+        nx = e.n[0]; ny = e.n[1]; nz = e.n[2];
+        if (o.has_vp) {
+            float dot = (o.vp[0] - q.x) * nx + (o.vp[1] - q.y) * ny + (o.vp[2] - q.z) * nz;
+            if (dot < 0.f) { nx = -nx; ny = -ny; nz = -nz; }
+        }
+        if (o.normalise_hist) {                                // cv.cpp:293
+            float nn = sqrtf(e0 * e0 + e1 * e1 + e2 * e2);
+            if (nn > 0.f) { e0 /= nn; e1 /= nn; e2 /= nn; }
+        }
+    }
+    if (o.eig3) { float *p = o.eig3 + row * 3; p[0] = e0; p[1] = e1; p[2] = e2; }
+    if (o.normal4) reinterpret_cast<float4 *>(o.normal4)[row] = make_float4(nx, ny, nz, curv);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// tile kernel with a top-k list
+// ---------------------------------------------------------------------------------------------------
+struct TileParams {
+    int mode, k;
+    float rb;
+    int tile_begin, tile_end;
+    long long row_begin;          // sorted_rows: row = pos - row_begin
+    int sorted_rows;
+    int32_t *idx; float *d2; int32_t *count;
+    PcaOut pca;
+    int mean_k; float *mean_d;
+    unsigned long long *stat_scanned;
+};
+
+template <int K>
+__global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = P.tile_begin + blockIdx.x * 4 + warp;
+    if (tile >= P.tile_end) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    const int qidx = __float_as_int(q.w);
+    TopK<K> v;
+    v.init(P.k, P.rb, active);
+    int scanned = traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+
+    const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)qidx;
+    const int k = P.k;
+    if (P.mode == MODE_KNN) {
+        if (!active) return;
+        int cnt = 0;
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+            if (i >= K - k) {
+                const int j = i - (K - k);
+                const bool real = v.key[i] != kEmptyKey;
+                cnt += real ? 1 : 0;
+                if (P.idx) P.idx[row * k + j] = real ? (int)(unsigned)(v.key[i] & 0xffffffffu) : -1;
+                if (P.d2) P.d2[row * k + j] = __uint_as_float((unsigned)(v.key[i] >> 32));
+            }
+        }
+        if (P.count) P.count[row] = cnt;
+    } else if (P.mode == MODE_PCA) {
+        // gather the neighbours (original-order array) and accumulate moments of (p - q)
+        float m[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) m[i] = 0.f;
+        int cnt = 0;
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+            if (i >= K - k) {
+                const bool real = active && v.key[i] != kEmptyKey;
+                if (real) {
+                    const float4 p = T.orig[(unsigned)(v.key[i] & 0xffffffffu)];
+                    float x = p.x - q.x, y = p.y - q.y, z = p.z - q.z;
+                    m[0] += x; m[1] += y; m[2] += z;
+                    m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+                    ++cnt;
+                }
+            }
+        }
+        if (!active) cnt = 0;
+        PcaOut o = P.pca;
+        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; }
+        pca_finish(o, q, m, cnt, row);
+        if (P.count && active) P.count[row] = cnt;
+    } else {   // MODE_SOR: mean distance to the mean_k nearest, self (first entry) dropped
+        if (!active) return;
+        double s = 0.0;
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+            if (i > K - k) {
+                float d = __uint_as_float((unsigned)(v.key[i] >> 32));
+                if (v.key[i] != kEmptyKey) s += (double)__fsqrt_rn(d);
+            }
+        }
+        P.mean_d[row] = (float)(s / (double)P.mean_k);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// tile kernel without a list (radius count / uncapped radius PCA)
+// ---------------------------------------------------------------------------------------------------
+struct StreamParams {
+    int mode; float rb; int count_cap;
+    int tile_begin, tile_end; long long row_begin; int sorted_rows;
+    int32_t *count;
+    PcaOut pca;
+    unsigned long long *stat_scanned;
+};
+
+__global__ void __launch_bounds__(128) k_tile_stream(const __grid_constant__ TreeView T, const __grid_constant__ StreamParams P) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = P.tile_begin + blockIdx.x * 4 + warp;
+    if (tile >= P.tile_end) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    Stream v;
+    v.init(P.rb, P.count_cap, P.mode == 1, active);
+    int scanned = traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+    const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)__float_as_int(q.w);
+    if (P.mode == 1) {
+        PcaOut o = P.pca;
+        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; }
+        pca_finish(o, q, v.m, active ? v.count : 0, row);
+    }
+    if (P.count && active) P.count[row] = v.count;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------------
+template <int K>
+static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cudaStream_t st) {
+    k_tile_topk<K><<<blocks, 128, 0, st>>>(T, P);
+}
+
+int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
+    if (ctx->n == 0) return CCG_OK;
+    if (a.k < 1 || a.k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", a.k, CCG_MAX_K);
+    if (a.begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "range begin must be a multiple of 32");
+    size_t end = a.end > ctx->n ? ctx->n : a.end;
+    if (a.begin >= end) return CCG_OK;
+    TileParams P{};
+    P.mode = a.mode; P.k = a.k; P.rb = a.rb;
+    P.tile_begin = (int)(a.begin / kLeaf);
+    P.tile_end = (int)((end + kLeaf - 1) / kLeaf);
+    P.row_begin = (long long)a.begin; P.sorted_rows = a.sorted_rows;
+    P.idx = a.idx; P.d2 = a.d2; P.count = a.count;
+    P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
+    for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.mean_k = a.mean_k; P.mean_d = a.mean_d;
+    P.stat_scanned = nullptr;
+    if (ctx->collect_stats) {
+        CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 8, ctx->stream));
+        P.stat_scanned = (unsigned long long *)((char *)ctx->scratch.p + 1024);
+    }
+    const int ntiles = P.tile_end - P.tile_begin;
+    const int blocks = (ntiles + 3) / 4;
+    TreeView T = ctx->view();
+    cudaStream_t st = ctx->stream;
+    const int k = a.k;
+    if (k <= 8) launch_topk<8>(T, P, blocks, st);
+    else if (k <= 16) launch_topk<16>(T, P, blocks, st);
+    else if (k <= 20) launch_topk<20>(T, P, blocks, st);
+    else if (k <= 24) launch_topk<24>(T, P, blocks, st);
+    else if (k <= 32) launch_topk<32>(T, P, blocks, st);
+    else if (k <= 48) launch_topk<48>(T, P, blocks, st);
+    else launch_topk<64>(T, P, blocks, st);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    if (ctx->collect_stats) {
+        unsigned long long s = 0;
+        CCG_CUDA(ctx, cudaMemcpyAsync(&s, P.stat_scanned, 8, cudaMemcpyDeviceToHost, st));
+        CCG_CUDA(ctx, cudaStreamSynchronize(st));
+        ctx->stats.leaves_scanned = (int64_t)s;
+    }
+    return CCG_OK;
+}
+
+int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a) {
+    if (ctx->n == 0) return CCG_OK;
+    if (a.begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "range begin must be a multiple of 32");
+    size_t end = a.end > ctx->n ? ctx->n : a.end;
+    if (a.begin >= end) return CCG_OK;
+    StreamParams P{};
+    P.mode = a.mode; P.rb = a.rb; P.count_cap = a.count_cap;
+    P.tile_begin = (int)(a.begin / kLeaf);
+    P.tile_end = (int)((end + kLeaf - 1) / kLeaf);
+    P.row_begin = (long long)a.begin; P.sorted_rows = a.sorted_rows;
+    P.count = a.count;
+    P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
+    for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.stat_scanned = nullptr;
+    if (ctx->collect_stats) {
+        CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 8, ctx->stream));
+        P.stat_scanned = (unsigned long long *)((char *)ctx->scratch.p + 1024);
+    }
+    const int ntiles = P.tile_end - P.tile_begin;
+    k_tile_stream<<<(ntiles + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    if (ctx->collect_stats) {
+        unsigned long long s = 0;
+        CCG_CUDA(ctx, cudaMemcpyAsync(&s, P.stat_scanned, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->stats.leaves_scanned = (int64_t)s;
+    }
+    return CCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// a9: eigen-derived features (elementwise; HBM-streaming: 12 B in, 28 B out per point)
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_features(const float *__restrict__ eig3, size_t n, int formula_set, float *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float l0 = eig3[3 * i], l1 = eig3[3 * i + 1], l2 = eig3[3 * i + 2];
+    float *o = out + 7 * i;
+    o[0] = __fdiv_rn(__fsub_rn(l0, l2), l0);                 // markov.cpp:451
+    o[1] = __fdiv_rn(__fsub_rn(l1, l2), l0);                 // :455
+    o[2] = __fdiv_rn(l2, l0);                                // :459
+    o[3] = __fdiv_rn(__fsub_rn(l0, l1), l0);                 // :463
+    if (formula_set == 0) {
+        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l0));      // :467 (sic)
+        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l0));   // :471 (sic)
+        o[6] = __fdiv_rn(l0, __fadd_rn(__fadd_rn(l0, l1), l2));     // :475 (sic)
+    } else {
+        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l2));
+        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l2));
+        o[6] = __fdiv_rn(l2, __fadd_rn(__fadd_rn(l0, l1), l2));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_eigen_scalar(const float *__restrict__ eig3, size_t n, int which, float *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float l0 = eig3[3 * i], l1 = eig3[3 * i + 1], l2 = eig3[3 * i + 2];
+    float r;
+    if (l1 < l2) r = 0.f;                                    // the (0,0,1) marker: featureeval.cpp:1107-1110
+    else if (which == 0) r = l0 > l2 ? __fdiv_rn(l1, l0) : 1.f;   // :1130-1135
+    else {                                                   // :1201-1220, cv.h:498-501
+        float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(l0, l0), __fmul_rn(l1, l1)), __fmul_rn(l2, l2)));
+        float c = __fdiv_rn(l0, nn);
+        r = c < 0.f ? 0.f : (c > 1.f ? 1.f : c);
+    }
+    out[i] = r;
+}
+
+int launch_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out) {
+    if (n == 0) return CCG_OK;
+    k_features<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(eig3, n, formula_set, out);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+int launch_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out) {
+    if (n == 0) return CCG_OK;
+    k_eigen_scalar<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(eig3, n, which, out);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+
+// out[order[i]] = in[i], rows of `words` 32-bit words
+__global__ void __launch_bounds__(256) k_unpermute(const uint32_t *__restrict__ in, const unsigned *__restrict__ order, size_t n,
+                                                   int words, uint32_t *__restrict__ out) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t i = t / words;
+    int w = (int)(t % words);
+    if (i >= n) return;
+    out[(size_t)order[i] * words + w] = in[i * words + w];
+}
+int launch_unpermute(ccg_ctx *ctx, const void *in, size_t row_bytes, void *out) {
+    if (ctx->n == 0) return CCG_OK;
+    int words = (int)(row_bytes / 4);
+    size_t total = ctx->n * (size_t)words;
+    k_unpermute<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>((const uint32_t *)in, ctx->vals[ctx->order_sel].as<unsigned>(),
+                                                                          ctx->n, words, (uint32_t *)out);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// warp-per-query kernel: arbitrary query lists (stage (iii) of the grid normals, deferred stragglers).
+// The 32 lanes score the 32 candidates of a leaf at once; the bounded top-k (k <= 64) lives one or two
+// keys per lane and is updated with warp shuffles.
+// ---------------------------------------------------------------------------------------------------
+struct PointParams {
+    const int32_t *queries;      // original indices; NULL = 0..nq-1
+    int nq;
+    int mode, k;
+    float rb;
+    int list_rows;               // 1: output row = position in `queries`, 0: row = original index
+    int32_t *idx; float *d2; int32_t *count;
+    PcaOut pca;
+    int mean_k; float *mean_d;
+};
+
+struct WarpStack {
+    int base[kMaxLevels];
+    unsigned mask[kMaxLevels];
+};
+
+__device__ __forceinline__ u64 shfl64(u64 v, int src) {
+    unsigned lo = __shfl_sync(kFull, (unsigned)v, src), hi = __shfl_sync(kFull, (unsigned)(v >> 32), src);
+    return ((u64)hi << 32) | lo;
+}
+__device__ __forceinline__ u64 shfl_up64(u64 v) {
+    unsigned lo = __shfl_up_sync(kFull, (unsigned)v, 1), hi = __shfl_up_sync(kFull, (unsigned)(v >> 32), 1);
+    return ((u64)hi << 32) | lo;
+}
+
+__global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ TreeView T, const __grid_constant__ PointParams P) {
+    __shared__ WarpStack s_st[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qslot = blockIdx.x * 4 + warp;
+    if (qslot >= P.nq) return;
+    WarpStack &ws = s_st[warp];
+    const int qi = P.queries ? P.queries[qslot] : qslot;
+    const float4 q = T.orig[qi];
+    const int k = P.k;
+    u64 key0 = kEmptyKey, key1 = kEmptyKey;        // list slots lane and 32+lane, ascending
+    u64 worst = kEmptyKey;                         // key at slot k-1
+    float bound = P.rb;
+
+    int sp = 0;
+    const int top = T.nlevels - 1;                 // root level; entry d holds children at level top-1-d
+    if (top == 0) {                                // single leaf
+        if (lane == 0) { ws.base[0] = 0; ws.mask[0] = 1u; }
+        sp = 1;
+    } else {
+        const int c = lane;
+        bool pass = false;
+        if (c < T.count[top - 1]) pass = d2_point_box(q, T.lo[top - 1][c], T.hi[top - 1][c]) <= bound;
+        unsigned m = __ballot_sync(kFull, pass);
+        if (lane == 0) { ws.base[0] = 0; ws.mask[0] = m; }
+        sp = 1;
+    }
+    __syncwarp();
+    const int lv0 = top == 0 ? 0 : top - 1;
+    while (sp > 0) {
+        const int lv = lv0 - (sp - 1);
+        const int base = ws.base[sp - 1];
+        unsigned m = ws.mask[sp - 1];
+        __syncwarp();
+        if (m == 0) { --sp; continue; }
+        // nearest surviving child first: tightens the bound quickly
+        int cbit;
+        {
+            const bool mine = (m >> lane) & 1u;
+            float bd = INFINITY;
+            if (mine) bd = d2_point_box(q, T.lo[lv][base + lane], T.hi[lv][base + lane]);
+            unsigned kk = __float_as_uint(bd);
+            unsigned best = kk;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(kFull, best, o));
+            const unsigned who = __ballot_sync(kFull, mine && kk == best);
+            cbit = who ? (__ffs(who) - 1) : (__ffs(m) - 1);
+            // drop children that no longer pass the current bound
+            const unsigned still = __ballot_sync(kFull, mine && bd <= bound);
+            m &= still;
+            if (!((m >> cbit) & 1u)) { if (lane == 0) ws.mask[sp - 1] = 0; __syncwarp(); --sp; continue; }
+        }
+        m &= ~(1u << cbit);
+        if (lane == 0) ws.mask[sp - 1] = m;
+        const int child = base + cbit;
+        if (lv == 0) {
+            const float4 c = T.pts[(size_t)child * kLeaf + lane];
+            const float dd = d2_point(q, c);
+            const u64 ck = ((u64)__float_as_uint(dd) << 32) | (unsigned)__float_as_int(c.w);
+            unsigned passers = __ballot_sync(kFull, dd <= bound && ck < worst);
+            while (passers) {
+                const int src = __ffs(passers) - 1;
+                passers &= passers - 1;
+                const u64 nk = shfl64(ck, src);
+                if (!(nk < worst)) continue;                  // the bound moved since the ballot
+                const int pos = __popc(__ballot_sync(kFull, key0 < nk)) + __popc(__ballot_sync(kFull, key1 < nk));
+                const u64 up0 = shfl_up64(key0), up1 = shfl_up64(key1), carry = shfl64(key0, 31);
+                const int s0 = lane, s1 = 32 + lane;
+                key0 = s0 > pos ? up0 : (s0 == pos ? nk : key0);
+                key1 = s1 > pos ? (lane == 0 ? carry : up1) : (s1 == pos ? nk : key1);
+                worst = (k - 1) < 32 ? shfl64(key0, k - 1) : shfl64(key1, k - 1 - 32);
+                bound = fminf(P.rb, __uint_as_float((unsigned)(worst >> 32)));
+            }
+        } else {
+            const int first = child << 5;
+            const int c = first + lane;
+            bool pass = false;
+            if (c < T.count[lv - 1]) pass = d2_point_box(q, T.lo[lv - 1][c], T.hi[lv - 1][c]) <= bound;
+            const unsigned m2 = __ballot_sync(kFull, pass);
+            if (m2) {
+                if (lane == 0) { ws.base[sp] = first; ws.mask[sp] = m2; }
+                ++sp;
+            }
+        }
+        __syncwarp();
+    }
+
+    const size_t row = P.list_rows ? (size_t)qslot : (size_t)qi;
+    if (P.mode == MODE_KNN) {
+        int cnt = 0;
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int s = r * 32 + lane;
+            const u64 kk = r ? key1 : key0;
+            const bool real = s < k && kk != kEmptyKey;
+            cnt += __popc(__ballot_sync(kFull, real));
+            if (s < k) {
+                if (P.idx) P.idx[row * k + s] = real ? (int)(unsigned)(kk & 0xffffffffu) : -1;
+                if (P.d2) P.d2[row * k + s] = real ? __uint_as_float((unsigned)(kk >> 32)) : INFINITY;
+            }
+        }
+        if (P.count && lane == 0) P.count[row] = cnt;
+    } else if (P.mode == MODE_PCA) {
+        float m[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) m[i] = 0.f;
+        int cnt = 0;
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int s = r * 32 + lane;
+            const u64 kk = r ? key1 : key0;
+            if (s < k && kk != kEmptyKey) {
+                const float4 p = T.orig[(unsigned)(kk & 0xffffffffu)];
+                float x = p.x - q.x, y = p.y - q.y, z = p.z - q.z;
+                m[0] += x; m[1] += y; m[2] += z;
+                m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+                ++cnt;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) m[i] += __shfl_xor_sync(kFull, m[i], o);
+            cnt += __shfl_xor_sync(kFull, cnt, o);
+        }
+        if (lane == 0) {
+            pca_finish(P.pca, q, m, cnt, row);
+            if (P.count) P.count[row] = cnt;
+        }
+    } else {
+        double s = 0.0;
+        for (int j = 1; j < k; ++j) {
+            const u64 kk = j < 32 ? shfl64(key0, j) : shfl64(key1, j - 32);
+            if (kk != kEmptyKey) s += (double)__fsqrt_rn(__uint_as_float((unsigned)(kk >> 32)));
+        }
+        if (lane == 0) P.mean_d[row] = (float)(s / (double)P.mean_k);
+    }
+}
+
+int launch_point_query(ccg_ctx *ctx, const PointArgs &a) {
+    if (ctx->n == 0 || a.nq == 0) return CCG_OK;
+    if (a.k < 1 || a.k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", a.k, CCG_MAX_K);
+    PointParams P{};
+    P.queries = a.queries; P.nq = a.nq; P.mode = a.mode; P.k = a.k; P.rb = a.rb; P.list_rows = a.list_rows;
+    P.idx = a.idx; P.d2 = a.d2; P.count = a.count;
+    P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
+    for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.mean_k = a.mean_k; P.mean_d = a.mean_d;
+    k_point_query<<<(a.nq + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+
+}  // namespace ccg

@@ -1,0 +1,160 @@
+/*
+ * ccgpu.h — C ABI of libccgpu.so: CloudClean's per-point neighbourhood hot path on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Each entry point replaces one serial
+ * `for (i < cloud->size())` loop of the reference, which today calls PCL/FLANN/Eigen in-process; the file:line
+ * of the loop it replaces is cited on every declaration (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - Every function returns CCG_OK (0) or a negative CCG_ERR_* code; nothing throws; ccg_last_error()
+ *     gives the message.  There is no CPU fallback: without a usable CUDA device ccg_create fails.
+ *   - One ccg_ctx drives ONE GPU (one process per GPU; multi-GPU runs replicate the cloud and shard the
+ *     query range, see ccg_*_range).  A ctx may be used from any single thread at a time — the reference's
+ *     std::async normal-estimation worker (normalestimation.cpp:196) must be able to call it — so every call
+ *     sets the device itself and relies on no thread-local CUDA state.
+ *   - All buffers are caller-allocated.  Input and output pointers may be HOST pointers (pageable or
+ *     pinned) or DEVICE pointers of the ctx's GPU; the library detects which (cudaPointerGetAttributes)
+ *     and stages copies only when needed.
+ *   - Indices are 32-bit *original* cloud indices (the internal Morton permutation never leaks), except in
+ *     the *_range entry points which are explicitly in sorted order.
+ *   - Distances are the contract's fp32 d2 = ((dx*dx + dy*dy) + dz*dz), no fma; neighbour order is the
+ *     total order (d2, original index); the query point itself is a neighbour (d2 = 0).
+ */
+#ifndef CCGPU_H
+#define CCGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCG_VERSION 100
+
+enum {
+    CCG_OK = 0,
+    CCG_ERR_INVALID = -1,      /* bad argument */
+    CCG_ERR_CUDA = -2,         /* CUDA runtime error (message has the call) */
+    CCG_ERR_NO_CLOUD = -3,     /* query before ccg_set_cloud */
+    CCG_ERR_NONFINITE = -4,    /* cloud holds NaN/Inf coordinates (PCL's kd-tree rejects those too) */
+    CCG_ERR_UNSUPPORTED = -5,  /* parameter outside the compiled range (e.g. k > CCG_MAX_K) */
+    CCG_ERR_CANCELLED = -6     /* the caller's cancel flag was raised between stages */
+};
+
+#define CCG_MAX_K 64           /* largest k / capped max_nn kept as an ordered list */
+
+/* covariance normalisation of the 3x3 scatter S = sum (p-mu)(p-mu)^T */
+enum {
+    CCG_COV_SCATTER = 0,       /* S            — pcl::PCA in PCL 1.7.0 (README.md:26-27) */
+    CCG_COV_NM1 = 1,           /* S/(n-1)      — pcl::PCA in PCL >= 1.8 (CMakeLists.txt:110)  [default] */
+    CCG_COV_N = 2              /* S/n          — pcl::NormalEstimation::computePointNormal */
+};
+
+typedef struct ccg_ctx ccg_ctx;
+
+/* Per-call statistics of the most recent query on a ctx (device time from CUDA events on the ctx stream). */
+typedef struct ccg_stats {
+    float ms_upload;           /* H2D of the cloud (0 for device-resident input) */
+    float ms_build;            /* ingest + Morton keys + radix sort + reorder + bounding-box levels */
+    float ms_query;            /* the query kernels of the last call */
+    float ms_download;         /* D2H of the outputs (0 for device-resident outputs) */
+    int32_t launches;          /* kernels of this library launched by the last call (build counted by set_cloud) */
+    int32_t launches_build;
+    int64_t n_points;
+    int64_t n_leaves;          /* 32-point leaves of the Morton order */
+    int64_t leaves_scanned;    /* leaf scans summed over query tiles (0 unless CCG_COLLECT_STATS=1) */
+    int64_t deferred_queries;  /* queries finished by the warp-per-query kernel */
+} ccg_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------------------ */
+int ccg_create(ccg_ctx **out, int device_id);
+void ccg_destroy(ccg_ctx *ctx);
+const char *ccg_last_error(const ccg_ctx *ctx);     /* never NULL; owned by the ctx (static text for ctx==NULL) */
+int ccg_version(void);
+int ccg_get_stats(const ccg_ctx *ctx, ccg_stats *out);
+/* Optional cancellation: checked between stages, honours PointCloud::deleting_ (normalestimation.cpp:305-306). */
+int ccg_set_cancel_flag(ccg_ctx *ctx, const volatile int *flag);
+
+/* ---- cloud ---------------------------------------------------------------------------------------- */
+/* Replaces pcl::KdTreeFLANN::setInputCloud (cv.h:83-84, cv.cpp:254-255, normalestimation.cpp:428-429) and the
+ * async octree build (pointcloud.cpp:312-323).  `xyz` points at the first float of an array of structs with
+ * `stride_bytes` between points: 32 for pcl::PointXYZI, 48 for pcl::PointXYZINormal, 16 for packed float4,
+ * 12 for packed xyz.  Host or device pointer.  The data is copied before return. */
+int ccg_set_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes);
+int64_t ccg_cloud_size(const ccg_ctx *ctx);
+/* sorted position -> original index (int32[n]); the Morton order used to shard queries across GPUs */
+int ccg_get_order(ccg_ctx *ctx, int32_t *order);
+
+/* ---- a1: exact kNN -------------------------------------------------------------------------------- */
+/* Replaces the per-point pcl::KdTreeFLANN::nearestKSearch loops: normalestimation.cpp:436-439 (k=50),
+ * flood.cpp:306-327 (k=8), graphcut/mincut.cpp:462-466 (k=14).  idx, d2: n*k, row i = neighbours of point i,
+ * ascending (d2, index), self first.  Rows are padded with idx=-1, d2=+inf when k > n.  d2 may be NULL. */
+int ccg_knn(ccg_ctx *ctx, int k, int32_t *idx, float *d2);
+
+/* ---- a2 / a3: fixed-radius search ----------------------------------------------------------------- */
+/* Replaces KdTreeFLANN::radiusSearch (cv.h:98, cv.cpp:273, featureeval/utils.h:50) with strict_lt=1
+ * [d2 < (float)(r*r)] and OctreePointCloudSearch::radiusSearch (outlierfilter.cpp:169, cv.cpp:194) with
+ * strict_lt=0 [(double)d2 <= r*r].  1 <= max_nn <= CCG_MAX_K: the max_nn nearest inside the radius, ascending;
+ * idx/d2: n*max_nn padded with -1/+inf; count[i] = entries kept.  idx and d2 may be NULL (count only), and
+ * with idx==d2==NULL max_nn may be 0 (count everything inside the radius). */
+int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, float *d2, int32_t *count);
+
+/* ---- a12: kNN + PCA normals / curvature ----------------------------------------------------------- */
+/* The north-star op (PCL NormalEstimation definition): kNN(k, self included) -> 3x3 covariance -> symmetric
+ * eigensolve.  eig3: n*3 eigenvalues descending (scaled per cov_norm).  normal4: n*4 = unit eigenvector of the
+ * smallest eigenvalue + curvature l2/(l0+l1+l2); flipped towards viewpoint3 (3 floats) when that is non-NULL
+ * (pcl::flipNormalTowardsViewpoint, cf. the commented call at normalestimation.cpp:417).  Either output may be NULL. */
+int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4);
+
+/* ---- a4 / a5 / a6: radius + PCA (getPCA / getHist) ------------------------------------------------ */
+/* Replaces the body of getPCA<PointT> (cv.h:96-113) and getHist (cv.cpp:271-295): strict radius search with
+ * the max_nn cap (0 = uncapped), `<3 neighbours -> (0,0,1)` marker (cv.h:105-109), else PCA eigenvalues
+ * descending.  normalise_hist!=0 applies getHist's L2 normalisation (cv.cpp:293).  normal4 / count optional. */
+int ccg_pca_radius(ccg_ctx *ctx, double r, int max_nn, int cov_norm, int normalise_hist, const float *viewpoint3,
+                   float *eig3, float *normal4, int32_t *count);
+
+/* ---- a9: eigen-derived features ------------------------------------------------------------------- */
+/* out: n*7 = anisotropy, planarity, sphericity, linearity, omnivariance, eigenentropy, curvature.
+ * formula_set 0 = exactly as written in Markov::mkFeatureVector (markov.cpp:449-475, including its slips),
+ * 1 = textbook definitions. */
+int ccg_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out);
+/* featureeval.cpp:1104-1137 (which=0: eigen ratio) and :1201-1220 (which=1: plane cosine similarity); out: n */
+int ccg_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out);
+
+/* ---- a11: statistical outlier filter -------------------------------------------------------------- */
+/* PCL StatisticalOutlierRemoval definition: mean distance to the mean_k nearest neighbours (self dropped),
+ * global mean + stddev_mul * sigma threshold, fp64 sums in index order.  outlier: n bytes (1 = outlier);
+ * mean_d: n floats or NULL. */
+int ccg_sor_mask(ccg_ctx *ctx, int mean_k, double stddev_mul, uint8_t *outlier, float *mean_d);
+
+/* ---- a10: radius / min-neighbour outlier filter --------------------------------------------------- */
+/* Replaces OutlierFilter::filter's loop (outlierfilter.cpp:157-173): outlier[i] = 1 when the inclusive r-ball
+ * of point i (self included) holds fewer than min_neighbours points.  prefilter!=0 also applies the
+ * octreeDownsample(2r) candidate step (:126-147): only points whose voxel of edge 2r holds fewer than
+ * min_neighbours points can be flagged (voxel lattice: first cloud point at a voxel centre). */
+int ccg_radius_count_mask(ccg_ctx *ctx, double r, int min_neighbours, int prefilter, uint8_t *outlier);
+
+/* ---- a7: scan-grid triangle-fan normals ----------------------------------------------------------- */
+/* Replaces NormalEstimator::estimateNormals (normalestimation.cpp:268-470).  cloud_to_grid: int32[n] grid index
+ * of every point (PointCloud::cloudToGridMap, pointcloud.cpp:389-391); scan_w/scan_h as PointCloud::scan_width()/
+ * scan_height().  normal4: n*4 = nx,ny,nz,data_n[3]; NaN x4 where the fan has no face.  do_fallback!=0 runs stage
+ * (iii): kNN(50) mean of neighbours' normals for the missing ones, in order.  *n_missing (optional) = normals
+ * still NaN at the end. */
+int ccg_grid_normals(ccg_ctx *ctx, const int32_t *cloud_to_grid, int scan_w, int scan_h, int do_fallback,
+                     float *normal4, int32_t *n_missing);
+
+/* ---- multi-GPU sharding ----------------------------------------------------------- */
+/* Every rank holds the whole cloud and builds the identical Morton order; rank g owns sorted positions
+ * [begin, end) (multiples of 32 except the last end = n).  Outputs are compact, row (pos - begin), in SORTED
+ * order; ccg_unpermute scatters gathered rows back to original order. */
+int ccg_pca_knn_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, size_t begin, size_t end,
+                      float *eig3_sorted, float *normal4_sorted);
+int ccg_sor_mean_range(ccg_ctx *ctx, int mean_k, size_t begin, size_t end, float *mean_d_sorted);
+/* out[order[i]] = in[i] for rows of row_bytes (multiple of 4) bytes; in/out host or device */
+int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void *rows_original);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCGPU_H */
