@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — points/s of kNN(k=20)+PCA features on the 30 M-point synthetic scan (BASELINE.json `metric`).
+
+One step = one pass of the hot path over the scan through the C ABI of libccgpu.so:
+    ccg_set_cloud          (ingest + Morton keys + radix sort + leaves + box hierarchy — the "grid build")
+    ccg_pca_knn_features   (exact kNN(k=20) + 3x3 covariance + eigensolve -> eig3, normal+curvature, and the 7 eigen
+                            features of Markov::mkFeatureVector fused into the same kernel)
+N = 1 : `value` = points / step time with the scan ALREADY RESIDENT in HBM (device pointers in, device
+        pointers out); `e2e` = the same calls with pinned HOST buffers (H2D of the 32-byte PointXYZI AoS and
+        D2H of every output inside the timed region).
+N > 1 : one process per GPU (torchrun).  Rank 0 owns the scan; each step broadcasts it over NCCL, every rank
+        builds the identical Morton order, answers its own contiguous range of the sorted order
+        (ccg_pca_knn_range), and the per-point outputs are all-gathered and un-permuted — strong scaling of a
+        fixed 30 M-point job (north star: replicated cloud, query shards by Morton range).
+The scan is 960 MB of input and >1.6 GB of outputs per step, far above the 126 MB L2, so no explicit L2 flush
+is needed between timed iterations (stated in config.l2).
+
+`--impl reference` times the reference's CPU algorithm for the same path (oracle/ restatement — PCL/FLANN/Eigen
+cannot be built here) with all host threads on a bounded sample of the same scan.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+
+K = 20
+BYTES_QUERY = 48 + 16 * K          # own point 16 + k x 16 + outputs 32
+BYTES_BUILD = 144
+METRIC = "points/s kNN(k=20)+PCA features, 30M-pt scan"
+CPU_SAMPLE_POINTS = 2_000_000
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every 100 ms while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._halt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._halt.wait(0.1)
+
+    def stop(self):
+        self._halt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": float(self.max_mhz) if self.max_mhz else None,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_device_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# ------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle's restatement of the reference CPU path, all host threads
+# ------------------------------------------------------------------------------------------------------------
+def cpu_sample_points(scan_cfg, shrink):
+    """The bounded CPU sample: the first CPU_SAMPLE_POINTS points of the workload scan in file order (whole scan
+    columns, i.e. a contiguous azimuth sector with the workload's own density), generated on the CPU-visible
+    device that is available."""
+    import torch
+    from cloudclean_b200 import synth
+    dev = "cuda" if torch.cuda.is_available() else "cpu"
+    a = dict(synth.CONFIGS[scan_cfg])
+    a["scan_w"] = max(8, a["scan_w"] // shrink)
+    a["scan_h"] = max(8, a["scan_h"] // shrink)
+    # only the columns that are needed: ~0.574 valid returns per ray in this scene
+    cols = min(a["scan_w"], int(CPU_SAMPLE_POINTS / (0.55 * a["scan_h"])) + 2)
+    a_full_w = a["scan_w"]
+    s = synth.make_scan(device=dev, max_cols=cols, **a)
+    pts = s["points"][:CPU_SAMPLE_POINTS].cpu().numpy()
+    return pts, f"first {pts.shape[0]} points (file order, {cols} of {a_full_w} scan columns) of the workload scan"
+
+
+def cpu_pass(pts):
+    """One pass of the reference's CPU path: KdTreeFLANN::setInputCloud + per-point kNN(20) + pcl::PCA
+    (cv.h:83-113 control flow) + feature formulas, OpenMP over queries.  Returns seconds."""
+    import oracle
+    t0 = time.perf_counter()
+    T = oracle.Tree(pts)
+    idx, _ = T.knn(K)
+    res = oracle.pca_lists(pts, idx, cov_norm=1)
+    oracle.features(res["eig32"], 0)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    pts, sample = cpu_sample_points(args.scan_cfg, args.shrink)
+    cores = oracle.max_threads()
+    for _ in range(args.warmup):
+        cpu_pass(pts)
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_pass(pts)
+    v = pts.shape[0] * args.steps / t
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "points/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, None),
+            "cpu_baseline": {"value": v, "unit": "points/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference = oracle/ C restatement of the PCL/FLANN/Eigen path (kd-tree leaf 15, fp32 PCA), OpenMP over "
+                    "queries; the reference itself is single-threaded (cv.h:96) and cannot be built here"}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n):
+    from cloudclean_b200 import synth
+    a = dict(synth.CONFIGS[args.scan_cfg])
+    return {"workload": f"config {args.scan_cfg}: synthetic outdoor terrestrial scan {a['scan_w'] // args.shrink}x{a['scan_h'] // args.shrink} rays"
+                        f" (seed {a['seed']}), kNN(k={K})+PCA(cov 1/(n-1)) normals/curvature/eigenvalues + 7 eigen features",
+            "points": n, "k": K, "shrink": args.shrink,
+            "parallelism": "replicated cloud, query shards by Morton range" if args.gpus > 1 else "single GPU",
+            "l2": "inputs+outputs per step >> 126 MB L2 (no flush needed)"}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scan-cfg", type=int, default=3, help="synth.CONFIGS entry (3 = the 30 M-point scan of the metric)")
+    ap.add_argument("--shrink", type=int, default=1, help="divide the scan grid (debug only; a shrunk run is not the metric)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3) if args.shrink == 1 else args.warmup
+
+    import torch
+    import torch.distributed as dist
+    import cloudclean_b200 as cc
+    from cloudclean_b200 import sharding, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU: the product has no CPU path"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}"
+
+    # ---- workload ----------------------------------------------------------------------------------------
+    if rank == 0:
+        scan = synth.config_scan(args.scan_cfg, device=dev, shrink=args.shrink)
+        pts = scan["points"]                      # float32 [n, 8]  (pcl::PointXYZI layout, 32 B)
+        n = pts.shape[0]
+        del scan
+    else:
+        n = 0
+    if world > 1:
+        nt = torch.tensor([n], device=dev, dtype=torch.int64)
+        dist.broadcast(nt, 0)
+        n = int(nt.item())
+        if rank != 0:
+            pts = torch.empty((n, 8), device=dev, dtype=torch.float32)
+    torch.cuda.synchronize()
+
+    stream = torch.cuda.Stream(device=dev)
+    ctx = cc.Context(local)
+    ctx.set_stream(stream.cuda_stream)
+
+    begin, end, per = sharding.shard_range(n, rank, world)     # sorted positions of this rank
+    rows = per if world > 1 else n
+    # per-rank outputs (sorted order when sharded): eig3 | normal4 | feat7
+    eig = torch.empty((rows, 3), device=dev)
+    nrm = torch.empty((rows, 4), device=dev)
+    feat = torch.empty((rows, 7), device=dev)
+    if world > 1:
+        g_eig = torch.empty((world * per, 3), device=dev)
+        g_nrm = torch.empty((world * per, 4), device=dev)
+        g_feat = torch.empty((world * per, 7), device=dev)
+        if rank == 0:
+            o_eig = torch.empty((n, 3), device=dev)
+            o_nrm = torch.empty((n, 4), device=dev)
+            o_feat = torch.empty((n, 7), device=dev)
+    launches = [0]
+    kernel_ms = []
+
+    def step_device():
+        if world == 1:
+            ctx.set_cloud(pts)
+            launches[0] += ctx.stats()["launches_build"]
+            ctx.pca_knn_features_into(K, cc.COV_NM1, 0, eig, nrm, feat)
+            st = ctx.stats()
+            launches[0] += st["launches"]
+            kernel_ms.append(st["ms_query"])
+        else:
+            dist.broadcast(pts, 0)
+            ctx.set_cloud(pts)
+            launches[0] += ctx.stats()["launches_build"]
+            ctx.pca_knn_features_range(K, cc.COV_NM1, 0, begin, end, eig, nrm, feat)
+            st = ctx.stats()
+            launches[0] += st["launches"]
+            kernel_ms.append(st["ms_query"])
+            dist.all_gather_into_tensor(g_eig, eig)
+            dist.all_gather_into_tensor(g_nrm, nrm)
+            dist.all_gather_into_tensor(g_feat, feat)
+            if rank == 0:
+                ctx.unpermute(g_eig, o_eig)
+                ctx.unpermute(g_nrm, o_nrm)
+                ctx.unpermute(g_feat, o_feat)
+                launches[0] += 3
+
+    # host-buffer variant (e2e): pinned PointXYZI AoS in, pinned outputs out
+    if rank == 0:
+        h_pts = torch.empty((n, 8), dtype=torch.float32, pin_memory=True)
+        h_pts.copy_(pts)
+        h_eig = torch.empty((n, 3), dtype=torch.float32, pin_memory=True)
+        h_nrm = torch.empty((n, 4), dtype=torch.float32, pin_memory=True)
+        h_feat = torch.empty((n, 7), dtype=torch.float32, pin_memory=True)
+        np_pts, np_eig, np_nrm, np_feat = h_pts.numpy(), h_eig.numpy(), h_nrm.numpy(), h_feat.numpy()
+    h2d = n * 32
+    d2h = n * (12 + 16 + 28)
+
+    def step_host():
+        if world == 1:
+            ctx.set_cloud(np_pts)                                              # host AoS in: H2D inside the call
+            ctx.pca_knn_features_into(K, cc.COV_NM1, 0, np_eig, np_nrm, np_feat)   # host outputs: D2H inside the call
+        else:
+            if rank == 0:
+                pts.copy_(h_pts, non_blocking=True)                # H2D on rank 0, then NVLink broadcast
+            step_device()
+            if rank == 0:
+                h_eig.copy_(o_eig, non_blocking=True); h_nrm.copy_(o_nrm, non_blocking=True); h_feat.copy_(o_feat, non_blocking=True)
+
+    def timed(fn, steps, warmup):
+        with torch.cuda.stream(stream):
+            for _ in range(warmup):
+                fn()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(steps):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    sampler = ClockSampler(physical_device_index(local)) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    launches[0] = 0
+    kernel_ms.clear()
+    ms_dev = timed(step_device, args.steps, args.warmup)
+    n_launch = launches[0] * args.steps // (args.steps + args.warmup)
+    kms = kernel_ms[args.warmup:]
+    ms_e2e = timed(step_host, max(2, args.steps // 2), 1)
+    e2e_steps = max(2, args.steps // 2)
+    clocks = sampler.stop() if sampler else None
+
+    if rank == 0:
+        value = n * args.steps / (ms_dev * 1e-3)
+        e2e_v = n * e2e_steps / (ms_e2e * 1e-3)
+        peak, peak_src = _peaks()
+        q_rows = end - begin
+        k_ms = float(np.mean(kms))
+        achieved = BYTES_QUERY * q_rows / (k_ms * 1e-3) / 1e9
+        st = ctx.stats()
+        line = {"metric": METRIC, "value": value, "unit": "points/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
+                "e2e": {"value": e2e_v, "unit": "points/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "ms_per_step": ms_e2e / e2e_steps},
+                "gpu_launches": int(n_launch),
+                "clocks": clocks,
+                "roofline": {"bound": "hbm", "kernel": f"k_tile_topk<{K}> (kNN + covariance + eigensolve)", "achieved": achieved,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(),
+                             "peak_source": peak_src, "algorithmic_bytes_per_point": BYTES_QUERY, "points_per_launch": q_rows,
+                             "kernel_ms": k_ms,
+                             "whole_step_GBps": (BYTES_QUERY + BYTES_BUILD) * n / (ms_dev / args.steps * 1e-3) / 1e9},
+                "stage_ms": {"build": st["ms_build"], "query_kernel": k_ms}}
+        if not args.no_cpu_baseline and world == 1:
+            import oracle
+            cpts, sample = cpu_sample_points(args.scan_cfg, args.shrink)
+            t = cpu_pass(cpts)
+            line["cpu_baseline"] = {"value": cpts.shape[0] / t, "unit": "points/s", "cores": oracle.max_threads(), "kind": "port",
+                                    "sample": sample + f"; {t:.1f} s"}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _ncu_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "top_kernel_traffic.json")
+    try:
+        return float(json.load(open(p))["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
+if __name__ == "__main__":
+    main()

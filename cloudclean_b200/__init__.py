@@ -23,10 +23,10 @@ ERRORS = {0: "CCG_OK", -1: "CCG_ERR_INVALID", -2: "CCG_ERR_CUDA", -3: "CCG_ERR_N
 
 # every symbol include/ccgpu.h declares (tests/test_abi.py checks the header against this list and the .so)
 SYMBOLS = [
-    "ccg_create", "ccg_destroy", "ccg_last_error", "ccg_version", "ccg_get_stats", "ccg_set_cancel_flag",
+    "ccg_create", "ccg_destroy", "ccg_last_error", "ccg_version", "ccg_get_stats", "ccg_set_cancel_flag", "ccg_set_stream",
     "ccg_set_cloud", "ccg_cloud_size", "ccg_get_order", "ccg_knn", "ccg_radius", "ccg_pca_knn", "ccg_pca_radius",
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
-    "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute",
+    "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
 ]
 
 
@@ -65,6 +65,7 @@ def load_library():
     L.ccg_version.restype = i32
     L.ccg_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.ccg_set_cancel_flag.argtypes = [vp, vp]
+    L.ccg_set_stream.argtypes = [vp, vp]
     L.ccg_set_cloud.argtypes = [vp, vp, sz, sz]
     L.ccg_cloud_size.argtypes = [vp]
     L.ccg_cloud_size.restype = C.c_int64
@@ -81,6 +82,8 @@ def load_library():
     L.ccg_pca_knn_range.argtypes = [vp, i32, i32, vp, sz, sz, vp, vp]
     L.ccg_sor_mean_range.argtypes = [vp, i32, sz, sz, vp]
     L.ccg_unpermute.argtypes = [vp, vp, sz, vp]
+    L.ccg_pca_knn_features.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp]
+    L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     _lib = L
     return L
 
@@ -147,6 +150,10 @@ class Context:
             return torch.empty(shape, dtype=tdt, device=f"cuda:{self.device}")
         return np.empty(shape, dtype)
 
+    def set_stream(self, cuda_stream):
+        """run later calls on `cuda_stream` (an int cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream); None = own"""
+        self._check(self.L.ccg_set_stream(self.h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
     # ---- cloud -------------------------------------------------------------------------------------
     def set_cloud(self, points):
         """points: float32 [n, S>=3] (x, y, z first; S=8 mirrors pcl::PointXYZI).  numpy (host) or torch CUDA."""
@@ -203,6 +210,16 @@ class Context:
         """same, into caller-provided buffers (host numpy or torch CUDA) — what bench.py times"""
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn(self.h, k, cov_norm, _ptr(vp), _ptr(eig), _ptr(nrm)))
+
+    def pca_knn_features_into(self, k, cov_norm, formula_set, eig, nrm, feat, viewpoint=None):
+        """kNN + PCA + fused eigen features into caller buffers (host numpy or torch CUDA); any output may be None"""
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn_features(self.h, k, cov_norm, _ptr(vp), formula_set, _ptr(eig), _ptr(nrm), _ptr(feat)))
+
+    def pca_knn_features_range(self, k, cov_norm, formula_set, begin, end, eig_sorted, nrm_sorted, feat_sorted, viewpoint=None):
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn_features_range(self.h, k, cov_norm, _ptr(vp), formula_set, begin, end, _ptr(eig_sorted),
+                                                      _ptr(nrm_sorted), _ptr(feat_sorted)))
 
     # ---- a4 / a5 -----------------------------------------------------------------------------------
     def pca_radius(self, r, max_nn=0, cov_norm=COV_NM1, normalise_hist=False, viewpoint=None, want_normals=False,

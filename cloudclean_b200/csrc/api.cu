@@ -139,8 +139,9 @@ int ccg_create(ccg_ctx **out, int device_id) {
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
     ctx->sm_count = prop.multiProcessorCount;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
+    ctx->stream = ctx->own_stream;
     for (int i = 0; i < 8; ++i) if (cudaEventCreate(&ctx->ev[i]) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
     const char *cs = getenv("CCG_COLLECT_STATS");
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
@@ -157,7 +158,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release();
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
 }
@@ -173,6 +174,13 @@ int ccg_get_stats(const ccg_ctx *ctx, ccg_stats *out) {
 int ccg_set_cancel_flag(ccg_ctx *ctx, const volatile int *flag) {
     if (!ctx) return CCG_ERR_INVALID;
     ctx->cancel = flag;
+    return CCG_OK;
+}
+
+int ccg_set_stream(ccg_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return CCG_ERR_INVALID;
+    if (cudaSetDevice(ctx->device) == cudaSuccess && ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return CCG_OK;
 }
 
@@ -237,13 +245,16 @@ int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, 
 }
 
 static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise_hist, const float *vp, size_t begin, size_t end,
-                      int sorted_rows, float *eig3, float *normal4, int32_t *count, bool uncapped) {
+                      int sorted_rows, float *eig3, float *normal4, int32_t *count, bool uncapped, float *feat7 = nullptr,
+                      int formula_set = 0) {
     if (cov_norm < 0 || cov_norm > 2) return set_error(ctx, CCG_ERR_INVALID, "cov_norm must be 0, 1 or 2");
     size_t rows = sorted_rows ? (end > begin ? end - begin : 0) : ctx->n;
-    OutBuf oe, on, oc;
+    if (formula_set < 0 || formula_set > 1) return set_error(ctx, CCG_ERR_INVALID, "formula_set must be 0 or 1");
+    OutBuf oe, on, oc, of;
     CCG_TRY(oe.open(ctx, 0, eig3, rows * 12));
     CCG_TRY(on.open(ctx, 1, normal4, rows * 16));
     CCG_TRY(oc.open(ctx, 2, count, rows * 4));
+    CCG_TRY(of.open(ctx, 3, feat7, rows * 28));
     CCG_TRY(query_begin(ctx));
     if (!uncapped) {
         QueryArgs a = base_args(ctx);
@@ -251,6 +262,7 @@ static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise
         a.cov_norm = cov_norm; a.min_pts = 3; a.normalise_hist = normalise_hist; a.has_vp = vp ? 1 : 0;
         if (vp) for (int i = 0; i < 3; ++i) a.vp[i] = vp[i];
         a.eig3 = oe.dev<float>(); a.normal4 = on.dev<float>(); a.count = oc.dev<int32_t>();
+        a.feat7 = of.dev<float>(); a.formula_set = formula_set;
         CCG_TRY(launch_tile_query(ctx, a));
     } else {
         StreamArgs s{};
@@ -258,11 +270,29 @@ static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise
         s.cov_norm = cov_norm; s.min_pts = 3; s.normalise_hist = normalise_hist; s.has_vp = vp ? 1 : 0;
         if (vp) for (int i = 0; i < 3; ++i) s.vp[i] = vp[i];
         s.eig3 = oe.dev<float>(); s.normal4 = on.dev<float>(); s.count = oc.dev<int32_t>();
+        s.feat7 = of.dev<float>(); s.formula_set = formula_set;
         CCG_TRY(launch_tile_stream(ctx, s));
     }
     CCG_TRY(query_end(ctx));
-    CCG_TRY(oe.close()); CCG_TRY(on.close()); CCG_TRY(oc.close());
+    CCG_TRY(oe.close()); CCG_TRY(on.close()); CCG_TRY(oc.close()); CCG_TRY(of.close());
     return finish_call(ctx);
+}
+
+int ccg_pca_knn_features(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, float *eig3, float *normal4,
+                         float *feat7) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, 0, ctx->n, 0, eig3, normal4, nullptr, false, feat7, formula_set);
+}
+
+int ccg_pca_knn_features_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
+                               float *eig3_sorted, float *normal4_sorted, float *feat7_sorted) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    if (begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "begin must be a multiple of 32");
+    if (end > ctx->n) end = ctx->n;
+    return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, begin, end, 1, eig3_sorted, normal4_sorted, nullptr, false,
+                      feat7_sorted, formula_set);
 }
 
 int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4) {

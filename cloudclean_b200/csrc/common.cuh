@@ -61,7 +61,8 @@ struct HostBuf {   // grow-only pinned host buffer
 struct ccg_ctx {
     int device = 0;
     int sm_count = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;       // the stream calls run on (own_stream unless ccg_set_stream)
+    cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev[8] = {};
     const volatile int *cancel = nullptr;
@@ -140,7 +141,7 @@ struct QueryArgs {
     int32_t *idx; float *d2; int32_t *count;
     // MODE_PCA
     int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
-    float *eig3; float *normal4;
+    float *eig3; float *normal4; float *feat7; int formula_set;
     // MODE_SOR
     int mean_k; float *mean_d;
 };
@@ -154,7 +155,7 @@ struct StreamArgs {
     int sorted_rows;
     int32_t *count;
     int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
-    float *eig3; float *normal4;
+    float *eig3; float *normal4; float *feat7; int formula_set;
 };
 int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a);
 
@@ -165,7 +166,7 @@ struct PointArgs {
     int list_rows;          // 1: output row = position in the list, 0: row = original index
     int32_t *idx; float *d2; int32_t *count;
     int cov_norm; int min_pts; int normalise_hist; int has_vp; float vp[3];
-    float *eig3; float *normal4;
+    float *eig3; float *normal4; float *feat7; int formula_set;
     int mean_k; float *mean_d;
 };
 int launch_point_query(ccg_ctx *ctx, const PointArgs &a);

@@ -77,7 +77,8 @@ __global__ void __launch_bounds__(256) k_fan_normals(const float4 *__restrict__ 
         const float cxp = __fsub_rn(__fmul_rn(v1y, v2z), __fmul_rn(v1z, v2y));
         const float cyp = __fsub_rn(__fmul_rn(v1z, v2x), __fmul_rn(v1x, v2z));
         const float czp = __fsub_rn(__fmul_rn(v1x, v2y), __fmul_rn(v1y, v2x));
-        const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(cxp, cxp), __fmul_rn(cyp, cyp)), __fmul_rn(czp, czp)));
+        // Eigen 3.2 squaredNorm of a Vector3f: fixed-size redux halves the range, a0 + (a1 + a2) [EXT]
+        const float nn = __fsqrt_rn(__fadd_rn(__fmul_rn(cxp, cxp), __fadd_rn(__fmul_rn(cyp, cyp), __fmul_rn(czp, czp))));
         const float tx = __fdiv_rn(cxp, nn), ty = __fdiv_rn(cyp, nn), tz = __fdiv_rn(czp, nn);
         if (tx != tx || ty != ty || tz != tz) continue;        // :376-382
         ax = __fadd_rn(ax, tx); ay = __fadd_rn(ay, ty); az = __fadd_rn(az, tz);
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(256) k_fan_normals(const float4 *__restrict__ 
         missing_flag[i] = 1;
         return;
     }
-    const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(ax, ax), __fmul_rn(ay, ay)), __fmul_rn(az, az)));
+    const float nn = __fsqrt_rn(__fadd_rn(__fmul_rn(ax, ax), __fadd_rn(__fmul_rn(ay, ay), __fmul_rn(az, az))));
     normal4[ci] = make_float4(__fdiv_rn(ax, nn), __fdiv_rn(ay, nn), __fdiv_rn(az, nn), 1.0f);   // :416-422
 }
 

@@ -271,7 +271,26 @@ struct PcaOut {
     int cov_norm, min_pts, normalise_hist, has_vp;
     float vp[3];
     float *eig3, *normal4;
+    float *feat7; int formula_set;     // optional fused a9 epilogue
 };
+
+// a9: the 7 eigen features of Markov::mkFeatureVector (markov.cpp:449-475) from descending (l0, l1, l2).
+// formula_set 0 = exactly as written there (including its slips), 1 = textbook definitions.
+__device__ __forceinline__ void features7(float l0, float l1, float l2, int formula_set, float *o) {
+    o[0] = __fdiv_rn(__fsub_rn(l0, l2), l0);                 // markov.cpp:451
+    o[1] = __fdiv_rn(__fsub_rn(l1, l2), l0);                 // :455
+    o[2] = __fdiv_rn(l2, l0);                                // :459
+    o[3] = __fdiv_rn(__fsub_rn(l0, l1), l0);                 // :463
+    if (formula_set == 0) {
+        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l0));      // :467 (sic)
+        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l0));   // :471 (sic)
+        o[6] = __fdiv_rn(l0, __fadd_rn(__fadd_rn(l0, l1), l2));     // :475 (sic)
+    } else {
+        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l2));
+        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l2));
+        o[6] = __fdiv_rn(l2, __fadd_rn(__fadd_rn(l0, l1), l2));
+    }
+}
 
 // moments of (p - q): m = {sx sy sz sxx sxy sxz syy syz szz}, cnt points -> outputs for one row
 __device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, const float m[9], int cnt, size_t row) {
@@ -302,6 +321,13 @@ __device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, con
     }
     if (o.eig3) { float *p = o.eig3 + row * 3; p[0] = e0; p[1] = e1; p[2] = e2; }
     if (o.normal4) reinterpret_cast<float4 *>(o.normal4)[row] = make_float4(nx, ny, nz, curv);
+    if (o.feat7) {
+        float f[7];
+        features7(e0, e1, e2, o.formula_set, f);
+        float *p = o.feat7 + row * 7;
+#pragma unroll
+        for (int i = 0; i < 7; ++i) p[i] = f[i];
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -371,7 +397,7 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
         }
         if (!active) cnt = 0;
         PcaOut o = P.pca;
-        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; }
+        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; o.feat7 = nullptr; }
         pca_finish(o, q, m, cnt, row);
         if (P.count && active) P.count[row] = cnt;
     } else {   // MODE_SOR: mean distance to the mean_k nearest, self (first entry) dropped
@@ -414,7 +440,7 @@ __global__ void __launch_bounds__(128) k_tile_stream(const __grid_constant__ Tre
     const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)__float_as_int(q.w);
     if (P.mode == 1) {
         PcaOut o = P.pca;
-        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; }
+        if (!active) { o.eig3 = nullptr; o.normal4 = nullptr; o.feat7 = nullptr; }
         pca_finish(o, q, v.m, active ? v.count : 0, row);
     }
     if (P.count && active) P.count[row] = v.count;
@@ -442,7 +468,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.idx = a.idx; P.d2 = a.d2; P.count = a.count;
     P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
     for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
-    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {
@@ -485,7 +511,7 @@ int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a) {
     P.count = a.count;
     P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
     for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
-    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {
         CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 8, ctx->stream));
@@ -510,21 +536,11 @@ int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a) {
 __global__ void __launch_bounds__(256) k_features(const float *__restrict__ eig3, size_t n, int formula_set, float *__restrict__ out) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    float l0 = eig3[3 * i], l1 = eig3[3 * i + 1], l2 = eig3[3 * i + 2];
+    float f[7];
+    features7(eig3[3 * i], eig3[3 * i + 1], eig3[3 * i + 2], formula_set, f);
     float *o = out + 7 * i;
-    o[0] = __fdiv_rn(__fsub_rn(l0, l2), l0);                 // markov.cpp:451
-    o[1] = __fdiv_rn(__fsub_rn(l1, l2), l0);                 // :455
-    o[2] = __fdiv_rn(l2, l0);                                // :459
-    o[3] = __fdiv_rn(__fsub_rn(l0, l1), l0);                 // :463
-    if (formula_set == 0) {
-        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l0));      // :467 (sic)
-        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l0));   // :471 (sic)
-        o[6] = __fdiv_rn(l0, __fadd_rn(__fadd_rn(l0, l1), l2));     // :475 (sic)
-    } else {
-        o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l2));
-        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l2));
-        o[6] = __fdiv_rn(l2, __fadd_rn(__fadd_rn(l0, l1), l2));
-    }
+#pragma unroll
+    for (int j = 0; j < 7; ++j) o[j] = f[j];
 }
 
 __global__ void __launch_bounds__(256) k_eigen_scalar(const float *__restrict__ eig3, size_t n, int which, float *__restrict__ out) {
@@ -753,7 +769,7 @@ int launch_point_query(ccg_ctx *ctx, const PointArgs &a) {
     P.idx = a.idx; P.d2 = a.d2; P.count = a.count;
     P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
     for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
-    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4;
+    P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     k_point_query<<<(a.nq + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
     ctx->stats.launches++;

@@ -58,10 +58,11 @@ def _scene(name, scale, rng):
 
 
 def make_scan(scan_w, scan_h, scene="room", seed=1, scale=1.0, dropout=0.05, device="cpu", chunk_cols=None,
-              el_min_deg=-60.0, el_max_deg=90.0, duplicate=0):
+              el_min_deg=-60.0, el_max_deg=90.0, duplicate=0, max_cols=None):
     """Ray-cast an organised scan.
 
     Returns dict(points float32[n,8] (PointXYZI layout), cloud_to_grid int32[n], scan_w, scan_h, scene).
+    `max_cols` stops after that many scan columns (a file-order prefix of the same scan — the bounded CPU sample).
     `duplicate` > 0 appends that many exact copies of one point (adversarial cell occupancy, config 5)."""
     dev = torch.device(device)
     rng = np.random.default_rng(seed)
@@ -76,8 +77,9 @@ def make_scan(scan_w, scan_h, scene="room", seed=1, scale=1.0, dropout=0.05, dev
     blobs = None
     if sc["blobs"] is not None:
         blobs = (torch.as_tensor(sc["blobs"][0], device=dev, dtype=torch.float32), float(sc["blobs"][1]))
-    for c0 in range(0, scan_w, chunk_cols):
-        c1 = min(scan_w, c0 + chunk_cols)
+    last_col = scan_w if max_cols is None else min(scan_w, int(max_cols))
+    for c0 in range(0, last_col, chunk_cols):
+        c1 = min(last_col, c0 + chunk_cols)
         az = (torch.arange(c0, c1, device=dev, dtype=torch.float64) + 0.5) * (2.0 * math.pi / scan_w)
         ce, se = torch.cos(el), torch.sin(el)
         d = torch.stack([(torch.cos(az)[:, None] * ce[None, :]), (torch.sin(az)[:, None] * ce[None, :]),
@@ -162,9 +164,11 @@ def make_scan_np(*args, **kw):
 # the scene but shrink the grid so the CPU oracle finishes in seconds.
 CONFIGS = {
     1: dict(scan_w=1024, scan_h=1024, scene="room", seed=1, dropout=0.05),
-    2: dict(scan_w=4096, scan_h=2560, scene="outdoor", seed=2, dropout=0.05),
-    3: dict(scan_w=7680, scan_h=3968, scene="outdoor", seed=3, dropout=0.02),
-    4: dict(scan_w=14336, scan_h=7168, scene="outdoor", seed=4, dropout=0.02),
+    # outdoor rays that leave the scene (sky, beyond max_range) return nothing — about 57 % of the rays are valid
+    # returns — so the grids are sized for the POINT counts BASELINE.json names (10 M / 30 M / 100 M valid points).
+    2: dict(scan_w=5632, scan_h=3200, scene="outdoor", seed=2, dropout=0.05),
+    3: dict(scan_w=10240, scan_h=5120, scene="outdoor", seed=3, dropout=0.02),
+    4: dict(scan_w=18688, scan_h=9344, scene="outdoor", seed=4, dropout=0.02),
     5: dict(scan_w=8192, scan_h=4096, scene="planar", seed=5, dropout=0.02),
 }
 

@@ -75,6 +75,9 @@ int ccg_version(void);
 int ccg_get_stats(const ccg_ctx *ctx, ccg_stats *out);
 /* Optional cancellation: checked between stages, honours PointCloud::deleting_ (normalestimation.cpp:305-306). */
 int ccg_set_cancel_flag(ccg_ctx *ctx, const volatile int *flag);
+/* Run every later call on the caller's CUDA stream (a cudaStream_t, e.g. the stream NCCL collectives are enqueued
+ * on, so that broadcast -> build -> query -> gather needs no extra synchronisation); NULL restores the ctx's own. */
+int ccg_set_stream(ccg_ctx *ctx, void *cuda_stream);
 
 /* ---- cloud ---------------------------------------------------------------------------------------- */
 /* Replaces pcl::KdTreeFLANN::setInputCloud (cv.h:83-84, cv.cpp:254-255, normalestimation.cpp:428-429) and the
@@ -106,6 +109,11 @@ int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, 
  * smallest eigenvalue + curvature l2/(l0+l1+l2); flipped towards viewpoint3 (3 floats) when that is non-NULL
  * (pcl::flipNormalTowardsViewpoint, cf. the commented call at normalestimation.cpp:417).  Either output may be NULL. */
 int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4);
+
+/* Same with the a9 epilogue fused into the kernel: feat7 (n*7, see ccg_features) is computed from the eigenvalues
+ * while they are still in registers, so Markov::mkFeatureVector's inputs (markov.cpp:449-475) cost no second pass. */
+int ccg_pca_knn_features(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, float *eig3, float *normal4,
+                         float *feat7);
 
 /* ---- a4 / a5 / a6: radius + PCA (getPCA / getHist) ------------------------------------------------ */
 /* Replaces the body of getPCA<PointT> (cv.h:96-113) and getHist (cv.cpp:271-295): strict radius search with
@@ -150,6 +158,8 @@ int ccg_grid_normals(ccg_ctx *ctx, const int32_t *cloud_to_grid, int scan_w, int
  * order; ccg_unpermute scatters gathered rows back to original order. */
 int ccg_pca_knn_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, size_t begin, size_t end,
                       float *eig3_sorted, float *normal4_sorted);
+int ccg_pca_knn_features_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
+                               float *eig3_sorted, float *normal4_sorted, float *feat7_sorted);
 int ccg_sor_mean_range(ccg_ctx *ctx, int mean_k, size_t begin, size_t end, float *mean_d_sorted);
 /* out[order[i]] = in[i] for rows of row_bytes (multiple of 4) bytes; in/out host or device */
 int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void *rows_original);

@@ -682,7 +682,7 @@ int cco_grid_normals(const void *xyz, int n, int stride_bytes, const int32_t *cl
             float v1x = q1[0] - p0[0], v1y = q1[1] - p0[1], v1z = q1[2] - p0[2];
             float v2x = q2[0] - p0[0], v2y = q2[1] - p0[1], v2z = q2[2] - p0[2];
             float cxp = v1y * v2z - v1z * v2y, cyp = v1z * v2x - v1x * v2z, czp = v1x * v2y - v1y * v2x;
-            float nn = sqrtf((cxp * cxp + cyp * cyp) + czp * czp);
+            float nn = sqrtf(cxp * cxp + (cyp * cyp + czp * czp));   /* Eigen 3.2 fixed-size redux halves the range: a0 + (a1 + a2) [EXT] */
             float tx = cxp / nn, ty = cyp / nn, tz = czp / nn;          /* 0/0 = NaN, :376-382 */
             if (tx != tx || ty != ty || tz != tz) continue;
             ax += tx; ay += ty; az += tz;
@@ -694,7 +694,7 @@ int cco_grid_normals(const void *xyz, int n, int stride_bytes, const int32_t *cl
             o[0] = o[1] = o[2] = o[3] = NAN;
             continue;
         }
-        float nn = sqrtf((ax * ax + ay * ay) + az * az);
+        float nn = sqrtf(ax * ax + (ay * ay + az * az));
         o[0] = ax / nn; o[1] = ay / nn; o[2] = az / nn; o[3] = 1.0f;
     }
 #undef P

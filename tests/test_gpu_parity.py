@@ -1,0 +1,349 @@
+"""GPU parity: every C-ABI entry point of libccgpu.so against the CPU oracle and the committed golden vectors.
+
+Bars (BASELINE.json north_star): neighbour index sets / distances / counts / outlier masks / stage-(ii) grid
+normals BIT-EXACT; eigenvalues |d lambda_i| <= 1e-4 * lambda_0 against the fp64 truth; normals |cos| >= 1 - 1e-5
+wherever the normal is defined ((l1-l2)/l0 above GAP_MIN); curvature within 1e-5 absolute."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import cloudclean_b200 as cc
+import oracle
+from cloudclean_b200 import synth
+from conftest import clouds_small
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+EIG_TOL = 1e-4          # relative to lambda_0
+COS_TOL = 1e-5
+GAP_MIN = 1e-3          # below this (l1-l2)/l0 the smallest eigenvector is ill-conditioned in fp32: normal not compared
+SMALL = clouds_small()
+
+
+def gold(name):
+    return dict(np.load(os.path.join(GOLD, name + ".npz")))
+
+
+def check_pca(eig, nrm, ref, check_normals=True):
+    truth = ref["eig64"]
+    scale = np.maximum(truth[:, :1], 1e-30)
+    marker = (truth[:, 0] == 0) & (truth[:, 2] == 1)
+    err = np.abs(eig - truth) / scale
+    assert err[~marker].max(initial=0) <= EIG_TOL
+    assert np.array_equal(eig[marker], truth[marker].astype(np.float32))
+    if check_normals and nrm is not None:
+        ok = (ref["gap64"] > GAP_MIN) & ~marker
+        cos = np.abs((nrm[:, :3].astype(np.float64) * ref["nrm64"][:, :3]).sum(1))
+        assert (1 - cos[ok]).max(initial=0) <= COS_TOL
+        assert np.abs(nrm[ok, 3] - ref["nrm64"][ok, 3]).max(initial=0) <= 1e-5
+        assert np.isnan(nrm[marker]).all()
+        unit = np.linalg.norm(nrm[~marker, :3].astype(np.float64), axis=1)
+        assert np.abs(unit - 1).max(initial=0) <= 1e-5
+
+
+# ---- a1 kNN --------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["plane4x5", "room40x36"])
+def test_knn_golden(gpu_ctx, name):
+    g = gold(name)
+    gpu_ctx.set_cloud(g["points"])
+    for k in (1, 8, 20, 50):
+        idx, d2 = gpu_ctx.knn(k)
+        assert np.array_equal(idx, g[f"knn{k}_idx"])
+        assert np.array_equal(d2, g[f"knn{k}_d2"])
+
+
+@pytest.mark.parametrize("stride_floats", [3, 4, 8, 12])
+def test_knn_strides_and_device_pointers(gpu_ctx, stride_floats):
+    import torch
+    xyz = SMALL["lattice_ties"][:, :3]
+    pts = np.zeros((xyz.shape[0], stride_floats), np.float32)
+    pts[:, :3] = xyz
+    ref_i, ref_d = oracle.Tree(pts).knn(20)
+    gpu_ctx.set_cloud(pts)
+    idx, d2 = gpu_ctx.knn(20)
+    assert np.array_equal(idx, ref_i) and np.array_equal(d2, ref_d)
+    dev = torch.from_numpy(pts).cuda()
+    gpu_ctx.set_cloud(dev)
+    idx, d2 = gpu_ctx.knn(20)
+    assert idx.is_cuda and np.array_equal(idx.cpu().numpy(), ref_i) and np.array_equal(d2.cpu().numpy(), ref_d)
+
+
+def test_order_is_a_permutation(gpu_ctx):
+    pts = SMALL["uniform"]
+    gpu_ctx.set_cloud(pts)
+    o = gpu_ctx.order()
+    assert np.array_equal(np.sort(o), np.arange(pts.shape[0], dtype=np.int32))
+
+
+# ---- a2 / a3 radius ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["uniform", "lattice_ties", "coplanar", "dups_only", "n2", "clusters_outliers"])
+@pytest.mark.parametrize("r,cap", [(0.05, 8), (0.25, 20), (0.125, 64)])
+@pytest.mark.parametrize("strict", [True, False])
+def test_radius_lists(gpu_ctx, name, r, cap, strict):
+    pts = SMALL[name]
+    T = oracle.Tree(pts)
+    ref = T.radius(r, cap=cap, strict_lt=strict)
+    gpu_ctx.set_cloud(pts)
+    got = gpu_ctx.radius(r, max_nn=cap, strict_lt=strict)
+    assert np.array_equal(got["count"], ref["count"])
+    assert np.array_equal(got["idx"], ref["idx"])
+    assert np.array_equal(got["d2"], ref["d2"])
+
+
+@pytest.mark.parametrize("name", ["uniform", "lattice_ties", "clusters_outliers", "n1"])
+@pytest.mark.parametrize("strict", [True, False])
+def test_radius_counts(gpu_ctx, name, strict):
+    pts = SMALL[name]
+    T = oracle.Tree(pts)
+    gpu_ctx.set_cloud(pts)
+    for r in (0.0, 0.125, 0.5):            # 0.125 and 0.5 are lattice distances: the strict/inclusive edge is hit
+        total = T.radius(r, strict_lt=strict, lists=False)["total"]
+        got = gpu_ctx.radius(r, max_nn=0, strict_lt=strict, lists=False)["count"]
+        assert np.array_equal(got, total)
+        got = gpu_ctx.radius(r, max_nn=7, strict_lt=strict, lists=False)["count"]
+        assert np.array_equal(got, np.minimum(total, 7))
+
+
+@pytest.mark.parametrize("name", ["plane4x5", "room40x36"])
+def test_radius_golden(gpu_ctx, name):
+    g = gold(name)
+    gpu_ctx.set_cloud(g["points"])
+    for r, cap in ((0.3, 20), (0.12, 8)):
+        tag = f"r{int(r * 100):03d}_c{cap}"
+        got = gpu_ctx.radius(r, max_nn=cap, strict_lt=True)
+        assert np.array_equal(got["idx"], g[f"rad_{tag}_idx"])
+        assert np.array_equal(got["d2"], g[f"rad_{tag}_d2"])
+        assert np.array_equal(got["count"], g[f"rad_{tag}_count"])
+        assert np.array_equal(gpu_ctx.radius(r, lists=False)["count"], g[f"rad_{tag}_total"])
+        assert np.array_equal(gpu_ctx.radius(r, strict_lt=False, lists=False)["count"], g[f"rad_{tag}_total_incl"])
+
+
+# ---- a12 kNN + PCA -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", list(SMALL.keys()))
+@pytest.mark.parametrize("k,cov", [(20, cc.COV_NM1), (10, cc.COV_N), (50, cc.COV_SCATTER)])
+def test_pca_knn(gpu_ctx, name, k, cov):
+    pts = SMALL[name]
+    gpu_ctx.set_cloud(pts)
+    eig, nrm = gpu_ctx.pca_knn(k, cov)
+    ri, _ = oracle.Tree(pts).knn(k)
+    ref = oracle.pca_lists(pts, ri, cov_norm=cov)
+    check_pca(eig, nrm, ref)
+    assert (eig[:, 0] >= eig[:, 1]).all() and ((eig[:, 1] >= eig[:, 2]) | (eig[:, 2] == 1)).all()
+
+
+def test_pca_knn_golden_and_viewpoint(gpu_ctx):
+    g = gold("room40x36")
+    pts = g["points"]
+    gpu_ctx.set_cloud(pts)
+    for cn in (0, 1, 2):
+        eig, nrm = gpu_ctx.pca_knn(20, cn)
+        truth = g[f"pca20_cov{cn}_eig"]
+        assert (np.abs(eig - truth) / truth[:, :1]).max() <= EIG_TOL
+        gap = (truth[:, 1] - truth[:, 2]) / truth[:, 0]
+        cos = np.abs((nrm[:, :3] * g[f"pca20_cov{cn}_nrm"][:, :3]).sum(1))
+        assert (1 - cos[gap > GAP_MIN]).max() <= COS_TOL
+    vp = np.array([0.0, 0.0, 0.0], np.float32)            # the scanner: every flipped normal faces it
+    eig, nrm = gpu_ctx.pca_knn(20, cc.COV_NM1, viewpoint=vp)
+    assert ((nrm[:, :3] * (vp[None, :] - pts[:, :3])).sum(1) >= 0).all()
+
+
+def test_pca_knn_fused_features_equal_standalone(gpu_ctx):
+    pts = SMALL["uniform"]
+    n = pts.shape[0]
+    gpu_ctx.set_cloud(pts)
+    eig, nrm = gpu_ctx.pca_knn(20, cc.COV_NM1)
+    for fs in (0, 1):
+        e2, n2, f2 = np.empty((n, 3), np.float32), np.empty((n, 4), np.float32), np.empty((n, 7), np.float32)
+        gpu_ctx.pca_knn_features_into(20, cc.COV_NM1, fs, e2, n2, f2)
+        assert np.array_equal(e2, eig) and np.array_equal(n2, nrm)
+        assert np.array_equal(f2, gpu_ctx.features(eig, fs), equal_nan=True)
+
+
+# ---- a4 / a5 / a6 radius + PCA (getPCA / getHist) -------------------------------------------------------
+@pytest.mark.parametrize("name", ["uniform", "coplanar", "clusters_outliers", "n2", "lattice_ties"])
+@pytest.mark.parametrize("r,max_nn", [(0.2, 20), (0.1, 64), (0.15, 0), (0.2, 1000)])
+def test_pca_radius_getpca(gpu_ctx, name, r, max_nn):
+    pts = SMALL[name]
+    n = pts.shape[0]
+    T = oracle.Tree(pts)
+    total = T.radius(r, strict_lt=True, lists=False)["total"]
+    gpu_ctx.set_cloud(pts)
+    if max_nn > cc.MAX_K and max_nn < n and (total > max_nn).any():
+        with pytest.raises(cc.CcgError) as e:
+            gpu_ctx.pca_radius(r, max_nn)
+        assert e.value.code == -5
+        return
+    cap = n if (max_nn == 0 or max_nn >= n) else max_nn          # FLANN caps only when 0 < max_nn < n
+    lists = T.radius(r, cap=cap, strict_lt=True)
+    ref = oracle.pca_lists(pts, lists["idx"], count=lists["count"], cov_norm=cc.COV_NM1)
+    eig, nrm, count = gpu_ctx.pca_radius(r, max_nn, cc.COV_NM1, want_normals=True)
+    assert np.array_equal(count, lists["count"])
+    check_pca(eig, nrm, ref)
+    # getHist (cv.cpp:293): the same eigenvalues L2-normalised
+    hist, _, _ = gpu_ctx.pca_radius(r, max_nn, cc.COV_NM1, normalise_hist=True)
+    t = ref["eig64"] / np.maximum(np.linalg.norm(ref["eig64"], axis=1, keepdims=True), 1e-300)
+    assert np.abs(hist - t).max() <= 2e-4
+
+
+def test_pca_radius_golden(gpu_ctx):
+    g = gold("room40x36")
+    gpu_ctx.set_cloud(g["points"])
+    for r, cap in ((0.3, 20), (0.12, 8)):
+        tag = f"r{int(r * 100):03d}_c{cap}"
+        eig, _, count = gpu_ctx.pca_radius(r, cap, cc.COV_NM1)
+        assert np.array_equal(count, g[f"rad_{tag}_count"])
+        truth = g[f"pcarad_{tag}_eig"]
+        marker = count < 3
+        assert np.array_equal(eig[marker], truth[marker].astype(np.float32))
+        assert (np.abs(eig - truth)[~marker] / truth[~marker, :1]).max() <= EIG_TOL
+
+
+# ---- a9 features ---------------------------------------------------------------------------------------
+def test_features_and_scalars(gpu_ctx):
+    pts = SMALL["uniform"]
+    gpu_ctx.set_cloud(pts)
+    eig, _, _ = gpu_ctx.pca_radius(0.12, 20)              # includes (0,0,1) markers
+    assert ((eig[:, 0] == 0) & (eig[:, 2] == 1)).any()
+    for fs in (0, 1):
+        f = gpu_ctx.features(eig, fs)
+        ref = oracle.features(eig, fs)
+        assert np.array_equal(f[:, :4], ref[:, :4], equal_nan=True)          # +,-,/ only: bit-exact
+        assert np.allclose(f, ref, rtol=4e-6, atol=1e-7, equal_nan=True)     # cbrtf / logf: libm vs CUDA, few ulp
+    assert np.array_equal(gpu_ctx.eigen_scalar(eig, 0), oracle.eigen_ratio(eig))
+    assert np.array_equal(gpu_ctx.eigen_scalar(eig, 1), oracle.plane_similarity(eig))
+    g = gold("room40x36")
+    e32 = g["pca20_cov1_eig"].astype(np.float32)
+    for fs in (0, 1):
+        assert np.allclose(gpu_ctx.features(e32, fs), g[f"feat_set{fs}"], rtol=4e-6, atol=1e-7, equal_nan=True)
+
+
+# ---- a11 SOR -------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", list(SMALL.keys()))
+@pytest.mark.parametrize("k,alpha", [(8, 1.0), (30, 1.0), (63, 0.0)])
+def test_sor_mask(gpu_ctx, name, k, alpha):
+    pts = SMALL[name]
+    gpu_ctx.set_cloud(pts)
+    mask, md = gpu_ctx.sor_mask(k, alpha)
+    rmask, rmd, _, _ = oracle.Tree(pts).sor(k, alpha)
+    assert np.array_equal(md, rmd)
+    assert np.array_equal(mask, rmask)
+
+
+def test_sor_golden(gpu_ctx):
+    for name in ("plane4x5", "room40x36"):
+        g = gold(name)
+        gpu_ctx.set_cloud(g["points"])
+        for k, a in ((8, 1.0), (30, 0.5)):
+            mask, md = gpu_ctx.sor_mask(k, a)
+            assert np.array_equal(md, g[f"sor{k}_mean_d"]) and np.array_equal(mask, g[f"sor{k}_mask"])
+
+
+# ---- a10 radius / min-neighbour filter -------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["uniform", "lattice_ties", "clusters_outliers", "n33"])
+@pytest.mark.parametrize("r,mn", [(0.1, 10), (0.5, 10), (1.0, 3)])
+@pytest.mark.parametrize("prefilter", [False, True])
+def test_radius_count_mask(gpu_ctx, name, r, mn, prefilter):
+    pts = SMALL[name]
+    gpu_ctx.set_cloud(pts)
+    got = gpu_ctx.radius_count_mask(r, mn, prefilter)
+    ref = oracle.Tree(pts).radius_outliers(r, mn, prefilter)
+    assert np.array_equal(got, ref)
+
+
+# ---- a7 grid normals -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["plane4x5", "room40x36"])
+def test_grid_normals_golden(gpu_ctx, name):
+    g = gold(name)
+    w, h = int(g["scan_w"]), int(g["scan_h"])
+    gpu_ctx.set_cloud(g["points"])
+    s2, miss2 = gpu_ctx.grid_normals(g["cloud_to_grid"], w, h, fallback=False)
+    assert np.array_equal(s2, g["gridn_stage2"], equal_nan=True) and miss2 == len(g["gridn_missing"])
+    s3, miss3 = gpu_ctx.grid_normals(g["cloud_to_grid"], w, h, fallback=True)
+    assert np.array_equal(s3, g["gridn_final"], equal_nan=True) and miss3 == int(g["gridn_still"])
+
+
+@pytest.mark.parametrize("w,h,dropout,seed", [(64, 48, 0.05, 1), (96, 64, 0.45, 2), (33, 7, 0.6, 3)])
+def test_grid_normals_scan(gpu_ctx, w, h, dropout, seed):
+    s = synth.make_scan_np(w, h, scene="room", seed=seed, dropout=dropout)
+    pts, c2g = s["points"], s["cloud_to_grid"]
+    gpu_ctx.set_cloud(pts)
+    for fb in (False, True):
+        got, miss = gpu_ctx.grid_normals(c2g, w, h, fallback=fb)
+        ref, rmiss = oracle.grid_normals(pts, c2g, w, h, fallback=fb)
+        assert np.array_equal(got, ref, equal_nan=True)
+        assert miss == rmiss
+    with pytest.raises(cc.CcgError):
+        gpu_ctx.grid_normals(c2g + w * h, w, h)            # grid index outside the scan
+
+
+# ---- sharding entry points ---------------------------------------------------------------------------------
+def test_ranges_and_unpermute_reproduce_the_full_call(gpu_ctx):
+    from cloudclean_b200 import sharding
+    pts = SMALL["uniform"]
+    n = pts.shape[0]
+    gpu_ctx.set_cloud(pts)
+    eig, nrm = gpu_ctx.pca_knn(20, cc.COV_NM1)
+    feat = gpu_ctx.features(eig, 0)
+    _, md = gpu_ctx.sor_mask(30, 1.0)
+    world = 3
+    per = sharding.shard_range(n, 0, world)[2]
+    g_e, g_n = np.zeros((world * per, 3), np.float32), np.zeros((world * per, 4), np.float32)
+    g_f, g_m = np.zeros((world * per, 7), np.float32), np.zeros((world * per, 1), np.float32)
+    for r in range(world):
+        b, e, _ = sharding.shard_range(n, r, world)
+        se, sn, sf = np.zeros((per, 3), np.float32), np.zeros((per, 4), np.float32), np.zeros((per, 7), np.float32)
+        sm = np.zeros((per, 1), np.float32)
+        gpu_ctx.pca_knn_features_range(20, cc.COV_NM1, 0, b, e, se, sn, sf)
+        gpu_ctx.sor_mean_range(30, b, e, sm)
+        g_e[r * per:(r + 1) * per], g_n[r * per:(r + 1) * per], g_f[r * per:(r + 1) * per] = se, sn, sf
+        g_m[r * per:(r + 1) * per] = sm
+    for gathered, full in ((g_e, eig), (g_n, nrm), (g_f, feat), (g_m, md[:, None])):
+        out = np.empty_like(full)
+        gpu_ctx.unpermute(gathered, out)
+        assert np.array_equal(out, full, equal_nan=True)
+    order = gpu_ctx.order()
+    assert np.array_equal(g_e[:n], eig[order])
+
+
+# ---- error behaviour ---------------------------------------------------------------------------------------
+def test_errors_and_empty_cloud():
+    ctx = cc.Context(0)
+    with pytest.raises(cc.CcgError) as e:
+        ctx.n = 4
+        ctx.on_device = False
+        ctx.knn(3)
+    assert e.value.code == -3                                 # CCG_ERR_NO_CLOUD
+    bad = SMALL["n33"].copy()
+    bad[5, 1] = np.nan
+    with pytest.raises(cc.CcgError) as e:
+        ctx.set_cloud(bad)
+    assert e.value.code == -4                                 # CCG_ERR_NONFINITE (PCL's kd-tree rejects these too)
+    ctx.set_cloud(SMALL["n33"])
+    for k in (0, 65):
+        with pytest.raises(cc.CcgError) as e:
+            ctx.knn(k)
+        assert e.value.code == -5
+    with pytest.raises(cc.CcgError) as e:
+        ctx.radius(-1.0, 5)
+    assert e.value.code == -1
+    with pytest.raises(cc.CcgError) as e:
+        ctx.pca_knn(20, 7)
+    assert e.value.code == -1
+    flag = ctypes.c_int(1)
+    ctx.L.ccg_set_cancel_flag(ctx.h, ctypes.byref(flag))
+    with pytest.raises(cc.CcgError) as e:
+        ctx.knn(5)
+    assert e.value.code == -6                                 # honours PointCloud::deleting_
+    flag.value = 0
+    idx, _ = ctx.knn(5)
+    assert idx.shape == (33, 5)
+    ctx.L.ccg_set_cancel_flag(ctx.h, None)
+    ctx.set_cloud(np.zeros((0, 8), np.float32))               # empty cloud: every call is a no-op
+    idx, d2 = ctx.knn(4)
+    assert idx.shape == (0, 4)
+    mask, md = ctx.sor_mask(5, 1.0)
+    assert mask.shape == (0,)
+    ctx.close()

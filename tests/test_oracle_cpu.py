@@ -1,0 +1,161 @@
+"""CPU tests of the oracle (test infrastructure): the C restatement against the committed golden vectors
+(tests/golden/, produced by independent numpy/python restatements), against an in-test numpy brute force, and
+against two independent exact searches (scipy cKDTree; OpenCV's bundled FLANN KDTREE_SINGLE when importable)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import clouds_small
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDENS = ["plane4x5", "room40x36"]
+
+
+def load(name):
+    return dict(np.load(os.path.join(GOLD, name + ".npz")))
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_knn_golden(name):
+    g = load(name)
+    T = oracle.Tree(g["points"])
+    for k in (1, 8, 20, 50):
+        i, d = T.knn(k)
+        assert np.array_equal(i, g[f"knn{k}_idx"])
+        assert np.array_equal(d, g[f"knn{k}_d2"])
+        bi, bd = oracle.knn_brute(g["points"], k)
+        assert np.array_equal(bi, i) and np.array_equal(bd, d)
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+@pytest.mark.parametrize("r,cap", [(0.3, 20), (0.12, 8)])
+def test_radius_golden(name, r, cap):
+    g = load(name)
+    tag = f"r{int(r * 100):03d}_c{cap}"
+    T = oracle.Tree(g["points"])
+    res = T.radius(r, cap=cap, strict_lt=True)
+    assert np.array_equal(res["idx"], g[f"rad_{tag}_idx"])
+    assert np.array_equal(res["d2"], g[f"rad_{tag}_d2"])
+    assert np.array_equal(res["count"], g[f"rad_{tag}_count"])
+    assert np.array_equal(T.radius(r, strict_lt=True, lists=False)["total"], g[f"rad_{tag}_total"])
+    assert np.array_equal(T.radius(r, strict_lt=False, lists=False)["total"], g[f"rad_{tag}_total_incl"])
+
+
+def check_eig(eig, truth, tol=1e-4):
+    scale = np.maximum(truth[:, :1], 1e-30)
+    assert (np.abs(eig - truth) / scale).max() <= tol
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_pca_golden(name):
+    g = load(name)
+    pts = g["points"]
+    n = pts.shape[0]
+    for cn in (0, 1, 2):
+        res = oracle.pca_lists(pts, g["knn20_idx"], count=np.minimum(np.full(n, 20, np.int32), n), cov_norm=cn)
+        check_eig(res["eig64"], g[f"pca20_cov{cn}_eig"], 1e-9)
+        check_eig(res["eig32"], g[f"pca20_cov{cn}_eig"], 1e-4)
+        ok = res["gap64"] > 1e-3
+        cos = np.abs((res["nrm64"][:, :3] * g[f"pca20_cov{cn}_nrm"][:, :3]).sum(1))
+        assert (1 - cos[ok]).max() <= 1e-9
+        assert np.allclose(res["nrm64"][ok, 3], g[f"pca20_cov{cn}_nrm"][ok, 3], rtol=0, atol=1e-9)
+    for tag in ("r030_c20", "r012_c8"):
+        res = oracle.pca_lists(pts, g[f"rad_{tag}_idx"], count=g[f"rad_{tag}_count"], cov_norm=1)
+        check_eig(res["eig64"], g[f"pcarad_{tag}_eig"], 1e-9)
+        marker = g[f"rad_{tag}_count"] < 3
+        assert np.array_equal(res["eig32"][marker], np.tile(np.array([[0, 0, 1]], np.float32), (int(marker.sum()), 1)))
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_sor_golden(name):
+    g = load(name)
+    T = oracle.Tree(g["points"])
+    for k, a in ((8, 1.0), (30, 0.5)):
+        mask, md, mu, sg = T.sor(k, a)
+        assert np.array_equal(md, g[f"sor{k}_mean_d"])
+        assert np.array_equal(mask, g[f"sor{k}_mask"])
+        assert (mu, sg) == tuple(g[f"sor{k}_mu_sigma"])
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_grid_normals_golden(name):
+    g = load(name)
+    w, h = int(g["scan_w"]), int(g["scan_h"])
+    s2, still2 = oracle.grid_normals(g["points"], g["cloud_to_grid"], w, h, fallback=False)
+    assert np.array_equal(s2, g["gridn_stage2"], equal_nan=True)
+    assert still2 == len(g["gridn_missing"])
+    s3, still3 = oracle.grid_normals(g["points"], g["cloud_to_grid"], w, h, fallback=True)
+    assert np.array_equal(s3, g["gridn_final"], equal_nan=True)
+    assert still3 == int(g["gridn_still"])
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_features_golden(name):
+    g = load(name)
+    e = g["pca20_cov1_eig"].astype(np.float32)
+    for fs in (0, 1):
+        f = oracle.features(e, fs)
+        assert np.allclose(f, g[f"feat_set{fs}"], rtol=2e-6, atol=1e-7, equal_nan=True)
+        assert np.array_equal(f[:, :4], g[f"feat_set{fs}"][:, :4], equal_nan=True)     # pure +,-,/ : bit-exact
+
+
+@pytest.mark.parametrize("name", list(clouds_small().keys()))
+def test_tree_vs_numpy_brute(name):
+    pts = clouds_small()[name]
+    n = pts.shape[0]
+    T = oracle.Tree(pts)
+    for k in (1, 20, 64):
+        i, d = T.knn(k)
+        if n <= 5000:
+            kk = min(k, n)
+            ni, nd = oracle.knn_numpy(pts, kk)
+            assert np.array_equal(i[:, :kk], ni) and np.array_equal(d[:, :kk], nd)
+            assert (i[:, kk:] == -1).all() and np.isinf(d[:, kk:]).all()
+        assert (i[:, 0] >= 0).all() and (d[:, 0] == 0).all()          # a point is its own (or a duplicate's) nearest
+
+
+def test_independent_exact_searches_agree():
+    """scipy cKDTree (fp64) and OpenCV's FLANN fork (the closest relative of the reference's search that is
+    importable here) return the same neighbour SETS as the oracle on tie-free data."""
+    rng = np.random.default_rng(3)
+    pts = np.zeros((20000, 8), np.float32)
+    pts[:, :3] = rng.normal(size=(20000, 3))
+    i, d = oracle.Tree(pts).knn(20)
+    from scipy.spatial import cKDTree
+    dd, ii = cKDTree(pts[:, :3].astype(np.float64)).query(pts[:, :3].astype(np.float64), k=20)
+    assert np.array_equal(np.sort(ii, 1), np.sort(i, 1))
+    try:
+        import cv2
+    except Exception:
+        pytest.skip("cv2 not importable")
+    fl = cv2.flann_Index(pts[:, :3].copy(), {"algorithm": 4, "leaf_max_size": 15})
+    fi, fd = fl.knnSearch(pts[:2000, :3].copy(), 20, params={"checks": -1, "eps": 0.0, "sorted": True})
+    assert np.array_equal(np.sort(fi, 1), np.sort(i[:2000], 1))
+    assert (fi[:, 0] == np.arange(2000)).all()                          # self first, squared distances
+    assert np.allclose(fd, d[:2000], rtol=1e-5, atol=1e-7)
+
+
+def test_radius_outliers_prefilter_is_a_subset():
+    pts = clouds_small()["clusters_outliers"]
+    T = oracle.Tree(pts)
+    a = T.radius_outliers(0.5, 10, prefilter=False)
+    b = T.radius_outliers(0.5, 10, prefilter=True)
+    total = T.radius(0.5, strict_lt=False, lists=False)["total"]
+    assert np.array_equal(a, (total < 10).astype(np.uint8))
+    assert ((b == 1) <= (a == 1)).all()
+    assert a[-20:].sum() >= 15                                           # the isolated points are found
+
+
+def test_eig3_f32_tracks_f64():
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        p = rng.normal(size=(20, 3)) * np.array([1.0, 0.3, rng.uniform(1e-4, 1)])
+        c = np.cov(p.T)
+        a6 = np.array([c[0, 0], c[0, 1], c[0, 2], c[1, 1], c[1, 2], c[2, 2]])
+        w64, _ = oracle.eig3_f64(a6)
+        w32 = oracle.eig3_f32(a6.astype(np.float32))
+        ref = np.linalg.eigvalsh(c)[::-1]
+        assert np.allclose(w64, ref, rtol=1e-10, atol=1e-14)
+        assert np.abs(w32 - ref).max() <= 1e-5 * ref[0]
