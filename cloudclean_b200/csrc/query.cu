@@ -77,13 +77,30 @@ struct TopK {
         }
         key[0] = lt_i ? ck : key[0];
     }
-    __device__ __forceinline__ void candidate(const float4 &q, const float4 &c) {
-        float d2 = d2_point(q, c);
-        if (d2 <= bound) {
-            u64 ck = ((u64)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(c.w);
-            if (ck < key[K - 1]) {
-                insert(ck);
-                bound = fminf(rb, __uint_as_float((unsigned)(key[K - 1] >> 32)));
+    // Score the 32 staged candidates of one leaf.  Phase 1 is branch-free: every lane marks the candidates
+    // inside its bound in a 32-bit mask.  Phase 2 drains the masks together, so the (expensive, ~6 K
+    // instructions) ordered insert runs max-over-lanes(popcount) times per leaf instead of once per candidate
+    // that ANY lane accepts — the lanes' accepted candidates are different ones, and scoring them one candidate
+    // at a time left the insert running with a handful of active lanes (ncu r01: 17.5 of 32).
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        unsigned m = 0;
+        const float b = bound;
+#pragma unroll
+        for (int j = 0; j < kLeaf; ++j) {
+            const float d2 = d2_point(q, leaf[j]);
+            m |= (d2 <= b) ? (1u << j) : 0u;
+        }
+        while (__any_sync(kFull, m != 0)) {
+            if (m != 0) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const float4 c = leaf[j];
+                const float d2 = d2_point(q, c);                 // same expression as phase 1: same bits
+                const u64 ck = ((u64)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(c.w);
+                if (ck < key[K - 1]) {                           // d2 <= rb already holds (phase 1, b <= rb)
+                    insert(ck);
+                    bound = fminf(rb, __uint_as_float((unsigned)(key[K - 1] >> 32)));
+                }
             }
         }
     }
@@ -115,6 +132,10 @@ struct Stream {
             if (cap > 0 && count >= cap) bound = -1.f;   // enough neighbours seen: this lane is finished
         }
     }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 8
+        for (int j = 0; j < kLeaf; ++j) candidate(q, leaf[j]);
+    }
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -122,86 +143,111 @@ struct Stream {
 // ---------------------------------------------------------------------------------------------------
 struct WarpScratch {
     float4 leaf[kLeaf];
-    int base[kMaxLevels];
-    unsigned mask[kMaxLevels];
 };
 
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+
+// Bottom-up, nearest-first walk of the box hierarchy for the 32 queries of one leaf ("tile").
+//   * the tile's own leaf is scanned first (it alone fills a k <= 32 list and gives a finite bound);
+//   * then, level by level, the siblings of the tile's ancestor are searched top-down.  The (uniform) stack of
+//     {first child, surviving-children mask} lives in registers, entry d in lane d, read back with a shuffle;
+//   * children are taken in order of the distance from the tile's centre to their box, so that the bound
+//     tightens before the far ones are looked at; before every pop the survivors are re-tested against the
+//     warp's largest current bound (box-box distance, one child per lane) and the chosen one against every
+//     lane's own bound (point-box distance).
 template <class V>
 __device__ __forceinline__ int traverse_tile(const TreeView &T, int tile, const float4 &q, V &v, WarpScratch &ws) {
     const int lane = threadIdx.x & 31;
     const float4 tlo = T.lo[0][tile], thi = T.hi[0][tile];
-    int scanned = 0;
-    int node = tile;       // ancestor of the tile at level L
-    int L = 0;
-    int sp = 1;            // stack depth; entry d holds children at level (top_lv - d), exhausted entries pop lazily
-    int top_lv = 0;
-    if (lane == 0) { ws.base[0] = tile & ~31; ws.mask[0] = 1u << (tile & 31); }
+    const float4 tc = make_float4(0.5f * (tlo.x + thi.x), 0.5f * (tlo.y + thi.y), 0.5f * (tlo.z + thi.z), 0.f);
+    int scanned = 1;
+    ws.leaf[lane] = q;                       // the own leaf is exactly the 32 query points of the warp
     __syncwarp();
-    while (true) {
-        if (sp == 0) {
-            // all subtrees below the level-L ancestor are done: test its siblings
-            ++L;
-            if (L >= T.nlevels) break;
-            const int parent = node >> 5;
-            const int first = parent << 5;
-            const int c = first + lane;
-            const bool in = c < T.count[L - 1];
-            const float rmax = warp_max(v.bound);
-            if (rmax < 0.f) break;                           // every lane is finished
-            bool pass = false;
-            if (in) {
-                float4 clo = T.lo[L - 1][c], chi = T.hi[L - 1][c];
-                pass = d2_box_box(tlo, thi, clo, chi) <= rmax;
+    v.scan_leaf(q, ws.leaf);
+
+    int node = tile;                         // ancestor (level L-1) whose subtree is finished
+    for (int L = 1; L < T.nlevels; ++L) {
+        const int parent = node >> 5;
+        float rmax = warp_max(v.bound);
+        if (rmax < 0.f) break;               // every lane is finished
+        int st_base = 0;                     // lane d holds stack entry d: children at level (L-1-d)
+        unsigned st_mask = 0;
+        int sp = 0;
+        bool mine = false;                   // registers describing the TOP entry: this lane's child survives,
+        float dbb = 0.f, dc = 0.f;           // its box-box distance to the tile and its distance to the tile centre
+        {
+            const int c = (parent << 5) + lane;
+            if (c < T.count[L - 1] && c != node) {
+                const float4 clo = T.lo[L - 1][c], chi = T.hi[L - 1][c];
+                dbb = d2_box_box(tlo, thi, clo, chi);
+                dc = d2_point_box(tc, clo, chi);
+                mine = dbb <= rmax;
             }
-            unsigned m = __ballot_sync(kFull, pass) & ~(1u << (node & 31));
-            node = parent;
-            top_lv = L - 1;
-            if (!m) continue;
-            if (lane == 0) { ws.base[0] = first; ws.mask[0] = m; }
-            __syncwarp();
-            sp = 1;
+            const unsigned m = __ballot_sync(kFull, mine);
+            if (m) { if (lane == 0) { st_base = parent << 5; st_mask = m; } sp = 1; }
         }
-        // take one child off the top entry
-        const int lv = top_lv - (sp - 1);
-        const int base = ws.base[sp - 1];
-        unsigned m = ws.mask[sp - 1];
-        __syncwarp();
-        if (m == 0) { --sp; continue; }
-        const int cbit = __ffs(m) - 1;
-        m &= m - 1;
-        if (lane == 0) ws.mask[sp - 1] = m;
-        const int child = base + cbit;
-        // exact per-query test of the child's box against each lane's current bound
-        const float4 clo = T.lo[lv][child], chi = T.hi[lv][child];
-        const bool want = d2_point_box(q, clo, chi) <= v.bound;
-        if (!__any_sync(kFull, want)) { __syncwarp(); continue; }
-        if (lv == 0) {
-            // stage the leaf (contiguous 512 B) and let every lane score all 32 candidates
-            const float4 mine = T.pts[(size_t)child * kLeaf + lane];
-            __syncwarp();
-            ws.leaf[lane] = mine;
-            __syncwarp();
-#pragma unroll 8
-            for (int j = 0; j < kLeaf; ++j) v.candidate(q, ws.leaf[j]);
-            ++scanned;
-        } else {
-            // expand: one lane per grandchild against the tile box
-            const int first = child << 5;
-            const int c = first + lane;
-            const bool in = c < T.count[lv - 1];
-            const float rmax = warp_max(v.bound);
-            bool pass = false;
-            if (in) {
-                float4 glo = T.lo[lv - 1][c], ghi = T.hi[lv - 1][c];
-                pass = d2_box_box(tlo, thi, glo, ghi) <= rmax;
+        bool top_valid = true;
+        while (sp > 0) {
+            const int lv = L - sp;
+            const int base = __shfl_sync(kFull, st_base, sp - 1);
+            unsigned m = __shfl_sync(kFull, st_mask, sp - 1);
+            if (!top_valid) {                // back on an outer entry: reload this lane's child of it
+                mine = (m >> lane) & 1u;
+                if (mine) {
+                    const float4 clo = T.lo[lv][base + lane], chi = T.hi[lv][base + lane];
+                    dbb = d2_box_box(tlo, thi, clo, chi);
+                    dc = d2_point_box(tc, clo, chi);
+                }
+                top_valid = true;
             }
-            const unsigned m2 = __ballot_sync(kFull, pass);
-            if (m2) {
-                if (lane == 0) { ws.base[sp] = first; ws.mask[sp] = m2; }
-                ++sp;
+            rmax = warp_max(v.bound);
+            mine = mine && ((m >> lane) & 1u) && dbb <= rmax;
+            m = __ballot_sync(kFull, mine);
+            if (m == 0) { --sp; top_valid = false; continue; }
+            const float best = warp_min(mine ? dc : INFINITY);
+            const unsigned who = __ballot_sync(kFull, mine && dc == best);
+            const int cbit = who ? __ffs(who) - 1 : __ffs(m) - 1;
+            m &= ~(1u << cbit);
+            if (lane == cbit) mine = false;
+            if (lane == sp - 1) st_mask = m;
+            const int child = base + cbit;
+            // exact per-query test of the chosen child against each lane's own bound
+            const float4 clo = T.lo[lv][child], chi = T.hi[lv][child];
+            const bool want = d2_point_box(q, clo, chi) <= v.bound;
+            if (!__any_sync(kFull, want)) continue;
+            if (lv == 0) {
+                // stage the leaf (a contiguous 512-byte run) and let every lane score its 32 candidates
+                const float4 p = T.pts[(size_t)child * kLeaf + lane];
+                __syncwarp();
+                ws.leaf[lane] = p;
+                __syncwarp();
+                v.scan_leaf(q, ws.leaf);
+                ++scanned;
+            } else {
+                // expand: one lane per grandchild against the tile box
+                const int first = child << 5;
+                const int c = first + lane;
+                bool pass = false;
+                float ndbb = 0.f, ndc = 0.f;
+                if (c < T.count[lv - 1]) {
+                    const float4 glo = T.lo[lv - 1][c], ghi = T.hi[lv - 1][c];
+                    ndbb = d2_box_box(tlo, thi, glo, ghi);
+                    ndc = d2_point_box(tc, glo, ghi);
+                    pass = ndbb <= rmax;
+                }
+                const unsigned m2 = __ballot_sync(kFull, pass);
+                if (m2) {
+                    if (lane == sp) { st_base = first; st_mask = m2; }
+                    ++sp;
+                    mine = pass; dbb = ndbb; dc = ndc;      // the registers now describe the new top entry
+                } 
             }
         }
-        __syncwarp();
+        node = parent;
     }
     return scanned;
 }
@@ -283,11 +329,11 @@ __device__ __forceinline__ void features7(float l0, float l1, float l2, int form
     o[3] = __fdiv_rn(__fsub_rn(l0, l1), l0);                 // :463
     if (formula_set == 0) {
         o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l0));      // :467 (sic)
-        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l0));   // :471 (sic)
+        o[5] = -__fadd_rn(__fadd_rn(__fmul_rn(l0, logf(l0)), __fmul_rn(l1, logf(l1))), __fmul_rn(l2, logf(l0)));   // :471 (sic)
         o[6] = __fdiv_rn(l0, __fadd_rn(__fadd_rn(l0, l1), l2));     // :475 (sic)
     } else {
         o[4] = cbrtf(__fmul_rn(__fmul_rn(l0, l1), l2));
-        o[5] = -(l0 * logf(l0) + l1 * logf(l1) + l2 * logf(l2));
+        o[5] = -__fadd_rn(__fadd_rn(__fmul_rn(l0, logf(l0)), __fmul_rn(l1, logf(l1))), __fmul_rn(l2, logf(l2)));
         o[6] = __fdiv_rn(l2, __fadd_rn(__fadd_rn(l0, l1), l2));
     }
 }
