@@ -86,6 +86,7 @@ struct ccg_ctx {
     ccg::DevBuf scratch;     // bbox / flags / counters
     ccg::DevBuf out[4];      // staged outputs for host destinations
     ccg::DevBuf tmp[4];      // per-call temporaries
+    ccg::DevBuf defer;       // [count | query list | output rows] of queries deferred to the exact point kernel
     ccg::HostBuf hpin[2];    // pinned bounce buffers
     float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};
 

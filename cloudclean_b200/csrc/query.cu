@@ -139,6 +139,90 @@ struct Stream {
 };
 
 // ---------------------------------------------------------------------------------------------------
+// two-pass selection (PCA / SOR): pass 1 keeps only the K smallest d2 VALUES, pass 2 collects
+// ---------------------------------------------------------------------------------------------------
+// The 64-bit (d2, index) list above costs ~6 ALU-pipe instructions per slot and insert (no 64-bit min/max in
+// hardware; ncu r01: ISETP+SEL = 53 % of all instructions).  Covariance and SOR do not need the ORDER of the
+// neighbours, only the SET, and the set is fixed by the k-th smallest d2 value T alone unless more candidates
+// tie at T than the list has room for.  So pass 1 keeps a sorted list of plain fp32 d2 values, where an insert
+// is new[i] = max(old[i-1], min(old[i], c)) — two independent FMNMX per slot, no dependency chain — and pass 2
+// walks the hierarchy again with the bound fixed at T and accumulates count and moments of everything with
+// d2 <= T.  count == k proves the set is exactly the (d2, index)-ordered kNN set; count > k means ties overflow
+// at T and the query is handed to the exact warp-per-query kernel (k_point_query).
+template <int K>
+struct ValK {
+    float key[K];    // ascending d2 values; front slots pinned to -1 when k < K
+    float bound;     // min(rb, key[K-1]); -1 for inactive lanes
+    float rb;
+
+    __device__ __forceinline__ void init(int k, float rb_, bool active) {
+#pragma unroll
+        for (int i = 0; i < K; ++i) key[i] = (i < K - k) ? -1.f : INFINITY;
+        rb = rb_;
+        bound = active ? rb_ : -1.f;
+    }
+    __device__ __forceinline__ void insert(float c) {
+        // descending i so that old[i-1] is still the old value when slot i is rewritten
+#pragma unroll
+        for (int i = K - 1; i > 0; --i) key[i] = fmaxf(key[i - 1], fminf(key[i], c));
+        key[0] = fminf(key[0], c);
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        unsigned m = 0;
+        const float b = bound;
+#pragma unroll
+        for (int j = 0; j < kLeaf; ++j) {
+            const float d2 = d2_point(q, leaf[j]);
+            m |= (d2 <= b) ? (1u << j) : 0u;
+        }
+        while (__any_sync(kFull, m != 0)) {
+            if (m != 0) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const float d2 = d2_point(q, leaf[j]);
+                if (d2 < key[K - 1]) {               // equal values change nothing in a value list
+                    insert(d2);
+                    bound = fminf(rb, key[K - 1]);
+                }
+            }
+        }
+    }
+};
+
+// pass 2: everything with d2 <= bound (fixed), count + moments of (p - q)
+struct Collect {
+    float bound;
+    int count;
+    float m[9];
+    __device__ __forceinline__ void init(float t, bool active) {
+        bound = active ? t : -1.f;
+        count = 0;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) m[i] = 0.f;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        unsigned msk = 0;
+        const float b = bound;
+#pragma unroll
+        for (int j = 0; j < kLeaf; ++j) {
+            const float d2 = d2_point(q, leaf[j]);
+            msk |= (d2 <= b) ? (1u << j) : 0u;
+        }
+        count += __popc(msk);
+        while (__any_sync(kFull, msk != 0)) {
+            if (msk != 0) {
+                const int j = __ffs(msk) - 1;
+                msk &= msk - 1;
+                const float4 c = leaf[j];
+                const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
+                m[0] += x; m[1] += y; m[2] += z;
+                m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+            }
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
 // tile traversal
 // ---------------------------------------------------------------------------------------------------
 struct WarpScratch {
@@ -379,6 +463,20 @@ __device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, con
 // ---------------------------------------------------------------------------------------------------
 // tile kernel with a top-k list
 // ---------------------------------------------------------------------------------------------------
+struct PointParams {
+    const int32_t *queries;      // original indices; NULL = 0..nq-1
+    int nq;
+    int mode, k;
+    float rb;
+    int list_rows;               // 1: output row = position in `queries`, 0: row = original index
+    int32_t *idx; float *d2; int32_t *count;
+    PcaOut pca;
+    int mean_k; float *mean_d;
+    const int *nq_dev;           // non-NULL: the list length lives on the device (deferred queries of k_tile_sel)
+    const long long *rows;       // non-NULL: explicit output row per list entry
+};
+__global__ void k_point_query(const __grid_constant__ TreeView T, const __grid_constant__ PointParams P);
+
 struct TileParams {
     int mode, k;
     float rb;
@@ -389,6 +487,7 @@ struct TileParams {
     PcaOut pca;
     int mean_k; float *mean_d;
     unsigned long long *stat_scanned;
+    int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
 };
 
 template <int K>
@@ -461,6 +560,56 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 }
 
 // ---------------------------------------------------------------------------------------------------
+// tile kernel, two-pass selection: MODE_PCA (kNN or capped radius -> covariance -> eigen) and MODE_SOR
+// ---------------------------------------------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(128) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = P.tile_begin + blockIdx.x * 4 + warp;
+    if (tile >= P.tile_end) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    const int qidx = __float_as_int(q.w);
+    const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)qidx;
+    const int k = P.k;
+
+    float t;                                        // per-lane selection threshold
+    int scanned;
+    {
+        ValK<K> v;
+        v.init(k, P.rb, active);
+        scanned = traverse_tile(T, tile, q, v, s_ws[warp]);
+        if (P.mode == MODE_SOR) {
+            if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+            if (!active) return;
+            double s = 0.0;
+#pragma unroll
+            for (int i = 0; i < K; ++i)
+                if (i > K - k && v.key[i] != INFINITY) s += (double)__fsqrt_rn(v.key[i]);
+            P.mean_d[row] = (float)(s / (double)P.mean_k);
+            return;
+        }
+        t = fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX);   // finite: the +inf pad points of the last leaf never qualify
+    }
+    Collect c;
+    c.init(t, active);
+    __syncwarp();
+    scanned += traverse_tile(T, tile, q, c, s_ws[warp]);
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+    if (!active) return;
+    if (c.count > k) {                              // ties at the k-th distance overflow the list: exact kernel decides
+        const int slot = atomicAdd(P.defer_count, 1);
+        P.defer_list[slot] = qidx;
+        P.defer_row[slot] = (long long)row;
+        return;
+    }
+    pca_finish(P.pca, q, c.m, c.count, row);
+    if (P.count) P.count[row] = c.count;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // tile kernel without a list (radius count / uncapped radius PCA)
 // ---------------------------------------------------------------------------------------------------
 struct StreamParams {
@@ -500,6 +649,11 @@ static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cuda
     k_tile_topk<K><<<blocks, 128, 0, st>>>(T, P);
 }
 
+template <int K>
+static void launch_sel(const TreeView &T, const TileParams &P, int blocks, cudaStream_t st) {
+    k_tile_sel<K><<<blocks, 128, 0, st>>>(T, P);
+}
+
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     if (ctx->n == 0) return CCG_OK;
     if (a.k < 1 || a.k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", a.k, CCG_MAX_K);
@@ -526,20 +680,51 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     TreeView T = ctx->view();
     cudaStream_t st = ctx->stream;
     const int k = a.k;
-    if (k <= 8) launch_topk<8>(T, P, blocks, st);
-    else if (k <= 16) launch_topk<16>(T, P, blocks, st);
-    else if (k <= 20) launch_topk<20>(T, P, blocks, st);
-    else if (k <= 24) launch_topk<24>(T, P, blocks, st);
-    else if (k <= 32) launch_topk<32>(T, P, blocks, st);
-    else if (k <= 48) launch_topk<48>(T, P, blocks, st);
-    else launch_topk<64>(T, P, blocks, st);
+    if (a.mode == MODE_KNN) {
+        if (k <= 8) launch_topk<8>(T, P, blocks, st);
+        else if (k <= 16) launch_topk<16>(T, P, blocks, st);
+        else if (k <= 20) launch_topk<20>(T, P, blocks, st);
+        else if (k <= 24) launch_topk<24>(T, P, blocks, st);
+        else if (k <= 32) launch_topk<32>(T, P, blocks, st);
+        else if (k <= 48) launch_topk<48>(T, P, blocks, st);
+        else launch_topk<64>(T, P, blocks, st);
+    } else {
+        // two-pass selection; queries whose k-th distance is tied beyond the list go to the exact point kernel
+        const size_t rows = (size_t)ntiles * kLeaf;
+        const size_t off_list = 256, off_rows = off_list + ((rows * 4 + 255) & ~(size_t)255);
+        if (a.mode == MODE_PCA) {
+            CCG_CUDA(ctx, ctx->defer.reserve(off_rows + rows * 8));
+            CCG_CUDA(ctx, cudaMemsetAsync(ctx->defer.p, 0, 4, st));
+            P.defer_count = ctx->defer.as<int>();
+            P.defer_list = (int32_t *)((char *)ctx->defer.p + off_list);
+            P.defer_row = (long long *)((char *)ctx->defer.p + off_rows);
+        }
+        if (k <= 8) launch_sel<8>(T, P, blocks, st);
+        else if (k <= 16) launch_sel<16>(T, P, blocks, st);
+        else if (k <= 20) launch_sel<20>(T, P, blocks, st);
+        else if (k <= 24) launch_sel<24>(T, P, blocks, st);
+        else if (k <= 32) launch_sel<32>(T, P, blocks, st);
+        else if (k <= 48) launch_sel<48>(T, P, blocks, st);
+        else launch_sel<64>(T, P, blocks, st);
+        if (a.mode == MODE_PCA) {
+            PointParams Q{};
+            Q.queries = P.defer_list; Q.nq = 0; Q.nq_dev = P.defer_count; Q.rows = P.defer_row;
+            Q.mode = MODE_PCA; Q.k = k; Q.rb = a.rb; Q.list_rows = 0;
+            Q.count = a.count; Q.pca = P.pca;
+            k_point_query<<<ctx->sm_count * 4, 128, 0, st>>>(T, Q);
+            ctx->stats.launches++;
+        }
+    }
     ctx->stats.launches++;
     CCG_CUDA(ctx, cudaGetLastError());
     if (ctx->collect_stats) {
         unsigned long long s = 0;
         CCG_CUDA(ctx, cudaMemcpyAsync(&s, P.stat_scanned, 8, cudaMemcpyDeviceToHost, st));
+        int nd = 0;
+        if (P.defer_count) CCG_CUDA(ctx, cudaMemcpyAsync(&nd, P.defer_count, 4, cudaMemcpyDeviceToHost, st));
         CCG_CUDA(ctx, cudaStreamSynchronize(st));
         ctx->stats.leaves_scanned = (int64_t)s;
+        ctx->stats.deferred_queries = nd;
     }
     return CCG_OK;
 }
@@ -644,16 +829,6 @@ int launch_unpermute(ccg_ctx *ctx, const void *in, size_t row_bytes, void *out) 
 // The 32 lanes score the 32 candidates of a leaf at once; the bounded top-k (k <= 64) lives one or two
 // keys per lane and is updated with warp shuffles.
 // ---------------------------------------------------------------------------------------------------
-struct PointParams {
-    const int32_t *queries;      // original indices; NULL = 0..nq-1
-    int nq;
-    int mode, k;
-    float rb;
-    int list_rows;               // 1: output row = position in `queries`, 0: row = original index
-    int32_t *idx; float *d2; int32_t *count;
-    PcaOut pca;
-    int mean_k; float *mean_d;
-};
 
 struct WarpStack {
     int base[kMaxLevels];
@@ -672,9 +847,9 @@ __device__ __forceinline__ u64 shfl_up64(u64 v) {
 __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ TreeView T, const __grid_constant__ PointParams P) {
     __shared__ WarpStack s_st[4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qslot = blockIdx.x * 4 + warp;
-    if (qslot >= P.nq) return;
+    const int nq = P.nq_dev ? *P.nq_dev : P.nq;
     WarpStack &ws = s_st[warp];
+    for (int qslot = blockIdx.x * 4 + warp; qslot < nq; qslot += gridDim.x * 4) {
     const int qi = P.queries ? P.queries[qslot] : qslot;
     const float4 q = T.orig[qi];
     const int k = P.k;
@@ -755,7 +930,7 @@ __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ Tre
         __syncwarp();
     }
 
-    const size_t row = P.list_rows ? (size_t)qslot : (size_t)qi;
+    const size_t row = P.rows ? (size_t)P.rows[qslot] : (P.list_rows ? (size_t)qslot : (size_t)qi);
     if (P.mode == MODE_KNN) {
         int cnt = 0;
 #pragma unroll
@@ -805,6 +980,8 @@ __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ Tre
         }
         if (lane == 0) P.mean_d[row] = (float)(s / (double)P.mean_k);
     }
+    __syncwarp();
+    }   // query loop
 }
 
 int launch_point_query(ccg_ctx *ctx, const PointArgs &a) {
