@@ -145,6 +145,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     for (int i = 0; i < 8; ++i) if (cudaEventCreate(&ctx->ev[i]) != cudaSuccess) { delete ctx; return CCG_ERR_CUDA; }
     const char *cs = getenv("CCG_COLLECT_STATS");
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
+    const char *sp = getenv("CCG_SPLIT_SPARSE");
+    ctx->split_sparse = (sp && sp[0] == '0') ? 0 : 1;
     *out = ctx;
     return CCG_OK;
 }

@@ -10,6 +10,7 @@
 // All stages are HBM-streaming kernels; algorithmic bytes per point are listed in DESIGN.md §4.
 #include "common.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_partition.cuh>
 #include <cfloat>
 
 namespace ccg {
@@ -98,6 +99,49 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
     unsigned qz = (unsigned)fminf(fmaxf((p.z - lo.z) * inv_cell, 0.f), 2097151.f);
     keys[i] = spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
     vals[i] = (unsigned)i;
+}
+
+
+// Isolated points (laser "mixed pixels", airborne returns: the very points the outlier filters exist for) sit between
+// surface points in the Morton order and stretch the box of whatever 32-point leaf they fall into from centimetres to
+// metres; a few thousand such boxes make every wide search intersect all of them (r01: 35 k instructions per deferred
+// query).  They are therefore moved to the END of the order, where they form leaves of their own — large boxes, but few
+// and hardly overlapping — and the remaining leaves stay tight.  Any classification is correct (the order is only a
+// permutation); this one calls a point isolated when the distance to its nearer neighbour along the curve is more than
+// kIsoFactor times the median of that distance over its aligned 32-point window.  One warp per window.
+constexpr float kIsoFactor = 8.f;
+__global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ orig, const unsigned *__restrict__ order, int n,
+                                                    unsigned char *__restrict__ dense) {
+    const int win = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int i = win * 32 + lane;
+    if (win * 32 >= n) return;
+    const bool valid = i < n;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) p = orig[order[i]];
+    float px = __shfl_up_sync(kFull, p.x, 1), py = __shfl_up_sync(kFull, p.y, 1), pz = __shfl_up_sync(kFull, p.z, 1);
+    float nx = __shfl_down_sync(kFull, p.x, 1), ny = __shfl_down_sync(kFull, p.y, 1), nz = __shfl_down_sync(kFull, p.z, 1);
+    bool has_prev = valid && i > 0, has_next = valid && i + 1 < n;
+    if (lane == 0 && has_prev) { const float4 t = orig[order[i - 1]]; px = t.x; py = t.y; pz = t.z; }
+    if (lane == 31 && has_next) { const float4 t = orig[order[i + 1]]; nx = t.x; ny = t.y; nz = t.z; }
+    float gp = INFINITY, gn = INFINITY;
+    if (has_prev) { const float x = p.x - px, y = p.y - py, z = p.z - pz; gp = x * x + y * y + z * z; }
+    if (has_next) { const float x = p.x - nx, y = p.y - ny, z = p.z - nz; gn = x * x + y * y + z * z; }
+    const float iso = valid ? fminf(gp, gn) : INFINITY;      // squared distance to the nearer curve neighbour
+    // bitonic sort of the 32 values across the warp -> median of the valid ones
+    float v = iso;
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const float o = __shfl_xor_sync(kFull, v, j);
+            const bool up = ((lane & k) == 0) == ((lane & j) == 0);
+            v = up ? fminf(v, o) : fmaxf(v, o);
+        }
+    }
+    const int nvalid = min(32, n - win * 32);
+    const float med = __shfl_sync(kFull, v, nvalid >> 1);
+    if (valid) dense[i] = (iso > kIsoFactor * kIsoFactor * med) ? 0 : 1;
 }
 
 // One warp per leaf: gather the 32 points of the leaf in Morton order, tag them with their original index,
@@ -260,6 +304,21 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
         CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, (int)n, 0, 63, st));
         ctx->order_sel = dv.selector;
         ctx->stats.launches_build += 9;   // onesweep: 1 histogram + 8 digit passes
+    }
+    // ---- isolated points to the end of the order ----------------------------------------------------------
+    if (ctx->split_sparse && n > 64) {
+        const unsigned *ord = ctx->vals[ctx->order_sel].as<unsigned>();
+        unsigned *ord2 = ctx->vals[ctx->order_sel ^ 1].as<unsigned>();
+        unsigned char *flags = ctx->keys[0].as<unsigned char>();          // the keys are not needed any more
+        int *nsel = (int *)((char *)ctx->scratch.p + 2048);
+        const int nwin = (int)((n + 31) / 32);
+        k_flag_dense<<<(nwin + 7) / 8, 256, 0, st>>>(ctx->orig.as<float4>(), ord, (int)n, flags);
+        size_t tmp_bytes = 0;
+        CCG_CUDA(ctx, cub::DevicePartition::Flagged(nullptr, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
+        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+        CCG_CUDA(ctx, cub::DevicePartition::Flagged(ctx->sort_tmp.p, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
+        ctx->order_sel ^= 1;
+        ctx->stats.launches_build += 3;
     }
     // ---- leaves + box levels ----------------------------------------------------------------------------
     {

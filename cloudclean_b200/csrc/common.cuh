@@ -92,6 +92,7 @@ struct ccg_ctx {
 
     ccg_stats stats = {};
     int collect_stats = 0;
+    int split_sparse = 1;    // move isolated points to the end of the order (CCG_SPLIT_SPARSE=0 disables)
     char err[512] = "";
 
     ccg::TreeView view() const {

@@ -16,6 +16,7 @@
 // current k-th d2, so ties at the k-th distance are always visited.
 #include "common.cuh"
 #include <cfloat>
+#include <stdlib.h>
 
 namespace ccg {
 
@@ -488,6 +489,7 @@ struct TileParams {
     int mean_k; float *mean_d;
     unsigned long long *stat_scanned;
     int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
+    int *slow_count; int32_t *slow_tiles;                          // k_tile_sel: tiles handed to k_tile_sel_stack
 };
 
 template <int K>
@@ -562,51 +564,354 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 // ---------------------------------------------------------------------------------------------------
 // tile kernel, two-pass selection: MODE_PCA (kNN or capped radius -> covariance -> eigen) and MODE_SOR
 // ---------------------------------------------------------------------------------------------------
+// Candidate leaves of a tile, found ONCE and used by both passes.  After the tile's own leaf and its two
+// neighbours in the Morton order have been scanned every lane has a finite bound; a top-down breadth-first walk
+// with one lane per child box then lists every leaf whose box is within the warp's largest bound of the tile
+// box (ballot + popc compaction into shared memory).  Compared with the nearest-first stack walk this costs a
+// few hundred instructions per tile instead of ~100 per visited child, and pass 2 re-uses the list.
+constexpr int kListCap = 128;     // leaves listed per tile (overflow -> stack walk, exact as well)
+constexpr int kQueueCap = 64;     // inner nodes per level
+struct WarpScratch2 {
+    WarpScratch ws;
+    int list[kListCap];
+    int queue[2][kQueueCap];
+    float4 sub[16];
+};
+
+// SUB: the tile box alone is a poor description of a tile that straddles a jump of the Morton curve (two far-apart
+// clusters in one leaf): everything between the clusters is "inside" it.  Such tiles are described by 8 sub-boxes
+// of 4 consecutive lanes each with that group's own largest bound (w.sub[2g], w.sub[2g+1].w = bound).
+template <bool SUB>
+__device__ __forceinline__ int collect_leaves(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, float rmax,
+                                              WarpScratch2 &w) {
+    const int lane = threadIdx.x & 31;
+    const int top = T.nlevels - 1;
+    if (top == 0) return 0;
+    if (lane == 0) w.queue[0][0] = 0;
+    __syncwarp();
+    int cur = 0, ncur = 1, nlist = 0;
+    for (int lv = top; lv >= 1; --lv) {
+        int nnext = 0;
+        for (int i = 0; i < ncur; ++i) {
+            const int node = w.queue[cur][i];
+            const int c = (node << 5) + lane;
+            bool pass = false;
+            if (c < T.count[lv - 1]) {
+                const float4 clo = T.lo[lv - 1][c], chi = T.hi[lv - 1][c];
+                pass = d2_box_box(tlo, thi, clo, chi) <= rmax;
+                if (lv == 1) pass = pass && (c < tile - 1 || c > tile + 1);     // already scanned
+                if (SUB && pass) {
+                    pass = false;
+#pragma unroll 1
+                    for (int g = 0; g < 8; ++g) {
+                        const float4 slo = w.sub[2 * g], shi = w.sub[2 * g + 1];
+                        pass = pass || d2_box_box(slo, shi, clo, chi) <= shi.w;
+                    }
+                }
+            }
+            const unsigned m = __ballot_sync(kFull, pass);
+            const int before = __popc(m & ((1u << lane) - 1u));
+            if (lv == 1) {
+                if (pass && nlist + before < kListCap) w.list[nlist + before] = c;
+                nlist += __popc(m);
+            } else {
+                if (pass && nnext + before < kQueueCap) w.queue[cur ^ 1][nnext + before] = c;
+                nnext += __popc(m);
+            }
+        }
+        if (nnext > kQueueCap || nlist > kListCap) return -1;
+        __syncwarp();
+        cur ^= 1; ncur = nnext;
+    }
+    return nlist;
+}
+
+// boxes and largest bound of each group of 4 consecutive lanes -> w.sub (inactive lanes: bound -1, box from +inf pads)
+__device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, bool active, WarpScratch2 &w) {
+    const int lane = threadIdx.x & 31;
+    float lx = active ? q.x : INFINITY, ly = active ? q.y : INFINITY, lz = active ? q.z : INFINITY;
+    float hx = active ? q.x : -INFINITY, hy = active ? q.y : -INFINITY, hz = active ? q.z : -INFINITY;
+    float b = bound;
+#pragma unroll
+    for (int o = 1; o <= 2; o <<= 1) {
+        lx = fminf(lx, __shfl_xor_sync(kFull, lx, o)); ly = fminf(ly, __shfl_xor_sync(kFull, ly, o));
+        lz = fminf(lz, __shfl_xor_sync(kFull, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(kFull, hx, o));
+        hy = fmaxf(hy, __shfl_xor_sync(kFull, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(kFull, hz, o));
+        b = fmaxf(b, __shfl_xor_sync(kFull, b, o));
+    }
+    if ((lane & 3) == 0) {
+        w.sub[2 * (lane >> 2)] = make_float4(lx, ly, lz, 0.f);
+        w.sub[2 * (lane >> 2) + 1] = make_float4(hx, hy, hz, b);
+    }
+    __syncwarp();
+}
+
+// Pass-1 visitor of k_tile_sel: the value list of ValK plus (LOG) a per-lane LOG in shared memory of every
+// candidate that was inside the lane's bound when it was scored.  The final neighbour set {d2 <= T} is a subset
+// of the log (T <= bound at all times), so pass 2 never rescans leaves: it walks the ~k surviving log entries.
+// A log word holds d2 with its low 13 mantissa bits replaced by (scan slot << 5 | position in leaf); the
+// truncated d2 is a lower bound of the true one, good enough to drop stale entries (compact) without a gather.
+constexpr unsigned kLogIdMask = 0x1fffu;
+constexpr int kSlotCap = 256;     // leaves scanned per tile that the 8-bit slot can name
+template <int K> struct LogCap { static constexpr int value = K <= 32 ? 96 : 128; };
+
+template <int K, bool LOG>
+struct ValLog {
+    float key[K];
+    float bound, rb;
+    int cnt;              // log entries of this lane
+    int slot;             // scan slot of the leaf being scored (warp-uniform)
+    unsigned *log;        // this lane's column: entry e at log[e * 32]
+
+    __device__ __forceinline__ void init(int k, float rb_, bool active, unsigned *log_) {
+#pragma unroll
+        for (int i = 0; i < K; ++i) key[i] = (i < K - k) ? -1.f : INFINITY;
+        rb = rb_;
+        bound = active ? rb_ : -1.f;
+        cnt = 0; slot = 0; log = log_;
+    }
+    __device__ __forceinline__ void insert(float c) {
+#pragma unroll
+        for (int i = K - 1; i > 0; --i) key[i] = fmaxf(key[i - 1], fminf(key[i], c));
+        key[0] = fminf(key[0], c);
+    }
+    // Prefilter (all 32 candidates, every lane): d2 ~ |P|^2 - 2 P.Q + |Q|^2 with P, Q relative to the tile centre,
+    // |P|^2 staged with the candidate -> 3 FFMA + compare per candidate instead of the contract's 8 unfused
+    // operations.  Its absolute error is below 2^-19 (|P| + |Q|)^2 (roundings of P, Q, |P|^2 and of the three fma),
+    // and a true neighbour has |P| <= |Q| + sqrt(bound), so with (a+b)^2 <= 2a^2 + 2b^2 the test
+    //     fma-chain <= bound - |Q|^2 + 2^-16 (|Q|^2 + bound)
+    // never rejects one.  Survivors are re-scored with the exact contract arithmetic in the drain loop.
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 &qr, const float4 *exact, const float4 *rel) {
+        unsigned m = 0;
+        const float thr = __fadd_ru(__fsub_ru(bound, qr.w), __fmul_ru(1.5258789e-5f, __fadd_ru(qr.w, bound)));
+#pragma unroll
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = rel[j];
+            const float a = fmaf(qr.x, c.x, fmaf(qr.y, c.y, fmaf(qr.z, c.z, c.w)));
+            m |= (a <= thr) ? (1u << j) : 0u;
+        }
+        while (__any_sync(kFull, m != 0)) {
+            if (m != 0) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                const float d2 = d2_point(q, exact[j]);
+                if (d2 <= bound) {                       // inclusive: candidates tied at the k-th value must be logged
+                    if (LOG) {
+                        log[cnt * 32] = (__float_as_uint(d2) & ~kLogIdMask) | (unsigned)(slot << 5 | j);
+                        ++cnt;                           // the caller keeps 32 free entries before every leaf
+                    }
+                    if (d2 < key[K - 1]) {
+                        insert(d2);
+                        bound = fminf(rb, key[K - 1]);
+                    }
+                }
+            }
+        }
+    }
+    // drop log entries that can no longer be inside `limit` (warp-uniform trip count, each lane its own column)
+    __device__ __forceinline__ void compact(float limit) {
+        const int maxc = __reduce_max_sync(kFull, cnt);
+        int wpos = 0;
+        for (int e = 0; e < maxc; ++e) {
+            if (e < cnt) {
+                const unsigned x = log[e * 32];
+                if (__uint_as_float(x & ~kLogIdMask) <= limit) { log[wpos * 32] = x; ++wpos; }
+            }
+        }
+        cnt = wpos;
+    }
+};
+
+template <int CAP>
+struct WarpScratch3 {
+    WarpScratch2 w;
+    float4 rel[kLeaf];    // staged leaf relative to the tile centre: (P, |P|^2)
+    int scanned[kSlotCap];
+    unsigned log[CAP * 32];
+};
+
+// Pass 1 over the tile's candidate leaves: slots 0..2 are the own leaf and its Morton neighbours (always scanned:
+// they produce the bound the list is collected with), the rest is the list.  One scan site keeps the kernel
+// inside the instruction cache (ncu r01 v4: one inlined scan per case stalled on no_instruction).
+// Returns leaves scanned, or -1 when the tile must go to the stack-walk kernel.
+template <int K, bool LOG, int CAP>
+__device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, const float4 &q,
+                                          ValLog<K, LOG> &v, WarpScratch3<CAP> &S, int &nlist, bool &lone) {
+    const int lane = threadIdx.x & 31;
+    lone = false;
+    const float cx = 0.5f * (tlo.x + thi.x), cy = 0.5f * (tlo.y + thi.y), cz = 0.5f * (tlo.z + thi.z);
+    float4 qr;                                  // (-2Q, |Q|^2), Q = q - centre
+    {
+        const float x = q.x - cx, y = q.y - cy, z = q.z - cz;
+        qr = make_float4(-2.f * x, -2.f * y, -2.f * z, fmaf(x, x, fmaf(y, y, z * z)));
+    }
+    int scanned = 0;
+    int total = 3;
+    for (int i = 0; i < total; ++i) {
+        int leaf;
+        if (i < 3) {
+            leaf = tile + (i == 0 ? 0 : (i == 1 ? -1 : 1));
+            if (leaf < 0 || leaf >= T.count[0]) leaf = -1;
+        } else {
+            leaf = S.w.list[i - 3];
+        }
+        if (leaf >= 0) {
+            bool want = true;
+            if (i >= 3) want = d2_point_box(q, T.lo[0][leaf], T.hi[0][leaf]) <= v.bound;
+            if (__any_sync(kFull, want)) {
+                if (LOG) {
+                    if (scanned >= kSlotCap) return -2;
+                    if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) {
+                        v.compact(v.bound);
+                        if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) return -3;   // that many ties: exact kernels decide
+                    }
+                    if (lane == 0) S.scanned[scanned] = leaf;
+                    v.slot = scanned;
+                }
+                const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
+                const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
+                __syncwarp();
+                S.w.ws.leaf[lane] = p;
+                S.rel[lane] = make_float4(x, y, z, fmaf(x, x, fmaf(y, y, z * z)));
+                __syncwarp();
+                v.scan_leaf(q, qr, S.w.ws.leaf, S.rel);
+                ++scanned;
+            }
+        }
+        if (i == 2) {
+            // A lane whose bound is far above the warp's median after the home leaves is an isolated point inside an
+            // otherwise dense tile: its search ball would make the whole tile list hundreds of leaves.  It leaves the
+            // tile (bound -1) and is finished by the point kernel.
+            {
+                float b = v.bound >= 0.f ? v.bound : INFINITY;
+#pragma unroll
+                for (int kk = 2; kk <= 32; kk <<= 1) {
+#pragma unroll
+                    for (int j = kk >> 1; j > 0; j >>= 1) {
+                        const float o = __shfl_xor_sync(kFull, b, j);
+                        const bool up = ((lane & kk) == 0) == ((lane & j) == 0);
+                        b = up ? fminf(b, o) : fmaxf(b, o);
+                    }
+                }
+                const int nact = __popc(__ballot_sync(kFull, v.bound >= 0.f));
+                const float med = __shfl_sync(kFull, b, nact >> 1);
+                lone = v.bound >= 0.f && v.bound > 16.f * med;
+                if (lone) v.bound = -1.f;
+            }
+            const float rmax = warp_max(v.bound);
+            if (!(rmax < INFINITY)) return -4;
+            nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w);
+            if (nlist < 0) {                    // wide or split tile: describe it by 8 sub-boxes and try again
+                make_sub_boxes(q, v.bound, v.bound >= 0.f, S.w);
+                nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w);
+                if (nlist < 0) return -5;
+            }
+            total = 3 + nlist;
+            if (LOG) v.compact(v.bound);        // the home leaves logged ~2-3 k entries per lane while the list filled up
+        }
+    }
+    return scanned;
+}
+
 template <int K>
-__global__ void __launch_bounds__(128) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
-    __shared__ WarpScratch s_ws[4];
+__device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, float *mean_d, size_t row) {
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < K; ++i)
+        if (i > K - k && key[i] != INFINITY) s += (double)__fsqrt_rn(key[i]);
+    mean_d[row] = (float)(s / (double)mean_k);
+}
+
+template <int K, int MODE>
+__global__ void __launch_bounds__(64) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+    constexpr int CAP = MODE == MODE_PCA ? LogCap<K>::value : 1;
+    constexpr bool LOG = MODE == MODE_PCA;
+    __shared__ WarpScratch3<CAP> s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = P.tile_begin + blockIdx.x * 4 + warp;
+    const int tile = P.tile_begin + blockIdx.x * 2 + warp;
     if (tile >= P.tile_end) return;
+    WarpScratch3<CAP> &S = s_ws[warp];
     const size_t pos = (size_t)tile * kLeaf + lane;
     const float4 q = T.pts[pos];
     const bool active = pos < (size_t)T.n;
     const int qidx = __float_as_int(q.w);
     const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)qidx;
     const int k = P.k;
+    const float4 tlo = T.lo[0][tile], thi = T.hi[0][tile];
 
-    float t;                                        // per-lane selection threshold
-    int scanned;
-    {
-        ValK<K> v;
-        v.init(k, P.rb, active);
-        scanned = traverse_tile(T, tile, q, v, s_ws[warp]);
-        if (P.mode == MODE_SOR) {
-            if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
-            if (!active) return;
-            double s = 0.0;
-#pragma unroll
-            for (int i = 0; i < K; ++i)
-                if (i > K - k && v.key[i] != INFINITY) s += (double)__fsqrt_rn(v.key[i]);
-            P.mean_d[row] = (float)(s / (double)P.mean_k);
-            return;
+    ValLog<K, LOG> v;
+    v.init(k, P.rb, active, S.log + lane);
+    int nlist = 0;
+    bool lone = false;
+    const int scanned = scan_pass1<K, LOG, CAP>(T, tile, tlo, thi, q, v, S, nlist, lone);
+    if (scanned >= 0) {                             // isolated lanes of a dense tile -> point kernel
+        const unsigned lm = __ballot_sync(kFull, lone);
+        if (lm) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(P.defer_count, __popc(lm));
+            base = __shfl_sync(kFull, base, 0);
+            if (lone) {
+                const int slot = base + __popc(lm & ((1u << lane) - 1u));
+                P.defer_list[slot] = qidx;
+                P.defer_row[slot] = (long long)row;
+            }
         }
-        t = fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX);   // finite: the +inf pad points of the last leaf never qualify
     }
-    Collect c;
-    c.init(t, active);
+    if (scanned < 0) {          // unbounded / very wide / heavily tied search: the tile's queries go to the exact point kernel
+        int base = 0;
+        const unsigned am = __ballot_sync(kFull, active);
+        if (lane == 0) {
+            base = atomicAdd(P.defer_count, __popc(am));
+            if (P.stat_scanned) { atomicAdd(P.stat_scanned + 3, 1ull); atomicAdd(P.stat_scanned + 4 - scanned, 1ull); }
+        }
+        base = __shfl_sync(kFull, base, 0);
+        if (active) {
+            const int slot = base + __popc(am & ((1u << lane) - 1u));
+            P.defer_list[slot] = qidx;
+            P.defer_row[slot] = (long long)row;
+        }
+        return;
+    }
+    if (P.stat_scanned && lane == 0) {
+        atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+        atomicAdd(P.stat_scanned + 2, (unsigned long long)nlist);
+    }
+    if (MODE == MODE_SOR) {
+        if (active && !lone) sor_finish<K>(v.key, k, P.mean_k, P.mean_d, row);
+        return;
+    }
+    // pass 2: the surviving log entries are the neighbour set (plus truncation false positives, re-tested exactly)
+    const float t = fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX);   // finite: the +inf pads of the last leaf never qualify
+    v.compact(t);
     __syncwarp();
-    scanned += traverse_tile(T, tile, q, c, s_ws[warp]);
-    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
-    if (!active) return;
-    if (c.count > k) {                              // ties at the k-th distance overflow the list: exact kernel decides
+    const int maxc = __reduce_max_sync(kFull, v.cnt);
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)maxc);
+    int count = 0;
+    float m[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) m[i] = 0.f;
+    for (int e = 0; e < maxc; ++e) {
+        if (e < v.cnt) {
+            const unsigned id = v.log[e * 32] & kLogIdMask;
+            const int leaf = S.scanned[id >> 5];
+            const float4 c = T.pts[(size_t)leaf * kLeaf + (id & 31u)];
+            if (d2_point(q, c) <= t) {
+                ++count;
+                const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
+                m[0] += x; m[1] += y; m[2] += z;
+                m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+            }
+        }
+    }
+    if (!active || lone) return;
+    if (count > k) {                                // ties at the k-th distance overflow the list: exact kernel decides
         const int slot = atomicAdd(P.defer_count, 1);
         P.defer_list[slot] = qidx;
         P.defer_row[slot] = (long long)row;
         return;
     }
-    pca_finish(P.pca, q, c.m, c.count, row);
-    if (P.count) P.count[row] = c.count;
+    pca_finish(P.pca, q, m, count, row);
+    if (P.count) P.count[row] = count;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -650,8 +955,10 @@ static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cuda
 }
 
 template <int K>
-static void launch_sel(const TreeView &T, const TileParams &P, int blocks, cudaStream_t st) {
-    k_tile_sel<K><<<blocks, 128, 0, st>>>(T, P);
+static void launch_sel(const TreeView &T, const TileParams &P, int blocks, int sms, cudaStream_t st) {
+    const int ntiles = P.tile_end - P.tile_begin;
+    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else k_tile_sel<K, MODE_SOR><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
 }
 
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
@@ -672,7 +979,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {
-        CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 8, ctx->stream));
+        CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 96, ctx->stream));
         P.stat_scanned = (unsigned long long *)((char *)ctx->scratch.p + 1024);
     }
     const int ntiles = P.tile_end - P.tile_begin;
@@ -692,39 +999,43 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
         // two-pass selection; queries whose k-th distance is tied beyond the list go to the exact point kernel
         const size_t rows = (size_t)ntiles * kLeaf;
         const size_t off_list = 256, off_rows = off_list + ((rows * 4 + 255) & ~(size_t)255);
-        if (a.mode == MODE_PCA) {
-            CCG_CUDA(ctx, ctx->defer.reserve(off_rows + rows * 8));
-            CCG_CUDA(ctx, cudaMemsetAsync(ctx->defer.p, 0, 4, st));
-            P.defer_count = ctx->defer.as<int>();
-            P.defer_list = (int32_t *)((char *)ctx->defer.p + off_list);
-            P.defer_row = (long long *)((char *)ctx->defer.p + off_rows);
-        }
-        if (k <= 8) launch_sel<8>(T, P, blocks, st);
-        else if (k <= 16) launch_sel<16>(T, P, blocks, st);
-        else if (k <= 20) launch_sel<20>(T, P, blocks, st);
-        else if (k <= 24) launch_sel<24>(T, P, blocks, st);
-        else if (k <= 32) launch_sel<32>(T, P, blocks, st);
-        else if (k <= 48) launch_sel<48>(T, P, blocks, st);
-        else launch_sel<64>(T, P, blocks, st);
-        if (a.mode == MODE_PCA) {
+        const size_t off_slow = off_rows + ((rows * 8 + 255) & ~(size_t)255);
+        CCG_CUDA(ctx, ctx->defer.reserve(off_slow + (size_t)ntiles * 4));
+        CCG_CUDA(ctx, cudaMemsetAsync(ctx->defer.p, 0, 8, st));
+        P.defer_count = ctx->defer.as<int>();
+        P.slow_count = ctx->defer.as<int>() + 1;
+        P.defer_list = (int32_t *)((char *)ctx->defer.p + off_list);
+        P.defer_row = (long long *)((char *)ctx->defer.p + off_rows);
+        P.slow_tiles = (int32_t *)((char *)ctx->defer.p + off_slow);
+        if (k <= 8) launch_sel<8>(T, P, blocks, ctx->sm_count, st);
+        else if (k <= 16) launch_sel<16>(T, P, blocks, ctx->sm_count, st);
+        else if (k <= 20) launch_sel<20>(T, P, blocks, ctx->sm_count, st);
+        else if (k <= 24) launch_sel<24>(T, P, blocks, ctx->sm_count, st);
+        else if (k <= 32) launch_sel<32>(T, P, blocks, ctx->sm_count, st);
+        else if (k <= 48) launch_sel<48>(T, P, blocks, ctx->sm_count, st);
+        else launch_sel<64>(T, P, blocks, ctx->sm_count, st);
+        {
             PointParams Q{};
             Q.queries = P.defer_list; Q.nq = 0; Q.nq_dev = P.defer_count; Q.rows = P.defer_row;
-            Q.mode = MODE_PCA; Q.k = k; Q.rb = a.rb; Q.list_rows = 0;
-            Q.count = a.count; Q.pca = P.pca;
-            k_point_query<<<ctx->sm_count * 4, 128, 0, st>>>(T, Q);
+            Q.mode = a.mode; Q.k = k; Q.rb = a.rb; Q.list_rows = 0;
+            Q.count = a.count; Q.pca = P.pca; Q.mean_k = a.mean_k; Q.mean_d = a.mean_d;
+            k_point_query<<<ctx->sm_count * 8, 128, 0, st>>>(T, Q);
             ctx->stats.launches++;
         }
     }
     ctx->stats.launches++;
     CCG_CUDA(ctx, cudaGetLastError());
     if (ctx->collect_stats) {
-        unsigned long long s = 0;
-        CCG_CUDA(ctx, cudaMemcpyAsync(&s, P.stat_scanned, 8, cudaMemcpyDeviceToHost, st));
+        unsigned long long s4[12] = {};
+        CCG_CUDA(ctx, cudaMemcpyAsync(s4, P.stat_scanned, 96, cudaMemcpyDeviceToHost, st));
         int nd = 0;
         if (P.defer_count) CCG_CUDA(ctx, cudaMemcpyAsync(&nd, P.defer_count, 4, cudaMemcpyDeviceToHost, st));
         CCG_CUDA(ctx, cudaStreamSynchronize(st));
-        ctx->stats.leaves_scanned = (int64_t)s;
+        ctx->stats.leaves_scanned = (int64_t)s4[0];
         ctx->stats.deferred_queries = nd;
+        if (getenv("CCG_VERBOSE_STATS"))
+            fprintf(stderr, "[ccg] tiles=%d leaves scanned=%llu (pass2 %llu) listed=%llu slow tiles=%llu (slots %llu, ties %llu, unbounded %llu, wide %llu) deferred=%d\n", ntiles,
+                    s4[0], s4[1], s4[2], s4[3], s4[6], s4[7], s4[8], s4[9], nd);
     }
     return CCG_OK;
 }
