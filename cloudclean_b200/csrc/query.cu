@@ -569,8 +569,8 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 // with one lane per child box then lists every leaf whose box is within the warp's largest bound of the tile
 // box (ballot + popc compaction into shared memory).  Compared with the nearest-first stack walk this costs a
 // few hundred instructions per tile instead of ~100 per visited child, and pass 2 re-uses the list.
-constexpr int kListCap = 128;     // leaves listed per tile (overflow -> stack walk, exact as well)
-constexpr int kQueueCap = 64;     // inner nodes per level
+constexpr int kListCap = 512;     // leaves listed per tile (overflow -> stack walk, exact as well)
+constexpr int kQueueCap = 128;     // inner nodes per level
 struct WarpScratch2 {
     WarpScratch ws;
     int list[kListCap];
@@ -653,7 +653,7 @@ __device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, boo
 // truncated d2 is a lower bound of the true one, good enough to drop stale entries (compact) without a gather.
 constexpr unsigned kLogIdMask = 0x1fffu;
 constexpr int kSlotCap = 256;     // leaves scanned per tile that the 8-bit slot can name
-template <int K> struct LogCap { static constexpr int value = K <= 32 ? 96 : 128; };
+template <int K> struct LogCap { static constexpr int value = K <= 20 ? 64 : (K <= 32 ? 96 : 128); };
 
 template <int K, bool LOG>
 struct ValLog {
@@ -747,17 +747,27 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
     }
     int scanned = 0;
     int total = 3;
+    // entry i+1 (its points and box) is fetched while entry i is scored: the walk is a chain of dependent L2 reads otherwise
+    int leaf = tile, nleaf = -1;
+    float4 p = q, blo = tlo, bhi = thi, np = q, nlo = tlo, nhi = thi;
     for (int i = 0; i < total; ++i) {
-        int leaf;
-        if (i < 3) {
-            leaf = tile + (i == 0 ? 0 : (i == 1 ? -1 : 1));
-            if (leaf < 0 || leaf >= T.count[0]) leaf = -1;
+        if (i + 1 < total) {
+            if (i + 1 < 3) {
+                nleaf = tile + (i == 0 ? -1 : 1);
+                if (nleaf < 0 || nleaf >= T.count[0]) nleaf = -1;
+            } else {
+                nleaf = S.w.list[i - 2];
+            }
+            if (nleaf >= 0) {
+                np = T.pts[(size_t)nleaf * kLeaf + lane];
+                nlo = T.lo[0][nleaf]; nhi = T.hi[0][nleaf];
+            }
         } else {
-            leaf = S.w.list[i - 3];
+            nleaf = -1;
         }
         if (leaf >= 0) {
             bool want = true;
-            if (i >= 3) want = d2_point_box(q, T.lo[0][leaf], T.hi[0][leaf]) <= v.bound;
+            if (i >= 3) want = d2_point_box(q, blo, bhi) <= v.bound;
             if (__any_sync(kFull, want)) {
                 if (LOG) {
                     if (scanned >= kSlotCap) return -2;
@@ -768,7 +778,6 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
                     if (lane == 0) S.scanned[scanned] = leaf;
                     v.slot = scanned;
                 }
-                const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
                 const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
                 __syncwarp();
                 S.w.ws.leaf[lane] = p;
@@ -808,7 +817,13 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
             }
             total = 3 + nlist;
             if (LOG) v.compact(v.bound);        // the home leaves logged ~2-3 k entries per lane while the list filled up
+            if (nlist > 0) {
+                nleaf = S.w.list[0];
+                np = T.pts[(size_t)nleaf * kLeaf + lane];
+                nlo = T.lo[0][nleaf]; nhi = T.hi[0][nleaf];
+            }
         }
+        leaf = nleaf; p = np; blo = nlo; bhi = nhi;
     }
     return scanned;
 }
@@ -823,7 +838,7 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
 }
 
 template <int K, int MODE>
-__global__ void __launch_bounds__(64) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+__global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
     constexpr int CAP = MODE == MODE_PCA ? LogCap<K>::value : 1;
     constexpr bool LOG = MODE == MODE_PCA;
     __shared__ WarpScratch3<CAP> s_ws[2];
@@ -1189,46 +1204,70 @@ __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ Tre
         unsigned m = ws.mask[sp - 1];
         __syncwarp();
         if (m == 0) { --sp; continue; }
-        // nearest surviving child first: tightens the bound quickly
-        int cbit;
-        {
-            const bool mine = (m >> lane) & 1u;
-            float bd = INFINITY;
-            if (mine) bd = d2_point_box(q, T.lo[lv][base + lane], T.hi[lv][base + lane]);
-            unsigned kk = __float_as_uint(bd);
-            unsigned best = kk;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(kFull, best, o));
-            const unsigned who = __ballot_sync(kFull, mine && kk == best);
-            cbit = who ? (__ffs(who) - 1) : (__ffs(m) - 1);
-            // drop children that no longer pass the current bound
-            const unsigned still = __ballot_sync(kFull, mine && bd <= bound);
-            m &= still;
-            if (!((m >> cbit) & 1u)) { if (lane == 0) ws.mask[sp - 1] = 0; __syncwarp(); --sp; continue; }
-        }
-        m &= ~(1u << cbit);
-        if (lane == 0) ws.mask[sp - 1] = m;
-        const int child = base + cbit;
+        const bool mine = (m >> lane) & 1u;
+        float bd = INFINITY;
+        if (mine) bd = d2_point_box(q, T.lo[lv][base + lane], T.hi[lv][base + lane]);
         if (lv == 0) {
-            const float4 c = T.pts[(size_t)child * kLeaf + lane];
-            const float dd = d2_point(q, c);
-            const u64 ck = ((u64)__float_as_uint(dd) << 32) | (unsigned)__float_as_int(c.w);
-            unsigned passers = __ballot_sync(kFull, dd <= bound && ck < worst);
-            while (passers) {
-                const int src = __ffs(passers) - 1;
-                passers &= passers - 1;
-                const u64 nk = shfl64(ck, src);
-                if (!(nk < worst)) continue;                  // the bound moved since the ballot
-                const int pos = __popc(__ballot_sync(kFull, key0 < nk)) + __popc(__ballot_sync(kFull, key1 < nk));
-                const u64 up0 = shfl_up64(key0), up1 = shfl_up64(key1), carry = shfl64(key0, 31);
-                const int s0 = lane, s1 = 32 + lane;
-                key0 = s0 > pos ? up0 : (s0 == pos ? nk : key0);
-                key1 = s1 > pos ? (lane == 0 ? carry : up1) : (s1 == pos ? nk : key1);
-                worst = (k - 1) < 32 ? shfl64(key0, k - 1) : shfl64(key1, k - 1 - 32);
-                bound = fminf(P.rb, __uint_as_float((unsigned)(worst >> 32)));
+            // A group of up to 32 leaves: rank them ONCE by box distance (bitonic sort of the distance bits with the lane
+            // id in the low 5 bits) and score them in that order until the first one beyond the bound — every later one
+            // is at least as far.  Re-ranking the group after every leaf cost more than the scoring itself.
+            if (lane == 0) ws.mask[sp - 1] = 0;
+            --sp;
+            unsigned key = mine ? ((__float_as_uint(bd) & ~31u) | (unsigned)lane) : (0xffffffe0u | (unsigned)lane);
+#pragma unroll
+            for (int kk = 2; kk <= 32; kk <<= 1) {
+#pragma unroll
+                for (int j = kk >> 1; j > 0; j >>= 1) {
+                    const unsigned o = __shfl_xor_sync(kFull, key, j);
+                    const bool up = ((lane & kk) == 0) == ((lane & j) == 0);
+                    key = up ? min(key, o) : max(key, o);
+                }
+            }
+            const int nmine = __popc(m);
+            for (int r = 0; r < nmine; ++r) {
+                const int cbit = (int)(__shfl_sync(kFull, key, r) & 31u);
+                const float bdc = __shfl_sync(kFull, bd, cbit);
+                if (bdc > bound) {
+                    // ranks ignore the low 5 distance bits: a later leaf may still be a hair closer than this one
+                    if (__float_as_uint(bdc) - __float_as_uint(bound) > 32u) break;
+                    continue;
+                }
+                const float4 c = T.pts[(size_t)(base + cbit) * kLeaf + lane];
+                const float dd = d2_point(q, c);
+                const u64 ck = ((u64)__float_as_uint(dd) << 32) | (unsigned)__float_as_int(c.w);
+                unsigned passers = __ballot_sync(kFull, dd <= bound && ck < worst);
+                while (passers) {
+                    const int src = __ffs(passers) - 1;
+                    passers &= passers - 1;
+                    const u64 nk = shfl64(ck, src);
+                    if (!(nk < worst)) continue;                  // the bound moved since the ballot
+                    const int pos = __popc(__ballot_sync(kFull, key0 < nk)) + __popc(__ballot_sync(kFull, key1 < nk));
+                    const u64 up0 = shfl_up64(key0), up1 = shfl_up64(key1), carry = shfl64(key0, 31);
+                    const int s0 = lane, s1 = 32 + lane;
+                    key0 = s0 > pos ? up0 : (s0 == pos ? nk : key0);
+                    key1 = s1 > pos ? (lane == 0 ? carry : up1) : (s1 == pos ? nk : key1);
+                    worst = (k - 1) < 32 ? shfl64(key0, k - 1) : shfl64(key1, k - 1 - 32);
+                    bound = fminf(P.rb, __uint_as_float((unsigned)(worst >> 32)));
+                }
             }
         } else {
-            const int first = child << 5;
+            // inner node: nearest surviving child first (tightens the bound quickly)
+            int cbit;
+            {
+                unsigned kk = __float_as_uint(bd);
+                unsigned best = kk;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(kFull, best, o));
+                const unsigned who = __ballot_sync(kFull, mine && kk == best);
+                cbit = who ? (__ffs(who) - 1) : (__ffs(m) - 1);
+                // drop children that no longer pass the current bound
+                const unsigned still = __ballot_sync(kFull, mine && bd <= bound);
+                m &= still;
+                if (!((m >> cbit) & 1u)) { if (lane == 0) ws.mask[sp - 1] = 0; __syncwarp(); --sp; continue; }
+            }
+            m &= ~(1u << cbit);
+            if (lane == 0) ws.mask[sp - 1] = m;
+            const int first = (base + cbit) << 5;
             const int c = first + lane;
             bool pass = false;
             if (c < T.count[lv - 1]) pass = d2_point_box(q, T.lo[lv - 1][c], T.hi[lv - 1][c]) <= bound;
