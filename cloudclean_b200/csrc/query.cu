@@ -646,29 +646,40 @@ __device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, boo
     __syncwarp();
 }
 
+// mask of the staged candidates that may lie within `bound` of the lane's query (never misses one; see ValLog)
+__device__ __forceinline__ unsigned prefilter(const float4 &qr, const float4 *rel, float bound) {
+    unsigned m = 0;
+    const float thr = __fadd_ru(__fsub_ru(bound, qr.w), __fmul_ru(1.5258789e-5f, __fadd_ru(qr.w, bound)));
+#pragma unroll
+    for (int j = 0; j < kLeaf; ++j) {
+        const float4 c = rel[j];
+        const float a = fmaf(qr.x, c.x, fmaf(qr.y, c.y, fmaf(qr.z, c.z, c.w)));
+        m |= (a <= thr) ? (1u << j) : 0u;
+    }
+    return m;
+}
+
 // Pass-1 visitor of k_tile_sel: the value list of ValK plus (LOG) a per-lane LOG in shared memory of every
-// candidate that was inside the lane's bound when it was scored.  The final neighbour set {d2 <= T} is a subset
-// of the log (T <= bound at all times), so pass 2 never rescans leaves: it walks the ~k surviving log entries.
-// A log word holds d2 with its low 13 mantissa bits replaced by (scan slot << 5 | position in leaf); the
-// truncated d2 is a lower bound of the true one, good enough to drop stale entries (compact) without a gather.
-constexpr unsigned kLogIdMask = 0x1fffu;
-constexpr int kSlotCap = 256;     // leaves scanned per tile that the 8-bit slot can name
-template <int K> struct LogCap { static constexpr int value = K <= 20 ? 64 : (K <= 32 ? 96 : 128); };
+// candidate of a LISTED leaf that was inside the lane's bound when it was scored.  The final neighbour set
+// {d2 <= T} is a subset of the home leaves' points and the log (T <= bound at all times), so pass 2 never rescans
+// the list: it re-scores the three home leaves against T and walks the log.  A log entry is 16 bits,
+// (list index << 5 | position in leaf); dropping stale entries (compact) re-scores them from the point array.
+template <int K> struct LogCap { static constexpr int value = K <= 32 ? 96 : 128; };
 
 template <int K, bool LOG>
 struct ValLog {
     float key[K];
     float bound, rb;
-    int cnt;              // log entries of this lane
-    int slot;             // scan slot of the leaf being scored (warp-uniform)
-    unsigned *log;        // this lane's column: entry e at log[e * 32]
+    int cnt;                  // log entries of this lane
+    int slot;                 // list index of the leaf being scored (warp-uniform); < 0: home leaf, not logged
+    unsigned short *log;      // this lane's column: entry e at log[e * 32]
 
-    __device__ __forceinline__ void init(int k, float rb_, bool active, unsigned *log_) {
+    __device__ __forceinline__ void init(int k, float rb_, bool active, unsigned short *log_) {
 #pragma unroll
         for (int i = 0; i < K; ++i) key[i] = (i < K - k) ? -1.f : INFINITY;
         rb = rb_;
         bound = active ? rb_ : -1.f;
-        cnt = 0; slot = 0; log = log_;
+        cnt = 0; slot = -1; log = log_;
     }
     __device__ __forceinline__ void insert(float c) {
 #pragma unroll
@@ -682,22 +693,15 @@ struct ValLog {
     //     fma-chain <= bound - |Q|^2 + 2^-16 (|Q|^2 + bound)
     // never rejects one.  Survivors are re-scored with the exact contract arithmetic in the drain loop.
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 &qr, const float4 *exact, const float4 *rel) {
-        unsigned m = 0;
-        const float thr = __fadd_ru(__fsub_ru(bound, qr.w), __fmul_ru(1.5258789e-5f, __fadd_ru(qr.w, bound)));
-#pragma unroll
-        for (int j = 0; j < kLeaf; ++j) {
-            const float4 c = rel[j];
-            const float a = fmaf(qr.x, c.x, fmaf(qr.y, c.y, fmaf(qr.z, c.z, c.w)));
-            m |= (a <= thr) ? (1u << j) : 0u;
-        }
+        unsigned m = prefilter(qr, rel, bound);
         while (__any_sync(kFull, m != 0)) {
             if (m != 0) {
                 const int j = __ffs(m) - 1;
                 m &= m - 1;
                 const float d2 = d2_point(q, exact[j]);
                 if (d2 <= bound) {                       // inclusive: candidates tied at the k-th value must be logged
-                    if (LOG) {
-                        log[cnt * 32] = (__float_as_uint(d2) & ~kLogIdMask) | (unsigned)(slot << 5 | j);
+                    if (LOG && slot >= 0) {
+                        log[cnt * 32] = (unsigned short)(slot << 5 | j);
                         ++cnt;                           // the caller keeps 32 free entries before every leaf
                     }
                     if (d2 < key[K - 1]) {
@@ -708,43 +712,41 @@ struct ValLog {
             }
         }
     }
-    // drop log entries that can no longer be inside `limit` (warp-uniform trip count, each lane its own column)
-    __device__ __forceinline__ void compact(float limit) {
-        const int maxc = __reduce_max_sync(kFull, cnt);
-        int wpos = 0;
-        for (int e = 0; e < maxc; ++e) {
-            if (e < cnt) {
-                const unsigned x = log[e * 32];
-                if (__uint_as_float(x & ~kLogIdMask) <= limit) { log[wpos * 32] = x; ++wpos; }
-            }
-        }
-        cnt = wpos;
-    }
 };
 
 template <int CAP>
 struct WarpScratch3 {
     WarpScratch2 w;
     float4 rel[kLeaf];    // staged leaf relative to the tile centre: (P, |P|^2)
-    int scanned[kSlotCap];
-    unsigned log[CAP * 32];
+    unsigned short log[CAP * 32];
 };
 
-// Pass 1 over the tile's candidate leaves: slots 0..2 are the own leaf and its Morton neighbours (always scanned:
+// re-score this lane's log entries and keep those still within `limit` (warp-uniform trip count)
+template <int K, bool LOG, int CAP>
+__device__ __forceinline__ void compact_log(const TreeView &T, const float4 &q, ValLog<K, LOG> &v, const WarpScratch3<CAP> &S,
+                                            float limit) {
+    const int maxc = __reduce_max_sync(kFull, v.cnt);
+    int wpos = 0;
+    for (int e = 0; e < maxc; ++e) {
+        if (e < v.cnt) {
+            const unsigned id = v.log[e * 32];
+            const float4 c = T.pts[(size_t)S.w.list[id >> 5] * kLeaf + (id & 31u)];
+            if (d2_point(q, c) <= limit) { v.log[wpos * 32] = (unsigned short)id; ++wpos; }
+        }
+    }
+    v.cnt = wpos;
+}
+
+// Pass 1 over the tile's candidate leaves: entries 0..2 are the own leaf and its Morton neighbours (always scanned:
 // they produce the bound the list is collected with), the rest is the list.  One scan site keeps the kernel
 // inside the instruction cache (ncu r01 v4: one inlined scan per case stalled on no_instruction).
-// Returns leaves scanned, or -1 when the tile must go to the stack-walk kernel.
+// Returns leaves scanned, or < 0 when the tile must go to the point kernel.
 template <int K, bool LOG, int CAP>
 __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, const float4 &q,
+                                          const float4 &qr, float cx, float cy, float cz,
                                           ValLog<K, LOG> &v, WarpScratch3<CAP> &S, int &nlist, bool &lone) {
     const int lane = threadIdx.x & 31;
     lone = false;
-    const float cx = 0.5f * (tlo.x + thi.x), cy = 0.5f * (tlo.y + thi.y), cz = 0.5f * (tlo.z + thi.z);
-    float4 qr;                                  // (-2Q, |Q|^2), Q = q - centre
-    {
-        const float x = q.x - cx, y = q.y - cy, z = q.z - cz;
-        qr = make_float4(-2.f * x, -2.f * y, -2.f * z, fmaf(x, x, fmaf(y, y, z * z)));
-    }
     int scanned = 0;
     int total = 3;
     // entry i+1 (its points and box) is fetched while entry i is scored: the walk is a chain of dependent L2 reads otherwise
@@ -769,14 +771,12 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
             bool want = true;
             if (i >= 3) want = d2_point_box(q, blo, bhi) <= v.bound;
             if (__any_sync(kFull, want)) {
-                if (LOG) {
-                    if (scanned >= kSlotCap) return -2;
+                if (LOG && i >= 3) {
                     if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) {
-                        v.compact(v.bound);
-                        if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) return -3;   // that many ties: exact kernels decide
+                        compact_log<K, LOG, CAP>(T, q, v, S, v.bound);
+                        if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) return -3;   // that many ties: exact kernel decides
                     }
-                    if (lane == 0) S.scanned[scanned] = leaf;
-                    v.slot = scanned;
+                    v.slot = i - 3;
                 }
                 const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
                 __syncwarp();
@@ -816,7 +816,6 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
                 if (nlist < 0) return -5;
             }
             total = 3 + nlist;
-            if (LOG) v.compact(v.bound);        // the home leaves logged ~2-3 k entries per lane while the list filled up
             if (nlist > 0) {
                 nleaf = S.w.list[0];
                 np = T.pts[(size_t)nleaf * kLeaf + lane];
@@ -854,11 +853,17 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
     const int k = P.k;
     const float4 tlo = T.lo[0][tile], thi = T.hi[0][tile];
 
+    const float cx = 0.5f * (tlo.x + thi.x), cy = 0.5f * (tlo.y + thi.y), cz = 0.5f * (tlo.z + thi.z);
+    float4 qr;                                  // (-2Q, |Q|^2), Q = q - centre
+    {
+        const float x = q.x - cx, y = q.y - cy, z = q.z - cz;
+        qr = make_float4(-2.f * x, -2.f * y, -2.f * z, fmaf(x, x, fmaf(y, y, z * z)));
+    }
     ValLog<K, LOG> v;
     v.init(k, P.rb, active, S.log + lane);
     int nlist = 0;
     bool lone = false;
-    const int scanned = scan_pass1<K, LOG, CAP>(T, tile, tlo, thi, q, v, S, nlist, lone);
+    const int scanned = scan_pass1<K, LOG, CAP>(T, tile, tlo, thi, q, qr, cx, cy, cz, v, S, nlist, lone);
     if (scanned >= 0) {                             // isolated lanes of a dense tile -> point kernel
         const unsigned lm = __ballot_sync(kFull, lone);
         if (lm) {
@@ -895,21 +900,42 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
         if (active && !lone) sor_finish<K>(v.key, k, P.mean_k, P.mean_d, row);
         return;
     }
-    // pass 2: the surviving log entries are the neighbour set (plus truncation false positives, re-tested exactly)
-    const float t = fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX);   // finite: the +inf pads of the last leaf never qualify
-    v.compact(t);
-    __syncwarp();
-    const int maxc = __reduce_max_sync(kFull, v.cnt);
-    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)maxc);
+    // pass 2: the neighbour set {d2 <= t} lies in the home leaves and the log
+    const float t = (active && !lone) ? fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX) : -1.f;   // finite: +inf pads never qualify
     int count = 0;
     float m[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) m[i] = 0.f;
+    for (int i = 0; i < 3; ++i) {
+        const int leaf = tile + (i == 0 ? 0 : (i == 1 ? -1 : 1));
+        if (leaf < 0 || leaf >= T.count[0]) continue;
+        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
+        const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
+        __syncwarp();
+        S.w.ws.leaf[lane] = p;
+        S.rel[lane] = make_float4(x, y, z, fmaf(x, x, fmaf(y, y, z * z)));
+        __syncwarp();
+        unsigned msk = prefilter(qr, S.rel, t);
+        while (__any_sync(kFull, msk != 0)) {
+            if (msk != 0) {
+                const int j = __ffs(msk) - 1;
+                msk &= msk - 1;
+                const float4 c = S.w.ws.leaf[j];
+                if (d2_point(q, c) <= t) {
+                    ++count;
+                    const float dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
+                    m[0] += dx; m[1] += dy; m[2] += dz;
+                    m[3] += dx * dx; m[4] += dx * dy; m[5] += dx * dz; m[6] += dy * dy; m[7] += dy * dz; m[8] += dz * dz;
+                }
+            }
+        }
+    }
+    const int maxc = __reduce_max_sync(kFull, v.cnt);
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)maxc);
     for (int e = 0; e < maxc; ++e) {
         if (e < v.cnt) {
-            const unsigned id = v.log[e * 32] & kLogIdMask;
-            const int leaf = S.scanned[id >> 5];
-            const float4 c = T.pts[(size_t)leaf * kLeaf + (id & 31u)];
+            const unsigned id = v.log[e * 32];
+            const float4 c = T.pts[(size_t)S.w.list[id >> 5] * kLeaf + (id & 31u)];
             if (d2_point(q, c) <= t) {
                 ++count;
                 const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
