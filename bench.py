@@ -348,7 +348,7 @@ def main():
                         "ms_per_step": ms_e2e / e2e_steps},
                 "gpu_launches": int(n_launch),
                 "clocks": clocks,
-                "roofline": {"bound": "hbm", "kernel": f"k_tile_topk<{K}> (kNN + covariance + eigensolve)", "achieved": achieved,
+                "roofline": {"bound": "hbm", "kernel": f"k_tile_sel<{K}, MODE_PCA> (two-pass kNN selection + covariance + eigensolve + features)", "achieved": achieved,
                              "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(),
                              "peak_source": peak_src, "algorithmic_bytes_per_point": BYTES_QUERY, "points_per_launch": q_rows,
                              "kernel_ms": k_ms,

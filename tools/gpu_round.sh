@@ -8,10 +8,10 @@ python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=
 cat gpurun_out/bench.json
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 cat gpurun_out/bench_ref.json
-CMD="python bench.py --steps 2 --warmup 1 --shrink 2 --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^k_|Device" -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu launches rc=$?"
 $CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_tile_topk -s 1 -c 1 -o gpurun_out/prof_topk $CMD > gpurun_out/ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_tile_sel -s 1 -c 1 -f -o gpurun_out/prof_sel $CMD > gpurun_out/ncu2.log 2>&1
 echo "ncu full rc=$?"
