@@ -7,7 +7,7 @@ SRC = cloudclean_b200/csrc
 OBJ = $(SRC)/build.o $(SRC)/query.o $(SRC)/gridnormals.o $(SRC)/api.o
 LIB = cloudclean_b200/libccgpu.so
 
-all: $(LIB) oracle
+all: $(LIB) oracle adapters
 
 $(SRC)/%.o: $(SRC)/%.cu $(SRC)/common.cuh include/ccgpu.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(@:.o=.ptxas.log) || (cat $(@:.o=.ptxas.log); exit 1)
@@ -18,7 +18,12 @@ $(LIB): $(OBJ)
 oracle:
 	$(MAKE) -C oracle
 
+# reference-named C++ host layer + its GPU test program (links only the C ABI)
+adapters: adapters/test_adapters
+adapters/test_adapters: adapters/test_adapters.cpp adapters/cloudclean_gpu.hpp include/ccgpu.h $(LIB)
+	g++ -O2 -std=c++14 -ffp-contract=off -Wall -I. adapters/test_adapters.cpp -o $@ -Lcloudclean_b200 -lccgpu -Wl,-rpath,'$$ORIGIN/../cloudclean_b200'
+
 clean:
-	rm -f $(OBJ) $(LIB) $(SRC)/*.ptxas.log
+	rm -f $(OBJ) $(LIB) $(SRC)/*.ptxas.log adapters/test_adapters
 	$(MAKE) -C oracle clean
-.PHONY: all oracle clean
+.PHONY: all oracle adapters clean

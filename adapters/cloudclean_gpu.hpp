@@ -1,0 +1,249 @@
+// cloudclean_gpu.hpp — C++ host layer over the libccgpu C ABI with the reference's own call surface.
+//
+// This is the file a CloudClean maintainer adds to src/utilities/ (INTEGRATION.md): every function keeps the
+// name, argument meaning, result layout and error behaviour of the reference function it replaces, and forwards
+// the per-point loop to the GPU through include/ccgpu.h.  No Qt, no PCL needed to compile it:
+//   * with -DCCGPU_WITH_PCL the real pcl::PointXYZI / pcl::Normal / Eigen::Vector3f are used;
+//   * otherwise layout-compatible stand-ins (same size, same field offsets — SURVEY.md §8 "Host layouts") are
+//     defined in namespace ccgpu so the adapters and their tests build in an image without PCL.
+//
+// Reference functions mirrored (file:line):
+//   getPCA<PointT>(cloud*, radius, max_nn)                    src/utilities/cv.h:76-116
+//   getHist(cloud, radius, max_nn)                            src/utilities/cv.cpp:249-308
+//   NormalEstimator::estimateNormals(cloud)                   src/plugins/normalestimation/normalestimation.cpp:268-470
+//   OutlierFilter::filter()  (index list handed to Select)    src/plugins/outlierfilter/outlierfilter.cpp:120-179
+//   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
+//   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
+// plus the two north-star operators that have no reference function (PCL definitions):
+//   knnNormals (kNN(k)+PCA normals/curvature), statisticalOutliers (mean + alpha*sigma).
+//
+// Error behaviour: the reference logs with qDebug and returns early / returns an empty result; nothing throws
+// across the plugin boundary (App::notify swallows exceptions, app.cpp:345-355).  Here every adapter returns an
+// empty result on failure and leaves the message in Session::lastError().
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../include/ccgpu.h"
+
+#ifdef CCGPU_WITH_PCL
+#include <pcl/point_types.h>
+#include <Eigen/Core>
+#endif
+
+namespace ccgpu {
+
+#ifdef CCGPU_WITH_PCL
+using PointXYZI = pcl::PointXYZI;
+using PointXYZINormal = pcl::PointXYZINormal;
+using Normal = pcl::Normal;
+using Vector3f = Eigen::Vector3f;
+#else
+// pcl::PointXYZI: 32 bytes, x y z 1.0f | intensity pad pad pad (the reference also keeps cloud/grid indices in
+// data_c[2..3], pointcloud.cpp:294-295)
+struct alignas(16) PointXYZI {
+    float x, y, z, w;
+    float intensity, c1, c2, c3;
+};
+// pcl::PointXYZINormal: 48 bytes
+struct alignas(16) PointXYZINormal {
+    float x, y, z, w;
+    float normal_x, normal_y, normal_z, nw;
+    float intensity, curvature, c2, c3;
+};
+// pcl::Normal: 32 bytes, normal[3] data_n[3] | curvature pad pad pad
+struct alignas(16) Normal {
+    float normal_x, normal_y, normal_z, data_n3;
+    float curvature, c1, c2, c3;
+};
+// Eigen::Vector3f: 12 bytes, not aligned (featureeval.cpp:1176 relies on the 12-byte stride)
+struct Vector3f {
+    float v[3];
+    float &operator[](int i) { return v[i]; }
+    const float &operator[](int i) const { return v[i]; }
+};
+#endif
+static_assert(sizeof(PointXYZI) == 32, "pcl::PointXYZI layout");
+static_assert(sizeof(PointXYZINormal) == 48, "pcl::PointXYZINormal layout");
+static_assert(sizeof(Normal) == 32, "pcl::Normal layout");
+static_assert(sizeof(Vector3f) == 12, "Eigen::Vector3f layout");
+
+// One GPU context per thread of use (the estimateNormals worker thread of the reference owns its own).
+class Session {
+ public:
+    explicit Session(int device = 0) {
+        const int rc = ccg_create(&ctx_, device);
+        if (rc != CCG_OK) {
+            err_ = rc == CCG_ERR_CUDA ? "ccg_create: no usable CUDA device (libccgpu has no CPU path)" : "ccg_create: invalid device id";
+            ctx_ = nullptr;
+        }
+    }
+    ~Session() {
+        if (ctx_) ccg_destroy(ctx_);
+    }
+    Session(const Session &) = delete;
+    Session &operator=(const Session &) = delete;
+    bool ok() const { return ctx_ != nullptr; }
+    ccg_ctx *ctx() const { return ctx_; }
+    const std::string &lastError() const { return err_; }
+    // PointCloud::deleting_ (normalestimation.cpp:305-306): polled between stages
+    void setCancelFlag(const volatile int *flag) {
+        if (ctx_) ccg_set_cancel_flag(ctx_, flag);
+    }
+    // KdTreeFLANN::setInputCloud / octree build equivalent; any point type whose first three floats are x, y, z
+    template <class PointT>
+    bool setInputCloud(const PointT *points, size_t n) {
+        return check(ccg_set_cloud(ctx_, points, n, sizeof(PointT)));
+    }
+    bool check(int rc) {
+        if (rc == CCG_OK) return true;
+        err_ = ctx_ ? ccg_last_error(ctx_) : "no GPU context";
+        return false;
+    }
+
+ private:
+    ccg_ctx *ctx_ = nullptr;
+    std::string err_;
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// getPCA — src/utilities/cv.h:76-116.  Same template, same arguments, same result: one Vector3f of eigenvalues
+// (descending) per point, (0,0,1) for neighbourhoods below 3 points.  `cloud` is anything with data()/size()
+// of PointT (pcl::PointCloud<PointT>::points is a std::vector<PointT>), so the reference call sites
+// `getPCA(cloud.get(), radius, max_nn)` keep compiling with a one-line overload.
+// The reference's `continue` on "too many" (cv.h:100-103) can never trigger with a capped search and is dropped.
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT>
+std::shared_ptr<std::vector<Vector3f>> getPCA(Session &s, const PointT *points, size_t n, double radius, unsigned max_nn = 0,
+                                               int cov_norm = CCG_COV_NM1) {
+    auto eigen_vals = std::make_shared<std::vector<Vector3f>>(n);
+    if (!s.ok() || !s.setInputCloud(points, n)) return std::make_shared<std::vector<Vector3f>>();
+    if (n == 0) return eigen_vals;
+    if (!s.check(ccg_pca_radius(s.ctx(), radius, (int)max_nn, cov_norm, /*normalise_hist=*/0, nullptr,
+                                reinterpret_cast<float *>(eigen_vals->data()), nullptr, nullptr)))
+        return std::make_shared<std::vector<Vector3f>>();
+    return eigen_vals;
+}
+template <class Cloud>
+auto getPCA(Session &s, const Cloud *cloud, double radius, unsigned max_nn = 0)
+    -> decltype(getPCA(s, cloud->data(), cloud->size(), radius, max_nn)) {
+    return getPCA(s, cloud->data(), cloud->size(), radius, max_nn);
+}
+
+// getHist — src/utilities/cv.cpp:249-308: as getPCA, eigenvalue vector L2-normalised (cv.cpp:293).
+template <class PointT>
+std::shared_ptr<std::vector<Vector3f>> getHist(Session &s, const PointT *points, size_t n, double radius, unsigned max_nn = 0,
+                                                int cov_norm = CCG_COV_NM1) {
+    auto eigen_vals = std::make_shared<std::vector<Vector3f>>(n);
+    if (!s.ok() || !s.setInputCloud(points, n)) return std::make_shared<std::vector<Vector3f>>();
+    if (n == 0) return eigen_vals;
+    if (!s.check(ccg_pca_radius(s.ctx(), radius, (int)max_nn, cov_norm, /*normalise_hist=*/1, nullptr,
+                                reinterpret_cast<float *>(eigen_vals->data()), nullptr, nullptr)))
+        return std::make_shared<std::vector<Vector3f>>();
+    return eigen_vals;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// NormalEstimator::estimateNormals — normalestimation.cpp:268-470.  Inputs are what the reference reads from
+// PointCloud: points, cloudToGridMap() (pointcloud.cpp:389-391), scan_width()/scan_height().  Result: one
+// pcl::Normal per point, curvature 0, data_n[3] = 1 for fan normals, NaN where nothing could be estimated.
+// Returns an empty vector when cancelled (the reference returns nullptr when cloud->deleting_, :305-306).
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT>
+std::vector<Normal> estimateNormals(Session &s, const PointT *points, size_t n, const std::vector<int> &cloud_to_grid_map,
+                                    int scan_width, int scan_height, bool knn_fallback = true) {
+    std::vector<Normal> normals;
+    if (!s.ok() || cloud_to_grid_map.size() != n || !s.setInputCloud(points, n)) return normals;
+    std::vector<float> n4(n * 4);
+    int32_t missing = 0;
+    static_assert(sizeof(int) == sizeof(int32_t), "int is 32-bit");
+    if (!s.check(ccg_grid_normals(s.ctx(), reinterpret_cast<const int32_t *>(cloud_to_grid_map.data()), scan_width, scan_height,
+                                  knn_fallback ? 1 : 0, n4.data(), &missing)))
+        return normals;
+    normals.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        Normal &o = normals[i];
+        std::memset(&o, 0, sizeof(Normal));
+        o.normal_x = n4[4 * i]; o.normal_y = n4[4 * i + 1]; o.normal_z = n4[4 * i + 2];
+#ifdef CCGPU_WITH_PCL
+        o.data_n[3] = n4[4 * i + 3];
+#else
+        o.data_n3 = n4[4 * i + 3];
+#endif
+    }
+    return normals;
+}
+
+// North-star operator a12 (PCL NormalEstimation definition): kNN(k) + PCA normal and curvature, optionally
+// flipped towards the sensor origin (PointCloud::sensor_origin_).
+template <class PointT>
+std::vector<Normal> knnNormals(Session &s, const PointT *points, size_t n, int k, const float *sensor_origin3 = nullptr) {
+    std::vector<Normal> normals;
+    if (!s.ok() || !s.setInputCloud(points, n)) return normals;
+    std::vector<float> n4(n * 4);
+    if (!s.check(ccg_pca_knn(s.ctx(), k, CCG_COV_N, sensor_origin3, nullptr, n4.data()))) return normals;
+    normals.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        Normal &o = normals[i];
+        std::memset(&o, 0, sizeof(Normal));
+        o.normal_x = n4[4 * i]; o.normal_y = n4[4 * i + 1]; o.normal_z = n4[4 * i + 2];
+        o.curvature = n4[4 * i + 3];
+    }
+    return normals;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// OutlierFilter::filter — outlierfilter.cpp:120-179.  radius_cm and min_neighbours are the plugin's spin-box
+// values (defaults 100 and 10, :46-47); the search radius is radius_cm/100 metres (:169).  Returns the index
+// list the plugin pushes as `new Select(cloud, indices, ...)` (:177), ascending.
+// ---------------------------------------------------------------------------------------------------------
+inline std::shared_ptr<std::vector<int>> mask_to_indices(const std::vector<uint8_t> &mask) {
+    auto indices = std::make_shared<std::vector<int>>();
+    for (size_t i = 0; i < mask.size(); ++i)
+        if (mask[i]) indices->push_back((int)i);
+    return indices;
+}
+template <class PointT>
+std::shared_ptr<std::vector<int>> outlierFilter(Session &s, const PointT *points, size_t n, double radius_cm = 100.0,
+                                                int min_neighbours = 10, bool octree_prefilter = true) {
+    if (!s.ok() || !s.setInputCloud(points, n)) return std::make_shared<std::vector<int>>();
+    std::vector<uint8_t> mask(n);
+    if (!s.check(ccg_radius_count_mask(s.ctx(), radius_cm / 100.0, min_neighbours, octree_prefilter ? 1 : 0, mask.data())))
+        return std::make_shared<std::vector<int>>();
+    return mask_to_indices(mask);
+}
+// Statistical outlier filter (north-star row a11, PCL StatisticalOutlierRemoval definition).
+template <class PointT>
+std::shared_ptr<std::vector<int>> statisticalOutliers(Session &s, const PointT *points, size_t n, int mean_k, double stddev_mul) {
+    if (!s.ok() || !s.setInputCloud(points, n)) return std::make_shared<std::vector<int>>();
+    std::vector<uint8_t> mask(n);
+    if (!s.check(ccg_sor_mask(s.ctx(), mean_k, stddev_mul, mask.data(), nullptr))) return std::make_shared<std::vector<int>>();
+    return mask_to_indices(mask);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Eigen features — Markov::mkFeatureVector's block markov.cpp:449-475 (7 values per point, as written there) and
+// FeatureEval::pca_eigen_value_ratio (featureeval.cpp:1104-1137) / eigen_plane_consine_similarity (:1201-1220).
+// ---------------------------------------------------------------------------------------------------------
+inline std::vector<float> eigenFeatures(Session &s, const std::vector<Vector3f> &pca, bool as_written = true) {
+    std::vector<float> out(pca.size() * 7);
+    if (!s.ok() || !s.check(ccg_features(s.ctx(), reinterpret_cast<const float *>(pca.data()), pca.size(), as_written ? 0 : 1, out.data())))
+        out.clear();
+    return out;
+}
+inline std::vector<float> pcaEigenValueRatio(Session &s, const std::vector<Vector3f> &pca) {
+    std::vector<float> out(pca.size());
+    if (!s.ok() || !s.check(ccg_eigen_scalar(s.ctx(), reinterpret_cast<const float *>(pca.data()), pca.size(), 0, out.data()))) out.clear();
+    return out;
+}
+inline std::vector<float> eigenPlaneCosineSimilarity(Session &s, const std::vector<Vector3f> &pca) {
+    std::vector<float> out(pca.size());
+    if (!s.ok() || !s.check(ccg_eigen_scalar(s.ctx(), reinterpret_cast<const float *>(pca.data()), pca.size(), 1, out.data()))) out.clear();
+    return out;
+}
+
+}  // namespace ccgpu

@@ -1,0 +1,278 @@
+// test_adapters.cpp — exercises adapters/cloudclean_gpu.hpp (the reference-named C++ host layer) on cuda:0 and
+// checks every adapter against brute-force CPU restatements written in this file (contract arithmetic,
+// SURVEY.md §8c).  Built by `make adapters`, run by tests/test_gpu_adapters.py (-m gpu).  Exit code 0 = all green.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <limits>
+#include <numeric>
+
+#include "cloudclean_gpu.hpp"
+
+using namespace ccgpu;
+
+static int g_fail = 0;
+#define CHECK(cond, ...)                                  \
+    do {                                                  \
+        if (!(cond)) {                                    \
+            ++g_fail;                                     \
+            std::printf("FAIL %s:%d: ", __FILE__, __LINE__); \
+            std::printf(__VA_ARGS__);                     \
+            std::printf("\n");                            \
+        }                                                 \
+    } while (0)
+
+static uint32_t g_rng = 12345u;
+static float urand() {  // LCG, [0,1)
+    g_rng = g_rng * 1664525u + 1013904223u;
+    return (float)(g_rng >> 8) * (1.0f / 16777216.0f);
+}
+
+// contract distance: ((dx*dx + dy*dy) + dz*dz) in fp32, no fma (this file is compiled with -ffp-contract=off)
+static float d2f(const PointXYZI &a, const PointXYZI &b) {
+    volatile float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
+    volatile float xx = dx * dx, yy = dy * dy, zz = dz * dz;
+    volatile float s = xx + yy;
+    return s + zz;
+}
+
+// fp64 cyclic Jacobi of a symmetric 3x3 (a = xx xy xz yy yz zz); eigenvalues descending, v2 = eigenvector of the smallest
+static void eig3d(const double a[6], double ev[3], double vmin[3]) {
+    double A[3][3] = {{a[0], a[1], a[2]}, {a[1], a[3], a[4]}, {a[2], a[4], a[5]}};
+    double V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (int sweep = 0; sweep < 60; ++sweep) {
+        double off = std::fabs(A[0][1]) + std::fabs(A[0][2]) + std::fabs(A[1][2]);
+        if (off < 1e-300) break;
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                if (A[p][q] == 0.0) continue;
+                double th = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+                double t = (th >= 0 ? 1.0 : -1.0) / (std::fabs(th) + std::sqrt(th * th + 1.0));
+                double c = 1.0 / std::sqrt(t * t + 1.0), s = t * c;
+                for (int r = 0; r < 3; ++r) {
+                    double arp = A[r][p], arq = A[r][q];
+                    A[r][p] = c * arp - s * arq; A[r][q] = s * arp + c * arq;
+                }
+                for (int r = 0; r < 3; ++r) {
+                    double apr = A[p][r], aqr = A[q][r];
+                    A[p][r] = c * apr - s * aqr; A[q][r] = s * apr + c * aqr;
+                }
+                for (int r = 0; r < 3; ++r) {
+                    double vrp = V[r][p], vrq = V[r][q];
+                    V[r][p] = c * vrp - s * vrq; V[r][q] = s * vrp + c * vrq;
+                }
+            }
+    }
+    int o[3] = {0, 1, 2};
+    std::sort(o, o + 3, [&](int i, int j) { return A[i][i] > A[j][j]; });
+    for (int i = 0; i < 3; ++i) ev[i] = A[o[i]][o[i]];
+    for (int r = 0; r < 3; ++r) vmin[r] = V[r][o[2]];
+}
+
+// PCA of a neighbour list in fp64: eigenvalues (desc) of S/(n-1) or S/n, eigenvector of the smallest
+static void pca_ref(const std::vector<PointXYZI> &pts, const std::vector<int> &nb, int cov_norm, double ev[3], double vmin[3]) {
+    double mu[3] = {0, 0, 0};
+    for (int j : nb) { mu[0] += pts[j].x; mu[1] += pts[j].y; mu[2] += pts[j].z; }
+    for (double &m : mu) m /= (double)nb.size();
+    double a[6] = {0, 0, 0, 0, 0, 0};
+    for (int j : nb) {
+        double x = pts[j].x - mu[0], y = pts[j].y - mu[1], z = pts[j].z - mu[2];
+        a[0] += x * x; a[1] += x * y; a[2] += x * z; a[3] += y * y; a[4] += y * z; a[5] += z * z;
+    }
+    double div = cov_norm == CCG_COV_NM1 ? (double)nb.size() - 1.0 : (cov_norm == CCG_COV_N ? (double)nb.size() : 1.0);
+    for (double &v : a) v /= div;
+    eig3d(a, ev, vmin);
+}
+
+// neighbours of i ordered by (d2, index)
+static std::vector<std::pair<float, int>> sorted_neighbours(const std::vector<PointXYZI> &pts, int i) {
+    std::vector<std::pair<float, int>> v(pts.size());
+    for (size_t j = 0; j < pts.size(); ++j) v[j] = {d2f(pts[i], pts[j]), (int)j};
+    std::sort(v.begin(), v.end());
+    return v;
+}
+
+int main() {
+    // organised patch: W columns x H rows, a floor with a step and noise, 5 % dropouts, a few far isolated points
+    const int W = 72, H = 56;
+    std::vector<PointXYZI> pts;
+    std::vector<int> c2g;
+    for (int g = 0; g < W * H; ++g) {
+        const int col = g / H, row = g % H;
+        if (urand() < 0.05f) continue;
+        PointXYZI p{};
+        p.x = 0.05f * col + 0.004f * (urand() - 0.5f);
+        p.y = 0.05f * row + 0.004f * (urand() - 0.5f);
+        p.z = (col > W / 2 ? 0.3f : 0.0f) + 0.002f * (urand() - 0.5f);
+        p.w = 1.0f; p.intensity = urand();
+        if (urand() < 0.004f) p.z += 2.0f + urand();      // isolated outliers above the floor
+        pts.push_back(p); c2g.push_back(g);
+    }
+    const size_t n = pts.size();
+    std::printf("adapters test: n=%zu\n", n);
+
+    Session s(0);
+    CHECK(s.ok(), "Session: %s", s.lastError().c_str());
+    if (!s.ok()) return 2;
+
+    std::vector<std::vector<std::pair<float, int>>> nbrs(n);
+    for (size_t i = 0; i < n; ++i) nbrs[i] = sorted_neighbours(pts, (int)i);
+
+    // ---- getPCA / getHist (cv.h:76-116, cv.cpp:249-308): strict radius, cap = max_nn nearest, <3 -> (0,0,1) ----
+    {
+        const double radius = 0.12; const unsigned max_nn = 20;
+        const float r2 = (float)(radius * radius);
+        auto pca = getPCA(s, &pts, radius, max_nn);                  // reference-style call: cloud pointer
+        auto pca2 = getPCA(s, pts.data(), n, radius, max_nn);        // raw pointer + size
+        auto hist = getHist(s, pts.data(), n, radius, max_nn);
+        CHECK(pca->size() == n && pca2->size() == n && hist->size() == n, "getPCA/getHist sizes (%s)", s.lastError().c_str());
+        double worst = 0, worst_h = 0; int markers = 0;
+        for (size_t i = 0; i < n && pca->size() == n; ++i) {
+            std::vector<int> nb;
+            for (auto &c : nbrs[i]) { if (!(c.first < r2) || nb.size() == max_nn) break; nb.push_back(c.second); }
+            const Vector3f &e = (*pca)[i];
+            CHECK(std::memcmp(&e, &(*pca2)[i], 12) == 0, "getPCA overloads differ at %zu", i);
+            if (nb.size() < 3) {
+                ++markers;
+                CHECK(e[0] == 0.f && e[1] == 0.f && e[2] == 1.f, "marker at %zu: %g %g %g", i, e[0], e[1], e[2]);
+                continue;
+            }
+            double ev[3], vm[3];
+            pca_ref(pts, nb, CCG_COV_NM1, ev, vm);
+            double nrm = std::sqrt(ev[0] * ev[0] + ev[1] * ev[1] + ev[2] * ev[2]);
+            for (int d = 0; d < 3; ++d) {
+                worst = std::max(worst, std::fabs(e[d] - ev[d]) / ev[0]);
+                worst_h = std::max(worst_h, std::fabs((*hist)[i][d] - ev[d] / nrm));
+            }
+        }
+        std::printf("getPCA: max |d lambda|/lambda0 = %.3g, getHist max abs err = %.3g, markers = %d\n", worst, worst_h, markers);
+        CHECK(worst <= 1e-4, "getPCA eigenvalues off by %g", worst);
+        CHECK(worst_h <= 1e-4, "getHist off by %g", worst_h);
+        CHECK(markers > 0, "the test cloud should hold isolated points");
+
+        auto f7 = eigenFeatures(s, *pca, true);
+        auto ratio = pcaEigenValueRatio(s, *pca);
+        CHECK(f7.size() == 7 * n && ratio.size() == n, "feature sizes");
+        double wf = 0;
+        for (size_t i = 0; i < n && f7.size() == 7 * n; ++i) {
+            const float l0 = (*pca)[i][0], l1 = (*pca)[i][1], l2 = (*pca)[i][2];
+            if (!(l0 > 0.f)) continue;
+            const float ref[4] = {(l0 - l2) / l0, (l1 - l2) / l0, l2 / l0, (l0 - l1) / l0};   // markov.cpp:451-463
+            for (int d = 0; d < 4; ++d) wf = std::max(wf, (double)std::fabs(f7[7 * i + d] - ref[d]));
+            if (!(l0 == 0.f && l1 == 0.f && l2 == 1.f)) {
+                const float rr = l0 > l2 ? l1 / l0 : 1.f;                                      // featureeval.cpp:1107-1135
+                wf = std::max(wf, (double)std::fabs(ratio[i] - rr));
+            }
+        }
+        CHECK(wf <= 1e-6, "eigen features off by %g", wf);
+    }
+
+    // ---- OutlierFilter::filter (outlierfilter.cpp:157-173): inclusive radius count incl. self < min_neighbours ----
+    {
+        const double radius_cm = 20.0; const int min_nb = 10;
+        const double r2 = (radius_cm / 100.0) * (radius_cm / 100.0);
+        auto got = outlierFilter(s, pts.data(), n, radius_cm, min_nb, /*octree_prefilter=*/false);
+        std::vector<int> want;
+        for (size_t i = 0; i < n; ++i) {
+            int c = 0;
+            for (auto &p : nbrs[i]) { if (!((double)p.first <= r2)) break; ++c; }
+            if (c < min_nb) want.push_back((int)i);
+        }
+        std::printf("outlierFilter: %zu flagged (expected %zu)\n", got->size(), want.size());
+        CHECK(*got == want, "outlierFilter index list differs");
+        CHECK(!want.empty(), "the test cloud should hold radius outliers");
+        auto pre = outlierFilter(s, pts.data(), n, radius_cm, min_nb, true);
+        CHECK(std::includes(want.begin(), want.end(), pre->begin(), pre->end()), "prefiltered list must be a subset");
+    }
+
+    // ---- statistical outliers: mean distance to mean_k neighbours (self dropped), mu + alpha*sigma in fp64 ----
+    {
+        const int mean_k = 12; const double alpha = 1.0;
+        std::vector<float> md(n);
+        double sum = 0, sq = 0;
+        for (size_t i = 0; i < n; ++i) {
+            double acc = 0;
+            for (int j = 1; j <= mean_k; ++j) acc += (double)std::sqrt(nbrs[i][j].first);
+            md[i] = (float)(acc / mean_k);
+            sum += md[i]; sq += (double)md[i] * (double)md[i];
+        }
+        const double mean = sum / (double)n, var = (sq - sum * sum / (double)n) / ((double)n - 1.0);
+        const double thr = mean + alpha * std::sqrt(var);
+        std::vector<int> want;
+        for (size_t i = 0; i < n; ++i) if ((double)md[i] > thr) want.push_back((int)i);
+        auto got = statisticalOutliers(s, pts.data(), n, mean_k, alpha);
+        std::printf("statisticalOutliers: %zu flagged (expected %zu)\n", got->size(), want.size());
+        CHECK(*got == want, "statistical outlier list differs");
+    }
+
+    // ---- knnNormals: kNN(k)+PCA normal = eigenvector of the smallest eigenvalue (S/n), |cos| >= 1-1e-5 ----
+    {
+        const int k = 16;
+        const float origin[3] = {1.8f, 1.4f, 5.0f};
+        auto nrm = knnNormals(s, pts.data(), n, k, origin);
+        CHECK(nrm.size() == n, "knnNormals size (%s)", s.lastError().c_str());
+        double worst = 0, worst_c = 0; int checked = 0, flipped_wrong = 0;
+        for (size_t i = 0; i < n && nrm.size() == n; ++i) {
+            std::vector<int> nb;
+            for (int j = 0; j < k; ++j) nb.push_back(nbrs[i][j].second);
+            double ev[3], vm[3];
+            pca_ref(pts, nb, CCG_COV_N, ev, vm);
+            if (ev[1] - ev[2] <= 1e-3 * ev[0]) continue;          // no unique normal
+            ++checked;
+            const Normal &o = nrm[i];
+            const double c = std::fabs(o.normal_x * vm[0] + o.normal_y * vm[1] + o.normal_z * vm[2]);
+            worst = std::max(worst, 1.0 - c);
+            worst_c = std::max(worst_c, std::fabs(o.curvature - ev[2] / (ev[0] + ev[1] + ev[2])));
+            const double tov = (origin[0] - pts[i].x) * o.normal_x + (origin[1] - pts[i].y) * o.normal_y + (origin[2] - pts[i].z) * o.normal_z;
+            if (tov < 0) ++flipped_wrong;
+        }
+        std::printf("knnNormals: checked %d, max 1-|cos| = %.3g, max curvature err = %.3g\n", checked, worst, worst_c);
+        CHECK(checked > (int)n / 2, "too few well-defined normals (%d)", checked);
+        CHECK(worst <= 1e-5, "normals off: 1-|cos| = %g", worst);
+        CHECK(worst_c <= 1e-4, "curvature off by %g", worst_c);
+        CHECK(flipped_wrong == 0, "%d normals point away from the viewpoint", flipped_wrong);
+    }
+
+    // ---- estimateNormals (normalestimation.cpp:268-470): organised fan normals + kNN(50) fallback ----
+    {
+        auto nrm = estimateNormals(s, pts.data(), n, c2g, W, H, true);
+        CHECK(nrm.size() == n, "estimateNormals size (%s)", s.lastError().c_str());
+        int nan = 0, unit = 0, upright = 0;
+        for (size_t i = 0; i < nrm.size(); ++i) {
+            const Normal &o = nrm[i];
+            if (std::isnan(o.normal_x)) { ++nan; continue; }
+            const double len = std::sqrt((double)o.normal_x * o.normal_x + (double)o.normal_y * o.normal_y + (double)o.normal_z * o.normal_z);
+            if (std::fabs(len - 1.0) < 1e-4) ++unit;
+            if (std::fabs(o.normal_z) > 0.9) ++upright;
+            CHECK(o.curvature == 0.f, "curvature must stay 0 (normalestimation.cpp leaves it untouched)");
+        }
+        std::printf("estimateNormals: %d NaN, %d unit, %d upright of %zu\n", nan, unit, upright, n);
+        CHECK(nan == 0, "%d normals left NaN after the fallback", nan);
+        CHECK(unit > (int)(0.9 * n), "fan normals must be unit length (%d of %zu)", unit, n);
+        CHECK(upright > (int)(0.8 * n), "a floor scan should have mostly vertical normals (%d of %zu)", upright, n);
+        std::vector<int> bad_map(n, 0);
+        bad_map.pop_back();
+        CHECK(estimateNormals(s, pts.data(), n, bad_map, W, H).empty(), "a short cloud_to_grid map must be refused");
+    }
+
+    // ---- error behaviour: empty result + message, no exception, session stays usable ----
+    {
+        std::vector<PointXYZI> bad(pts.begin(), pts.begin() + 100);
+        bad[17].y = std::numeric_limits<float>::quiet_NaN();
+        auto r = getPCA(s, bad.data(), bad.size(), 0.1, 20);
+        CHECK(r->empty() && !s.lastError().empty(), "NaN cloud must be refused with a message");
+        std::printf("refused NaN cloud: %s\n", s.lastError().c_str());
+        auto ok = getPCA(s, pts.data(), (size_t)64, 0.1, 20);
+        CHECK(ok->size() == 64, "session must stay usable after an error");
+        std::vector<PointXYZI> none;
+        CHECK(getPCA(s, none.data(), (size_t)0, 0.1, 20)->empty(), "empty cloud -> empty result");
+        volatile int cancel = 1;
+        s.setCancelFlag(&cancel);
+        CHECK(estimateNormals(s, pts.data(), n, c2g, W, H).empty(), "a raised deleting_ flag must cancel estimateNormals");
+        s.setCancelFlag(nullptr);
+    }
+
+    std::printf(g_fail ? "adapters: %d check(s) FAILED\n" : "adapters: all checks passed\n", g_fail);
+    return g_fail ? 1 : 0;
+}
