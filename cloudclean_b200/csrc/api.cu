@@ -111,6 +111,87 @@ __global__ void __launch_bounds__(256) k_voxel_candidates(const unsigned long lo
     cand[vals[i]] = run < min_neighbours ? 1 : 0;
 }
 
+// ---- output pipelining ---------------------------------------------------------------------------------
+// With HOST output pointers the D2H of the per-point rows (56 B/point for eig3+normal4+feat7) costs as much as
+// the query itself.  Rows are in ORIGINAL order while the kernel works in Morton tiles, so a prefix of rows is
+// complete only when every tile holding one of them has run.  Ordering the tiles by their smallest original
+// index makes that a prefix property: after the first T tiles of that order every row below the (T+1)-th
+// tile's smallest index is final.  The tile list is cut into chunks; the copy stream ships rows
+// [bound[c], bound[c+1]) while chunk c+1 is being computed.  For a scan in file order (column-major grid) the
+// row front follows the tile front closely; for a shuffled cloud the bounds stay near 0 and the last copy
+// moves everything — still correct, just not overlapped.
+__global__ void __launch_bounds__(256) k_tile_minidx(const float4 *__restrict__ sorted, int nleaf, unsigned *__restrict__ key,
+                                                     int32_t *__restrict__ tile) {
+    const int leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (leaf >= nleaf) return;
+    const int w = __float_as_int(sorted[(size_t)leaf * kLeaf + lane].w);       // pads carry INT_MAX
+    const int m = __reduce_min_sync(kFull, w);
+    if (lane == 0) { key[leaf] = (unsigned)m; tile[leaf] = leaf; }
+}
+
+struct PipeOut { OutBuf *o; size_t row_bytes; };
+
+static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, int chunks) {
+    const int nleaf = ctx->nleaf;
+    const size_t n = ctx->n;
+    cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
+    if (chunks > 16) chunks = 16;
+    for (int c = 0; c <= 16; ++c)
+        if (!ctx->ev_chunk[c]) CCG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chunk[c], cudaEventDisableTiming));
+    // tiles ordered by their smallest original index
+    const size_t stride = ((size_t)nleaf + 63) & ~(size_t)63;
+    CCG_CUDA(ctx, ctx->tmp[3].reserve(stride * 16));
+    unsigned *k0 = ctx->tmp[3].as<unsigned>(), *k1 = k0 + stride;
+    int32_t *v0 = (int32_t *)(k1 + stride), *v1 = v0 + stride;
+    k_tile_minidx<<<(nleaf + 7) / 8, 256, 0, st>>>(ctx->sorted.as<float4>(), nleaf, k0, v0);
+    int bits = 1;
+    while (bits < 32 && (n >> bits)) ++bits;
+    cub::DoubleBuffer<unsigned> dk(k0, k1);
+    cub::DoubleBuffer<int32_t> dv(v0, v1);
+    size_t tmp_bytes = 0;
+    CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, nleaf, 0, bits, st));
+    CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+    CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, nleaf, 0, bits, st));
+    ctx->stats.launches += 1 + (bits + 7) / 8 + 1;
+    // chunk c = slots [slot[c], slot[c+1]); rows below bound[c+1] are final once it has run
+    int per = ((nleaf + chunks - 1) / chunks + 1) & ~1;
+    if (per < 2) per = 2;
+    int slot[18]; size_t bound[18];
+    int nch = 0;
+    slot[0] = 0;
+    while (slot[nch] < nleaf) { slot[nch + 1] = slot[nch] + per < nleaf ? slot[nch] + per : nleaf; ++nch; }
+    CCG_CUDA(ctx, ctx->hpin[1].reserve(64 * sizeof(unsigned)));
+    unsigned *hb = ctx->hpin[1].as<unsigned>();
+    for (int c = 1; c < nch; ++c)
+        CCG_CUDA(ctx, cudaMemcpyAsync(hb + c, dk.Current() + slot[c], sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CCG_CUDA(ctx, cudaStreamSynchronize(st));
+    bound[0] = 0;
+    for (int c = 1; c < nch; ++c) bound[c] = hb[c] < n ? hb[c] : n;
+    bound[nch] = n;
+    a.tile_order = dv.Current();
+    int launches = ctx->stats.launches;
+    for (int c = 0; c < nch; ++c) {
+        if (ctx->cancel && *ctx->cancel) return set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller");
+        a.begin = (size_t)slot[c] * kLeaf;
+        a.end = (size_t)slot[c + 1] * kLeaf;
+        ctx->stats.launches = 0;
+        CCG_TRY(launch_tile_query(ctx, a));
+        launches += ctx->stats.launches;
+        CCG_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[c], st));
+        CCG_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[c], 0));
+        const size_t r0 = bound[c], r1 = bound[c + 1];
+        if (r1 > r0)
+            for (int i = 0; i < nouts; ++i)
+                CCG_CUDA(ctx, cudaMemcpyAsync((char *)outs[i].o->user + r0 * outs[i].row_bytes, (char *)outs[i].o->d + r0 * outs[i].row_bytes,
+                                              (r1 - r0) * outs[i].row_bytes, cudaMemcpyDeviceToHost, cs));
+    }
+    ctx->stats.launches = launches;
+    for (int i = 0; i < nouts; ++i) outs[i].o->staged = false;          // already shipped: close() has nothing left to do
+    CCG_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[16], cs));
+    CCG_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_chunk[16], 0));
+    return CCG_OK;
+}
+
 static QueryArgs base_args(ccg_ctx *ctx) {
     QueryArgs a{};
     a.rb = INFINITY; a.begin = 0; a.end = ctx->n; a.sorted_rows = 0;
@@ -147,6 +228,10 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
     const char *sp = getenv("CCG_SPLIT_SPARSE");
     ctx->split_sparse = (sp && sp[0] == '0') ? 0 : 1;
+    const char *pc = getenv("CCG_PIPELINE_CHUNKS");
+    if (pc) ctx->pipeline_chunks = atoi(pc);
+    const char *pm = getenv("CCG_PIPELINE_MIN_POINTS");
+    if (pm) ctx->pipeline_min_points = atoi(pm);
     *out = ctx;
     return CCG_OK;
 }
@@ -160,6 +245,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release();
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < 17; ++i) if (ctx->ev_chunk[i]) cudaEventDestroy(ctx->ev_chunk[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -265,7 +351,16 @@ static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise
         if (vp) for (int i = 0; i < 3; ++i) a.vp[i] = vp[i];
         a.eig3 = oe.dev<float>(); a.normal4 = on.dev<float>(); a.count = oc.dev<int32_t>();
         a.feat7 = of.dev<float>(); a.formula_set = formula_set;
-        CCG_TRY(launch_tile_query(ctx, a));
+        PipeOut po[4];
+        int npo = 0;
+        if (oe.staged) po[npo++] = PipeOut{&oe, 12};
+        if (on.staged) po[npo++] = PipeOut{&on, 16};
+        if (oc.staged) po[npo++] = PipeOut{&oc, 4};
+        if (of.staged) po[npo++] = PipeOut{&of, 28};
+        if (npo > 0 && !sorted_rows && ctx->pipeline_chunks > 1 && !ctx->collect_stats && ctx->n >= (size_t)ctx->pipeline_min_points)
+            CCG_TRY(pipelined_query(ctx, a, po, npo, ctx->pipeline_chunks));
+        else
+            CCG_TRY(launch_tile_query(ctx, a));
     } else {
         StreamArgs s{};
         s.mode = 1; s.rb = rb; s.count_cap = 0; s.begin = begin; s.end = end; s.sorted_rows = sorted_rows;

@@ -65,6 +65,7 @@ struct ccg_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev[8] = {};
+    cudaEvent_t ev_chunk[17] = {};       // output pipelining (created on first use)
     const volatile int *cancel = nullptr;
 
     bool has_cloud = false;
@@ -92,6 +93,8 @@ struct ccg_ctx {
 
     ccg_stats stats = {};
     int collect_stats = 0;
+    int pipeline_chunks = 8;         // host-output pipelining of the PCA query (CCG_PIPELINE_CHUNKS; <= 1 disables)
+    int pipeline_min_points = 1 << 18;
     int split_sparse = 1;    // move isolated points to the end of the order (CCG_SPLIT_SPARSE=0 disables)
     char err[512] = "";
 
@@ -146,6 +149,8 @@ struct QueryArgs {
     float *eig3; float *normal4; float *feat7; int formula_set;
     // MODE_SOR
     int mean_k; float *mean_d;
+    // MODE_PCA / MODE_SOR: optional processing order; begin/end then count 32-query SLOTS of this list (x32), not positions
+    const int32_t *tile_order;
 };
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a);
 

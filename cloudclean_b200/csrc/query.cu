@@ -490,6 +490,7 @@ struct TileParams {
     unsigned long long *stat_scanned;
     int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
     int *slow_count; int32_t *slow_tiles;                          // k_tile_sel: tiles handed to k_tile_sel_stack
+    const int32_t *tile_order;    // k_tile_sel: non-NULL = tile_begin/tile_end index this list of tiles (output pipelining)
 };
 
 template <int K>
@@ -842,8 +843,9 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
     constexpr bool LOG = MODE == MODE_PCA;
     __shared__ WarpScratch3<CAP> s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tile = P.tile_begin + blockIdx.x * 2 + warp;
-    if (tile >= P.tile_end) return;
+    const int slot = P.tile_begin + blockIdx.x * 2 + warp;
+    if (slot >= P.tile_end) return;
+    const int tile = P.tile_order ? P.tile_order[slot] : slot;
     WarpScratch3<CAP> &S = s_ws[warp];
     const size_t pos = (size_t)tile * kLeaf + lane;
     const float4 q = T.pts[pos];
@@ -1018,6 +1020,8 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
     P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
+    P.tile_order = a.tile_order;
+    if (a.tile_order && a.mode == MODE_KNN) return set_error(ctx, CCG_ERR_INVALID, "tile_order is only supported by the selection kernel");
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {
         CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 96, ctx->stream));

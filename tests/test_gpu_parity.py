@@ -347,3 +347,37 @@ def test_errors_and_empty_cloud():
     mask, md = ctx.sor_mask(5, 1.0)
     assert mask.shape == (0,)
     ctx.close()
+
+
+# ---- host-output pipelining (chunked D2H behind the query) ------------------------------------------------
+@pytest.mark.parametrize("shuffle", [False, True])
+@pytest.mark.parametrize("chunks", [2, 5, 16])
+def test_pipelined_host_outputs_are_identical(monkeypatch, shuffle, chunks):
+    """ccg_pca_knn_features / ccg_pca_radius with HOST outputs ship rows in chunks while later tiles are computed
+    (tiles ordered by their smallest original index).  Every row must equal the unpipelined call bit for bit —
+    for a scan in file order (row front follows the tile front) and for a shuffled cloud (all rows in the last copy)."""
+    scan = synth.make_scan_np(160, 120, scene="room", seed=21)
+    pts = np.ascontiguousarray(scan["points"])
+    if shuffle:
+        pts = np.ascontiguousarray(pts[np.random.default_rng(5).permutation(pts.shape[0])])
+    n = pts.shape[0]
+
+    def run():
+        with cc.Context(0) as ctx:
+            ctx.set_cloud(pts)
+            eig = np.full((n, 3), -7.0, np.float32); nrm = np.full((n, 4), -7.0, np.float32); feat = np.full((n, 7), -7.0, np.float32)
+            ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat)
+            e2, _, cnt = ctx.pca_radius(0.08, 20, device_out=False)
+            return eig, nrm, feat, e2, cnt
+
+    monkeypatch.setenv("CCG_PIPELINE_CHUNKS", "1")
+    ref = run()
+    monkeypatch.setenv("CCG_PIPELINE_CHUNKS", str(chunks))
+    monkeypatch.setenv("CCG_PIPELINE_MIN_POINTS", "0")
+    got = run()
+    for a, b in zip(ref, got):
+        assert np.array_equal(a, b, equal_nan=True)
+    # and the reference run itself is right
+    T = oracle.Tree(pts)
+    ri, _ = T.knn(20)
+    check_pca(ref[0], ref[1], oracle.pca_lists(pts, ri, cov_norm=1))
