@@ -9,9 +9,10 @@ N = 1 : `value` = points / step time with the scan ALREADY RESIDENT in HBM (devi
         pointers out); `e2e` = the same calls with pinned HOST buffers (H2D of the 32-byte PointXYZI AoS and
         D2H of every output inside the timed region).
 N > 1 : one process per GPU (torchrun).  Rank 0 owns the scan; each step broadcasts it over NCCL, every rank
-        builds the identical Morton order, answers its own contiguous range of the sorted order
-        (ccg_pca_knn_range), and the per-point outputs are all-gathered and un-permuted — strong scaling of a
-        fixed 30 M-point job (north star: replicated cloud, query shards by Morton range).
+        builds the identical Morton order, answers its own contiguous range of the sorted order and stores the
+        per-point rows, in original order, directly into rank 0's output arrays through NVLink peer memory from
+        inside the query kernel (ccg_pca_knn_features_scatter; one 1-element all_reduce as completion barrier) —
+        strong scaling of a fixed 30 M-point job (north star: replicated cloud, query shards by Morton range).
 The scan is 960 MB of input and >1.6 GB of outputs per step, far above the 126 MB L2, so no explicit L2 flush
 is needed between timed iterations (stated in config.l2).
 
@@ -240,13 +241,12 @@ def main():
     nrm = torch.empty((rows, 4), device=dev)
     feat = torch.empty((rows, 7), device=dev)
     if world > 1:
-        g_eig = torch.empty((world * per, 3), device=dev)
-        g_nrm = torch.empty((world * per, 4), device=dev)
-        g_feat = torch.empty((world * per, 7), device=dev)
+        # rank 0's original-order output arrays, mapped as NVLink peer memory on every rank (fused query + scatter)
+        peer = sharding.PeerRows(ctx, n, (3, 4, 7), collector=0)
+        p_eig, p_nrm, p_feat = peer.bufs
+        token = torch.zeros(1, device=dev)
         if rank == 0:
-            o_eig = torch.empty((n, 3), device=dev)
-            o_nrm = torch.empty((n, 4), device=dev)
-            o_feat = torch.empty((n, 7), device=dev)
+            o_eig, o_nrm, o_feat = (b.tensor(dev) for b in peer.bufs)
     launches = [0]
     kernel_ms = []
 
@@ -262,18 +262,13 @@ def main():
             dist.broadcast(pts, 0)
             ctx.set_cloud(pts)
             launches[0] += ctx.stats()["launches_build"]
-            ctx.pca_knn_features_range(K, cc.COV_NM1, 0, begin, end, eig, nrm, feat)
+            # every rank answers its Morton range and stores the rows, in original order, straight into rank 0's
+            # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
+            ctx.pca_knn_features_scatter(K, cc.COV_NM1, 0, begin, end, p_eig, p_nrm, p_feat)
             st = ctx.stats()
             launches[0] += st["launches"]
             kernel_ms.append(st["ms_query"])
-            dist.all_gather_into_tensor(g_eig, eig)
-            dist.all_gather_into_tensor(g_nrm, nrm)
-            dist.all_gather_into_tensor(g_feat, feat)
-            if rank == 0:
-                ctx.unpermute(g_eig, o_eig)
-                ctx.unpermute(g_nrm, o_nrm)
-                ctx.unpermute(g_feat, o_feat)
-                launches[0] += 3
+            dist.all_reduce(token)
 
     # host-buffer variant (e2e): pinned PointXYZI AoS in, pinned outputs out
     if rank == 0:
@@ -361,6 +356,10 @@ def main():
             line["cpu_baseline"] = {"value": cpts.shape[0] / t, "unit": "points/s", "cores": oracle.max_threads(), "kind": "port",
                                     "sample": sample + f"; {t:.1f} s"}
         print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        peer.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

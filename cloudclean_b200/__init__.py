@@ -27,6 +27,7 @@ SYMBOLS = [
     "ccg_set_cloud", "ccg_cloud_size", "ccg_get_order", "ccg_knn", "ccg_radius", "ccg_pca_knn", "ccg_pca_radius",
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
+    "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
 ]
 
 
@@ -84,12 +85,29 @@ def load_library():
     L.ccg_unpermute.argtypes = [vp, vp, sz, vp]
     L.ccg_pca_knn_features.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp]
     L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
+    L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
+    L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
+    L.ccg_dev_free.argtypes = [vp, vp]
+    L.ccg_ipc_export.argtypes = [vp, vp, vp]
+    L.ccg_ipc_open.argtypes = [vp, vp, C.POINTER(vp)]
+    L.ccg_ipc_close.argtypes = [vp, vp]
     _lib = L
     return L
 
 
 def _is_torch(a):
     return a is not None and type(a).__module__.startswith("torch")
+
+
+def _addr(a):
+    """tensor / array / DevBuffer / raw integer device address -> c_void_p"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    if hasattr(a, "addr"):
+        return C.c_void_p(a.addr)
+    return _ptr(a)
 
 
 def _ptr(a):
@@ -220,6 +238,35 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_range(self.h, k, cov_norm, _ptr(vp), formula_set, begin, end, _ptr(eig_sorted),
                                                       _ptr(nrm_sorted), _ptr(feat_sorted)))
+
+    def pca_knn_features_scatter(self, k, cov_norm, formula_set, begin, end, eig, nrm, feat, viewpoint=None):
+        """range query whose rows land in ORIGINAL order in eig/nrm/feat — tensors, DevBuffers or raw device addresses,
+        possibly peer memory of the collecting GPU (fused query + NVLink scatter, include/ccgpu.h)"""
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn_features_scatter(self.h, k, cov_norm, _ptr(vp), formula_set, begin, end, _addr(eig),
+                                                        _addr(nrm), _addr(feat)))
+
+    def dev_alloc(self, nbytes):
+        p = C.c_void_p()
+        self._check(self.L.ccg_dev_alloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def dev_free(self, addr):
+        self._check(self.L.ccg_dev_free(self.h, C.c_void_p(addr)))
+
+    def ipc_export(self, addr):
+        h = (C.c_ubyte * 64)()
+        self._check(self.L.ccg_ipc_export(self.h, C.c_void_p(addr), h))
+        return bytes(h)
+
+    def ipc_open(self, handle):
+        p = C.c_void_p()
+        buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+        self._check(self.L.ccg_ipc_open(self.h, buf, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, addr):
+        self._check(self.L.ccg_ipc_close(self.h, C.c_void_p(addr)))
 
     # ---- a4 / a5 -----------------------------------------------------------------------------------
     def pca_radius(self, r, max_nn=0, cov_norm=COV_NM1, normalise_hist=False, viewpoint=None, want_normals=False,

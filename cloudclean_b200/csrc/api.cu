@@ -392,6 +392,53 @@ int ccg_pca_knn_features_range(ccg_ctx *ctx, int k, int cov_norm, const float *v
                       feat7_sorted, formula_set);
 }
 
+int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
+                                 float *eig3, float *normal4, float *feat7) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    if (begin % kLeaf) return set_error(ctx, CCG_ERR_INVALID, "begin must be a multiple of 32");
+    if (end > ctx->n) end = ctx->n;
+    if ((eig3 && !is_dev(ctx, eig3)) || (normal4 && !is_dev(ctx, normal4)) || (feat7 && !is_dev(ctx, feat7)))
+        return set_error(ctx, CCG_ERR_INVALID, "scatter outputs must be device (own or peer) memory");
+    return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, begin, end, 0, eig3, normal4, nullptr, false, feat7, formula_set);
+}
+
+int ccg_dev_alloc(ccg_ctx *ctx, size_t bytes, void **out) {
+    CCG_TRY(begin_call(ctx, false));
+    if (!out) return set_error(ctx, CCG_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    CCG_CUDA(ctx, cudaMalloc(out, bytes ? bytes : 1));
+    return CCG_OK;
+}
+int ccg_dev_free(ccg_ctx *ctx, void *ptr) {
+    CCG_TRY(begin_call(ctx, false));
+    if (ptr) CCG_CUDA(ctx, cudaFree(ptr));
+    return CCG_OK;
+}
+int ccg_ipc_export(ccg_ctx *ctx, const void *ptr, void *handle64) {
+    CCG_TRY(begin_call(ctx, false));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    if (!ptr || !handle64) return set_error(ctx, CCG_ERR_INVALID, "NULL argument");
+    cudaIpcMemHandle_t h;
+    CCG_CUDA(ctx, cudaIpcGetMemHandle(&h, const_cast<void *>(ptr)));
+    memcpy(handle64, &h, 64);
+    return CCG_OK;
+}
+int ccg_ipc_open(ccg_ctx *ctx, const void *handle64, void **out) {
+    CCG_TRY(begin_call(ctx, false));
+    if (!handle64 || !out) return set_error(ctx, CCG_ERR_INVALID, "NULL argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    *out = nullptr;
+    CCG_CUDA(ctx, cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return CCG_OK;
+}
+int ccg_ipc_close(ccg_ctx *ctx, void *ptr) {
+    CCG_TRY(begin_call(ctx, false));
+    if (ptr) CCG_CUDA(ctx, cudaIpcCloseMemHandle(ptr));
+    return CCG_OK;
+}
+
 int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4) {
     CCG_TRY(begin_call(ctx, true));
     if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);

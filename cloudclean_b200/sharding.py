@@ -52,3 +52,52 @@ def sharded_rows(n, compute_range, width, dtype=torch.float32, device="cpu"):
     if end > begin:
         compute_range(begin, end, local)
     return gather_rows(local, per, world)
+
+
+# ---- fused query + scatter: the collector's output arrays opened as NVLink peer memory on every rank -----------
+class DevBuffer:
+    """A device array at a raw address (own cudaMalloc on the collector, IPC-mapped peer memory elsewhere)."""
+
+    def __init__(self, addr, shape, owner):
+        self.addr, self.shape, self.owner = addr, tuple(shape), owner
+        self.__cuda_array_interface__ = {"shape": self.shape, "typestr": "<f4", "data": (addr, False), "version": 3, "strides": None}
+
+    def tensor(self, device):
+        """torch view (collector only: the memory lives on its GPU)"""
+        return torch.as_tensor(self, device=device)
+
+
+class PeerRows:
+    """Row arrays [n, w] (float32) that live on rank `collector` and are writable from every local rank.
+
+    The collector allocates them through the library (plain cudaMalloc: an IPC handle names an allocation base),
+    exports one 64-byte handle per array, the handles travel through torch.distributed (any backend), and the other
+    ranks map them with ccg_ipc_open.  ccg_pca_knn_features_scatter then stores finished rows straight into the
+    collector's memory over NVLink from inside the query kernel."""
+
+    def __init__(self, ctx, n, widths, collector=0):
+        self.ctx, self.collector = ctx, collector
+        rank = dist.get_rank() if dist.is_initialized() else 0
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        self.is_collector = rank == collector
+        self.bufs = []
+        handles = []
+        if self.is_collector:
+            for w in widths:
+                addr = ctx.dev_alloc(max(1, n * w * 4))
+                self.bufs.append(DevBuffer(addr, (n, w), True))
+                handles.append(ctx.ipc_export(addr) if world > 1 else b"")
+        if world > 1:
+            box = [handles]
+            dist.broadcast_object_list(box, src=collector)
+            if not self.is_collector:
+                for w, h in zip(widths, box[0]):
+                    self.bufs.append(DevBuffer(ctx.ipc_open(h), (n, w), False))
+
+    def close(self):
+        for b in self.bufs:
+            if b.owner:
+                self.ctx.dev_free(b.addr)
+            else:
+                self.ctx.ipc_close(b.addr)
+        self.bufs = []

@@ -164,6 +164,24 @@ int ccg_sor_mean_range(ccg_ctx *ctx, int mean_k, size_t begin, size_t end, float
 /* out[order[i]] = in[i] for rows of row_bytes (multiple of 4) bytes; in/out host or device */
 int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void *rows_original);
 
+/* ---- fused query + scatter over NVLink peer memory (SURVEY.md §8e "collect") -------------------------------
+ * Same range query, but rows are written in ORIGINAL order at row = original index, straight from the query
+ * kernel.  The output pointers may be PEER memory of another GPU on the same NVSwitch domain (a buffer of the
+ * collecting rank opened with ccg_ipc_open): every rank then stores its finished rows directly into the
+ * collector's arrays through NVLink while it computes — no all-gather, no un-permute pass, no staging copy.
+ * Ranks own disjoint rows, so no two GPUs write the same address; the caller orders the collector's reads
+ * after all ranks' calls with one barrier-like collective on the stream (bench.py: a 1-element all_reduce). */
+int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
+                                 float *eig3, float *normal4, float *feat7);
+/* Plain cudaMalloc / cudaFree on the ctx's device (IPC handles need an allocation base, which a caching
+ * allocator's sub-block is not). */
+int ccg_dev_alloc(ccg_ctx *ctx, size_t bytes, void **out);
+int ccg_dev_free(ccg_ctx *ctx, void *ptr);
+/* handle64: 64 bytes (cudaIpcMemHandle_t) to be sent to the other local ranks by any means. */
+int ccg_ipc_export(ccg_ctx *ctx, const void *ptr, void *handle64);
+int ccg_ipc_open(ccg_ctx *ctx, const void *handle64, void **out);     /* enables peer access lazily */
+int ccg_ipc_close(ccg_ctx *ctx, void *ptr);
+
 #ifdef __cplusplus
 }
 #endif
