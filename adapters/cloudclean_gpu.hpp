@@ -12,6 +12,7 @@
 //   getHist(cloud, radius, max_nn)                            src/utilities/cv.cpp:249-308
 //   NormalEstimator::estimateNormals(cloud)                   src/plugins/normalestimation/normalestimation.cpp:268-470
 //   OutlierFilter::filter()  (index list handed to Select)    src/plugins/outlierfilter/outlierfilter.cpp:120-179
+//   octreeDownsample<PointT>(cloud*, resolution, sub_idxs)    src/utilities/utils.h:16-62
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
 // plus the two north-star operators that have no reference function (PCL definitions):
@@ -244,6 +245,28 @@ inline std::vector<float> eigenPlaneCosineSimilarity(Session &s, const std::vect
     std::vector<float> out(pca.size());
     if (!s.ok() || !s.check(ccg_eigen_scalar(s.ctx(), reinterpret_cast<const float *>(pca.data()), pca.size(), 1, out.data()))) out.clear();
     return out;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// octreeDownsample — src/utilities/utils.h:16-62: one averaged point per voxel of edge `resolution` (ALL float
+// fields of PointT, accumulator = default-constructed PCL point as in the reference) and the big -> small index map
+// in sub_idxs.  map_small_to_big (utils.h:74-86) is the reference's own host loop and stays as it is.
+// Voxel numbering is ascending packed key, not PCL's octree DFS order (include/ccgpu.h): consumers index the small
+// cloud only through sub_idxs, which is consistent with it.
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT>
+std::vector<PointT> octreeDownsample(Session &s, const PointT *input, size_t n, float resolution, std::vector<int> &sub_idxs) {
+    static_assert(sizeof(PointT) % sizeof(float) == 0 && sizeof(PointT) / sizeof(float) <= 16, "point type is a short array of floats");
+    std::vector<PointT> output;
+    sub_idxs.assign(n, 0);
+    if (!s.ok() || !s.setInputCloud(input, n) || n == 0) return output;
+    int64_t n_out = 0;
+    if (!s.check(ccg_voxel_downsample(s.ctx(), input, sizeof(PointT), (int)(sizeof(PointT) / sizeof(float)), resolution, /*as_written=*/1,
+                                      reinterpret_cast<int32_t *>(sub_idxs.data()), &n_out)))
+        return output;
+    output.resize((size_t)n_out);
+    if (!s.check(ccg_voxel_downsample_fetch(s.ctx(), reinterpret_cast<float *>(output.data())))) output.clear();
+    return output;
 }
 
 }  // namespace ccgpu

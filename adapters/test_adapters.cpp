@@ -256,6 +256,46 @@ int main() {
         CHECK(estimateNormals(s, pts.data(), n, bad_map, W, H).empty(), "a short cloud_to_grid map must be refused");
     }
 
+    // ---- octreeDownsample (utils.h:16-62): voxel means of all 8 floats + big -> small map ----
+    {
+        const float res = 0.2f;
+        std::vector<int> sub;
+        auto small = octreeDownsample(s, pts.data(), n, res, sub);
+        CHECK(!small.empty() && sub.size() == n, "octreeDownsample returned nothing (%s)", s.lastError().c_str());
+        std::vector<double> sx(small.size(), 0), sy(small.size(), 0), sz(small.size(), 0), si(small.size(), 0);
+        std::vector<int> cnt(small.size(), 0);
+        bool in_range = true, same_voxel = true;
+        const float h = res * 0.5f;
+        for (size_t i = 0; i < n && !small.empty(); ++i) {
+            const int v = sub[i];
+            if (v < 0 || v >= (int)small.size()) { in_range = false; continue; }
+            sx[v] += pts[i].x; sy[v] += pts[i].y; sz[v] += pts[i].z; si[v] += pts[i].intensity; cnt[v]++;
+        }
+        // points of one voxel share the lattice cell floor((p - (p0 - res/2)) / res)
+        std::vector<long long> cell(small.size(), -1);
+        for (size_t i = 0; i < n && in_range; ++i) {
+            long long kx = (long long)std::floor((pts[i].x - (pts[0].x - h)) / res), ky = (long long)std::floor((pts[i].y - (pts[0].y - h)) / res),
+                      kz = (long long)std::floor((pts[i].z - (pts[0].z - h)) / res);
+            long long key = ((kx & 0x1fffff) << 42) | ((ky & 0x1fffff) << 21) | (kz & 0x1fffff);
+            if (cell[sub[i]] == -1) cell[sub[i]] = key;
+            else if (cell[sub[i]] != key) same_voxel = false;
+        }
+        CHECK(in_range, "sub_idxs out of range");
+        CHECK(same_voxel, "points of different lattice cells share a voxel");
+        for (size_t v = 1; v < cell.size(); ++v) CHECK(cell[v] > cell[v - 1], "voxels must be numbered by ascending key");
+        double worst = 0;
+        for (size_t v = 0; v < small.size() && in_range; ++v) {
+            CHECK(cnt[v] > 0, "empty voxel %zu", v);
+            worst = std::max(worst, std::fabs(small[v].x - sx[v] / cnt[v]));
+            worst = std::max(worst, std::fabs(small[v].y - sy[v] / cnt[v]));
+            worst = std::max(worst, std::fabs(small[v].z - sz[v] / cnt[v]));
+            worst = std::max(worst, std::fabs(small[v].intensity - si[v] / cnt[v]));
+            worst = std::max(worst, std::fabs(small[v].w - (cnt[v] + 1.0) / cnt[v]));       // as written: float[3] starts at 1
+        }
+        std::printf("octreeDownsample: %zu voxels from %zu points, max mean error %.3g\n", small.size(), n, worst);
+        CHECK(worst <= 1e-5, "voxel means off by %g", worst);
+    }
+
     // ---- error behaviour: empty result + message, no exception, session stays usable ----
     {
         std::vector<PointXYZI> bad(pts.begin(), pts.begin() + 100);

@@ -28,6 +28,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch",
 ]
 
 
@@ -91,6 +92,8 @@ def load_library():
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
     L.ccg_ipc_open.argtypes = [vp, vp, C.POINTER(vp)]
     L.ccg_ipc_close.argtypes = [vp, vp]
+    L.ccg_voxel_downsample.argtypes = [vp, vp, sz, i32, C.c_float, i32, vp, C.POINTER(C.c_int64)]
+    L.ccg_voxel_downsample_fetch.argtypes = [vp, vp]
     _lib = L
     return L
 
@@ -245,6 +248,21 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_scatter(self.h, k, cov_norm, _ptr(vp), formula_set, begin, end, _addr(eig),
                                                         _addr(nrm), _addr(feat)))
+
+    def voxel_downsample(self, points, resolution, n_floats=None, as_written=True, device_out=None):
+        """octreeDownsample (utils.h:16-62): points = the [n, S] float32 array given to set_cloud ->
+        (means [nvox, n_floats], big_to_small int32[n])"""
+        nf = points.shape[1] if n_floats is None else n_floats
+        stride = points.stride(0) * 4 if _is_torch(points) else points.strides[0]
+        dev = self.on_device if device_out is None else device_out
+        b2s = self._out(dev, (self.n,), np.int32)
+        nv = C.c_int64(0)
+        self._check(self.L.ccg_voxel_downsample(self.h, _ptr(points), stride, nf, float(resolution), 1 if as_written else 0,
+                                                _ptr(b2s), C.byref(nv)))
+        out = self._out(dev, (nv.value, nf), np.float32)
+        if nv.value:
+            self._check(self.L.ccg_voxel_downsample_fetch(self.h, _ptr(out)))
+        return out, b2s
 
     def dev_alloc(self, nbytes):
         p = C.c_void_p()

@@ -85,19 +85,6 @@ __global__ void __launch_bounds__(256) k_count_mask(const int32_t *__restrict__ 
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = ((cand == nullptr || cand[i]) && count[i] < min_neighbours) ? 1 : 0;
 }
-// voxel key of octreeDownsample's lattice (utils.h:29-31 via outlierfilter.cpp:128): first point at a voxel centre
-__global__ void __launch_bounds__(256) k_voxel_keys(const float4 *__restrict__ orig, size_t n, float edge,
-                                                    unsigned long long *__restrict__ keys, unsigned *__restrict__ vals) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 p0 = orig[0], p = orig[i];
-    const float h = __fmul_rn(edge, 0.5f);
-    long long kx = (long long)floorf(__fdiv_rn(__fsub_rn(p.x, __fsub_rn(p0.x, h)), edge));
-    long long ky = (long long)floorf(__fdiv_rn(__fsub_rn(p.y, __fsub_rn(p0.y, h)), edge));
-    long long kz = (long long)floorf(__fdiv_rn(__fsub_rn(p.z, __fsub_rn(p0.z, h)), edge));
-    keys[i] = ((unsigned long long)(kx & 0x1fffff) << 42) | ((unsigned long long)(ky & 0x1fffff) << 21) | (unsigned long long)(kz & 0x1fffff);
-    vals[i] = (unsigned)i;
-}
 // after sorting by voxel key: candidate[i] = (points in i's voxel) < min_neighbours
 __global__ void __launch_bounds__(256) k_voxel_candidates(const unsigned long long *__restrict__ keys, const unsigned *__restrict__ vals,
                                                           size_t n, int min_neighbours, uint8_t *__restrict__ cand) {
@@ -242,6 +229,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     ctx->raw.release(); ctx->orig.release(); ctx->sorted.release();
     for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
+    ctx->vox_out.release();
     ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release();
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -439,6 +427,46 @@ int ccg_ipc_close(ccg_ctx *ctx, void *ptr) {
     return CCG_OK;
 }
 
+/* ---- f1: octreeDownsample (utils.h:16-62) -------------------------------------------------------------- */
+int ccg_voxel_downsample(ccg_ctx *ctx, const void *points, size_t stride_bytes, int n_floats, float resolution, int as_written,
+                         int32_t *big_to_small, int64_t *n_out) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!n_out) return set_error(ctx, CCG_ERR_INVALID, "n_out is NULL");
+    *n_out = 0;
+    ctx->vox_n = 0;
+    if (!(resolution > 0.f)) return set_error(ctx, CCG_ERR_INVALID, "resolution must be > 0");
+    if (stride_bytes < 12 || (stride_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "stride_bytes must be >= 12 and a multiple of 4");
+    if (n_floats < 1 || n_floats > 16 || (size_t)n_floats * 4 > stride_bytes)
+        return set_error(ctx, CCG_ERR_INVALID, "n_floats must be in [1,16] and fit the stride");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    if (!points) return set_error(ctx, CCG_ERR_INVALID, "points is NULL");
+    const void *pd = points;
+    if (!is_dev(ctx, points)) {
+        const size_t bytes = (n - 1) * stride_bytes + (size_t)n_floats * 4;
+        CCG_CUDA(ctx, ctx->raw.reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->raw.p, points, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        pd = ctx->raw.p;
+    }
+    OutBuf ob;
+    CCG_TRY(ob.open(ctx, 0, big_to_small, n * 4));
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(voxel_downsample(ctx, pd, stride_bytes, n_floats, resolution, as_written, ob.dev<int32_t>(), n_out));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(ob.close());
+    return finish_call(ctx);
+}
+
+int ccg_voxel_downsample_fetch(ccg_ctx *ctx, float *out_points) {
+    CCG_TRY(begin_call(ctx, false));
+    if (ctx->vox_n == 0) return CCG_OK;
+    if (!out_points) return set_error(ctx, CCG_ERR_INVALID, "out_points is NULL");
+    const size_t bytes = (size_t)ctx->vox_n * ctx->vox_nf * sizeof(float);
+    CCG_CUDA(ctx, cudaMemcpyAsync(out_points, ctx->vox_out.p, bytes, cudaMemcpyDefault, ctx->stream));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return CCG_OK;
+}
+
 int ccg_pca_knn(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, float *eig3, float *normal4) {
     CCG_TRY(begin_call(ctx, true));
     if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
@@ -586,21 +614,11 @@ int ccg_radius_count_mask(ccg_ctx *ctx, double r, int min_neighbours, int prefil
     CCG_TRY(query_begin(ctx));
     if (prefilter) {
         CCG_CUDA(ctx, ctx->tmp[1].reserve(n));
-        CCG_CUDA(ctx, ctx->tmp[2].reserve(n * 16 + 64));
-        CCG_CUDA(ctx, ctx->tmp[3].reserve(n * 8 + 64));
+        const unsigned long long *ks; const unsigned *vs;
         cand = ctx->tmp[1].as<uint8_t>();
-        unsigned long long *k0 = ctx->tmp[2].as<unsigned long long>(), *k1 = k0 + n;
-        unsigned *v0 = ctx->tmp[3].as<unsigned>(), *v1 = v0 + n;
-        const float edge = (float)(2.0 * r);
-        k_voxel_keys<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx->orig.as<float4>(), n, edge, k0, v0);
-        cub::DoubleBuffer<unsigned long long> dk(k0, k1);
-        cub::DoubleBuffer<unsigned> dv(v0, v1);
-        size_t tmp_bytes = 0;
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 63, st));
-        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, (int)n, 0, 63, st));
-        k_voxel_candidates<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(dk.Current(), dv.Current(), n, min_neighbours, cand);
-        ctx->stats.launches += 11;
+        CCG_TRY(voxel_sort(ctx, (float)(2.0 * r), &ks, &vs));
+        k_voxel_candidates<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ks, vs, n, min_neighbours, cand);
+        ctx->stats.launches += 1;
     }
     StreamArgs s{};
     s.mode = 0; s.rb = radius_bound(r, 0); s.count_cap = min_neighbours; s.begin = 0; s.end = n; s.count = cnt;

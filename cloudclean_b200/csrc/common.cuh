@@ -87,6 +87,8 @@ struct ccg_ctx {
     ccg::DevBuf scratch;     // bbox / flags / counters
     ccg::DevBuf out[4];      // staged outputs for host destinations
     ccg::DevBuf tmp[4];      // per-call temporaries
+    ccg::DevBuf vox_out;     // result of the last ccg_voxel_downsample: float[vox_n * vox_nf]
+    int64_t vox_n = 0; int vox_nf = 0;
     ccg::DevBuf defer;       // [count | query list | output rows] of queries deferred to the exact point kernel
     ccg::HostBuf hpin[2];    // pinned bounce buffers
     float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};
@@ -181,6 +183,11 @@ int launch_point_query(ccg_ctx *ctx, const PointArgs &a);
 int launch_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out);
 int launch_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out);
 int launch_unpermute(ccg_ctx *ctx, const void *in, size_t row_bytes, void *out);
+
+// voxel.cu
+int voxel_sort(ccg_ctx *ctx, float edge, const unsigned long long **keys_sorted, const unsigned **vals_sorted);
+int voxel_downsample(ccg_ctx *ctx, const void *points_dev, size_t stride, int nf, float resolution, int as_written,
+                     int32_t *big_to_small_dev, int64_t *n_out);
 
 // gridnormals.cu
 int launch_grid_normals(ccg_ctx *ctx, const int32_t *c2g_dev, int scan_w, int scan_h, int do_fallback, float *normal4_dev,

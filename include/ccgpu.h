@@ -182,6 +182,22 @@ int ccg_ipc_export(ccg_ctx *ctx, const void *ptr, void *handle64);
 int ccg_ipc_open(ccg_ctx *ctx, const void *handle64, void **out);     /* enables peer access lazily */
 int ccg_ipc_close(ccg_ctx *ctx, void *ptr);
 
+/* ---- f1: voxel downsample (octreeDownsample, src/utilities/utils.h:16-62) ----------------------------------
+ * The step in front of every feature call of the reference (featureeval.cpp:687,995,1029; markov.cpp:306;
+ * flood.cpp:269; outlierfilter.cpp:128).  `points` is the SAME array of structs that was given to ccg_set_cloud
+ * (host or device); the first n_floats floats of every struct are averaged per voxel of edge `resolution`
+ * (the reference averages sizeof(PointT)/sizeof(float) floats, padding included: 8 for PointXYZI).
+ * as_written != 0 reproduces the reference's accumulator, a default-constructed PCL point whose float[3] is 1
+ * (utils.h:41-48), so float[3] of a voxel comes out as (count + 1) / count; 0 gives the plain mean.
+ * Voxel lattice: the first cloud point sits at a voxel centre, voxel(p) = floor((p - (p0 - res/2)) / res) in fp32
+ * (PCL grows its octree box by whole voxels from the first point; its exact lattice depends on insertion history and
+ * cannot be reproduced — set-level parity only).  Voxels are numbered in ascending packed (x,y,z) key
+ * order; big_to_small[i] (int32[n], optional) = voxel of point i (utils.h:50).  *n_out = number of voxels.
+ * ccg_voxel_downsample_fetch then copies the n_out * n_floats packed means to out_points (host or device). */
+int ccg_voxel_downsample(ccg_ctx *ctx, const void *points, size_t stride_bytes, int n_floats, float resolution, int as_written,
+                         int32_t *big_to_small, int64_t *n_out);
+int ccg_voxel_downsample_fetch(ccg_ctx *ctx, float *out_points);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,8 @@ def lib():
         L.cco_radius_outliers.argtypes = [vp, f64, i32, i32, vp, i32]
         L.cco_grid_normals.restype = i32
         L.cco_grid_normals.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, vp]
+        L.cco_voxel_downsample.restype = i32
+        L.cco_voxel_downsample.argtypes = [vp, i32, i32, i32, C.c_float, i32, vp, vp]
         L.cco_eig3_f64_export.argtypes = [vp, vp, vp]
         L.cco_eig3_f32_export.argtypes = [vp, vp]
         L.cco_max_threads.restype = i32
@@ -199,6 +201,17 @@ def grid_normals(points, cloud_to_grid, scan_w, scan_h, fallback=True, k_fallbac
     still = lib().cco_grid_normals(_p(pts), pts.shape[0], pts.strides[0], _p(c2g), scan_w, scan_h,
                                    1 if fallback else 0, k_fallback, _p(out))
     return out, still
+
+
+def voxel_downsample(points, resolution, n_floats=None, as_written=True):
+    """f1 (utils.h:16-62) — (means[float32 nvox, nf], big_to_small[int32 n]); sequential fp32 sums in index order."""
+    pts = np.ascontiguousarray(points, dtype=np.float32)
+    nf = pts.shape[1] if n_floats is None else n_floats
+    out = np.empty((pts.shape[0], nf), np.float32)
+    b2s = np.empty(pts.shape[0], np.int32)
+    nv = lib().cco_voxel_downsample(_p(pts), pts.shape[0], pts.strides[0], nf, float(resolution), 1 if as_written else 0,
+                                    _p(out), _p(b2s))
+    return out[:nv].copy(), b2s
 
 
 def eig3_f64(a6):

@@ -630,6 +630,49 @@ void cco_radius_outliers(const void *tv, double r, int min_neighbours, int prefi
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* f1: octreeDownsample (src/utilities/utils.h:16-62)                                           */
+/* ------------------------------------------------------------------------------------------ */
+/* Per voxel of edge `resolution` (lattice of cco_voxel_key; voxels numbered in ascending key order — PCL's own
+ * leaf order is an octree DFS over an insertion-dependent box [EXT] and is not reproduced): the first nf floats
+ * of every point's struct are summed in INDEX order in fp32 into an accumulator that starts as a
+ * default-constructed PCL point (float[3] = 1 when as_written, utils.h:41-48), then scaled by
+ * (float)(1.0 / count) (utils.h:52-54).  big_to_small[i] = voxel of point i (utils.h:50).  Returns the voxel count;
+ * out must hold n*nf floats. */
+typedef struct { int64_t key; int idx; } cco_kv;
+static int cco_cmp_kv(const void *a, const void *b) {
+    const cco_kv *x = (const cco_kv *)a, *y = (const cco_kv *)b;
+    if (x->key != y->key) return x->key < y->key ? -1 : 1;
+    return x->idx < y->idx ? -1 : x->idx > y->idx;
+}
+int cco_voxel_downsample(const void *aos, int n, int stride_bytes, int nf, float resolution, int as_written,
+                         float *out, int32_t *big_to_small) {
+    if (n <= 0) return 0;
+#define CCO_PT(i) ((const float *)((const char *)aos + (size_t)(i) * (size_t)stride_bytes))
+    cco_kv *kv = (cco_kv *)malloc(sizeof(cco_kv) * (size_t)n);
+    for (int i = 0; i < n; i++) { kv[i].key = cco_voxel_key(CCO_PT(i), CCO_PT(0), resolution); kv[i].idx = i; }
+    qsort(kv, (size_t)n, sizeof(cco_kv), cco_cmp_kv);
+    int nv = 0;
+    for (int b = 0; b < n;) {
+        int e = b;
+        while (e < n && kv[e].key == kv[b].key) e++;
+        float acc[16];
+        for (int f = 0; f < nf; f++) acc[f] = (as_written && f == 3) ? 1.0f : 0.0f;
+        for (int j = b; j < e; j++) {
+            const float *p = CCO_PT(kv[j].idx);
+            for (int f = 0; f < nf; f++) acc[f] = acc[f] + p[f];
+            if (big_to_small) big_to_small[kv[j].idx] = nv;
+        }
+        float size_inv = (float)(1.0 / (double)(e - b));
+        for (int f = 0; f < nf; f++) out[(size_t)nv * nf + f] = acc[f] * size_inv;
+        nv++;
+        b = e;
+    }
+    free(kv);
+#undef CCO_PT
+    return nv;
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* a7: scan-grid triangle-fan normals (normalestimation.cpp:268-470)                            */
 /* ------------------------------------------------------------------------------------------ */
 static const int CCO_RING[8][2] = {{1, 0}, {1, -1}, {0, -1}, {-1, -1}, {-1, 0}, {-1, 1}, {0, 1}, {1, 1}}; /* :293-302 */

@@ -381,3 +381,43 @@ def test_pipelined_host_outputs_are_identical(monkeypatch, shuffle, chunks):
     T = oracle.Tree(pts)
     ri, _ = T.knn(20)
     check_pca(ref[0], ref[1], oracle.pca_lists(pts, ri, cov_norm=1))
+
+
+# ---- f1: voxel downsample (octreeDownsample, utils.h:16-62) -------------------------------------------------
+@pytest.mark.parametrize("res", [0.02, 0.1, 0.5])
+@pytest.mark.parametrize("as_written", [True, False])
+@pytest.mark.parametrize("device", [False, True])
+def test_voxel_downsample(gpu_ctx, res, as_written, device):
+    """Voxel membership (big_to_small, voxel count, numbering) bit-exact; the per-voxel means within 1e-5 relative of
+    the oracle's sequential fp32 sums (the GPU sums lane-strided partials, so the fp32 rounding order differs)."""
+    scan = synth.make_scan_np(120, 90, scene="room", seed=4)
+    pts = np.ascontiguousarray(scan["points"])
+    want, wmap = oracle.voxel_downsample(pts, res, as_written=as_written)
+    if device:
+        import torch
+        dpts = torch.as_tensor(pts, device="cuda")
+        gpu_ctx.set_cloud(dpts)
+        got, gmap = gpu_ctx.voxel_downsample(dpts, res, as_written=as_written)
+        got, gmap = got.cpu().numpy(), gmap.cpu().numpy()
+    else:
+        gpu_ctx.set_cloud(pts)
+        got, gmap = gpu_ctx.voxel_downsample(pts, res, as_written=as_written, device_out=False)
+    assert got.shape == want.shape
+    assert np.array_equal(gmap, wmap)
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    counts = np.bincount(wmap, minlength=want.shape[0])
+    w3 = (counts + (1 if as_written else 0)) / counts * pts[0, 3]
+    assert np.allclose(got[:, 3], w3, rtol=1e-5)
+
+
+def test_voxel_downsample_xyz_only_and_errors(gpu_ctx):
+    rng = np.random.default_rng(8)
+    pts = rng.random((5000, 3)).astype(np.float32)
+    gpu_ctx.set_cloud(pts)
+    got, gmap = gpu_ctx.voxel_downsample(pts, 0.2, as_written=False, device_out=False)
+    want, wmap = oracle.voxel_downsample(pts, 0.2, as_written=False)
+    assert np.array_equal(gmap, wmap) and np.allclose(got, want, rtol=1e-5, atol=1e-6)
+    with pytest.raises(cc.CcgError):
+        gpu_ctx.voxel_downsample(pts, 0.0, device_out=False)
+    with pytest.raises(cc.CcgError):
+        gpu_ctx.voxel_downsample(pts, 0.1, n_floats=4, device_out=False)      # 4 floats do not fit a 12-byte stride

@@ -159,3 +159,30 @@ def test_eig3_f32_tracks_f64():
         ref = np.linalg.eigvalsh(c)[::-1]
         assert np.allclose(w64, ref, rtol=1e-10, atol=1e-14)
         assert np.abs(w32 - ref).max() <= 1e-5 * ref[0]
+
+
+# ---- f1: octreeDownsample (utils.h:16-62) against an independent numpy restatement ---------------------------
+@pytest.mark.parametrize("res", [0.05, 0.3])
+def test_voxel_downsample_oracle_vs_numpy(res):
+    rng = np.random.default_rng(3)
+    n = 4000
+    pts = np.zeros((n, 8), np.float32)
+    pts[:, :3] = rng.normal(size=(n, 3)).astype(np.float32)
+    pts[:, 3] = 1.0
+    pts[:, 4] = rng.random(n).astype(np.float32)
+    means, b2s = oracle.voxel_downsample(pts, res)
+    p0 = pts[0, :3]
+    edge = np.float32(res)
+    cell = np.floor((pts[:, :3] - (p0 - edge * np.float32(0.5))) / edge).astype(np.int64)
+    packed = ((cell[:, 0] & 0x1FFFFF) << 42) | ((cell[:, 1] & 0x1FFFFF) << 21) | (cell[:, 2] & 0x1FFFFF)
+    uniq, inv = np.unique(packed, return_inverse=True)          # ascending packed key == the oracle's voxel numbering
+    assert means.shape == (len(uniq), 8)
+    assert np.array_equal(b2s, inv.astype(np.int32))
+    for v in range(0, len(uniq), max(1, len(uniq) // 50)):
+        sel = np.flatnonzero(inv == v)
+        acc = np.zeros(8, np.float32); acc[3] = 1.0              # default-constructed PCL point (utils.h:41-48)
+        for i in sel:
+            acc = acc + pts[i]
+        assert np.array_equal(means[v], acc * np.float32(1.0 / len(sel)))
+    plain, _ = oracle.voxel_downsample(pts, res, as_written=False)
+    assert np.allclose(plain[:, 3], 1.0)
