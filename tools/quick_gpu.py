@@ -33,9 +33,21 @@ for cfg, shrink in cfgs:
         ok = res["gap64"] > 1e-3
         print("  eig err max/ 99.9%:", err.max(), np.quantile(err, 0.999), " 1-|cos| max (gap>1e-3):", (1 - cos[ok]).max(), flush=True)
     out, md = ctx.sor_mask(30, 1.0)
+    out, md = ctx.sor_mask(30, 1.0)      # second call: pinned bounce buffer already grown
     q = ctx.stats(); print(f"  sor k=30 query_ms={q['ms_query']:.2f} outliers={int(out.sum())}", flush=True)
     for r in (0.05, 0.1, 0.2):
         e3, _, cnt = ctx.pca_radius(r, 20)
         q = ctx.stats(); print(f"  pca_radius r={r} max_nn=20 query_ms={q['ms_query']:.2f} mean count={float(cnt.float().mean()):.1f}", flush=True)
+    for res in (0.02, 0.1):
+        import time as _t
+        torch.cuda.synchronize(); t0 = _t.perf_counter()
+        small, b2s = ctx.voxel_downsample(pts, res)
+        torch.cuda.synchronize(); t1 = _t.perf_counter()
+        q = ctx.stats(); print(f"  voxel_downsample res={res} query_ms={q['ms_query']:.2f} wall_ms={(t1-t0)*1e3:.2f} voxels={small.shape[0]}", flush=True)
+    if n <= 8_000_000:
+        for k in (14, 20, 50):
+            idx, d2 = ctx.knn(k)
+            q = ctx.stats(); print(f"  knn lists k={k} query_ms={q['ms_query']:.2f} -> {n/(q['ms_query']*1e-3)/1e6:.1f} Mpts/s", flush=True)
+            del idx, d2
     del s, pts, eig, nrm
     torch.cuda.empty_cache()
