@@ -196,6 +196,10 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    # the ONE JSON line goes to the real stdout; anything a library prints meanwhile (e.g. NCCL's version banner) to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     args.warmup = max(args.warmup, 3) if args.shrink == 1 else args.warmup
 
     import torch
@@ -249,6 +253,7 @@ def main():
             o_eig, o_nrm, o_feat = (b.tensor(dev) for b in peer.bufs)
     launches = [0]
     kernel_ms = []
+    bcast_ev = []
 
     def step_device():
         if world == 1:
@@ -259,7 +264,11 @@ def main():
             launches[0] += st["launches"]
             kernel_ms.append(st["ms_query"])
         else:
+            eb0 = torch.cuda.Event(enable_timing=True); eb1 = torch.cuda.Event(enable_timing=True)
+            eb0.record(stream)
             dist.broadcast(pts, 0)
+            eb1.record(stream)
+            bcast_ev.append((eb0, eb1))
             ctx.set_cloud(pts)
             launches[0] += ctx.stats()["launches_build"]
             # every rank answers its Morton range and stores the rows, in original order, straight into rank 0's
@@ -321,7 +330,18 @@ def main():
         sampler.start()
     launches[0] = 0
     kernel_ms.clear()
+    bcast_ev.clear()
     ms_dev = timed(step_device, args.steps, args.warmup)
+    stage_extra = {}
+    if world > 1:
+        # per-stage picture of the sharded step: NCCL broadcast of the cloud, slowest rank's query (incl. its NVLink stores)
+        bms = float(np.mean([a.elapsed_time(b) for a, b in bcast_ev[args.warmup:]]))
+        qms = float(np.mean(kernel_ms[args.warmup:]))
+        tq = torch.tensor([qms, bms], device=dev, dtype=torch.float64)
+        tmax = tq.clone(); tmin = tq.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX); dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        stage_extra = {"broadcast": float(tmax[1].item()), "query_kernel_max_over_ranks": float(tmax[0].item()),
+                       "query_kernel_min_over_ranks": float(tmin[0].item())}
     n_launch = launches[0] * args.steps // (args.steps + args.warmup)
     kms = kernel_ms[args.warmup:]
     ms_e2e = timed(step_host, max(2, args.steps // 2), 1)
@@ -348,14 +368,15 @@ def main():
                              "peak_source": peak_src, "algorithmic_bytes_per_point": BYTES_QUERY, "points_per_launch": q_rows,
                              "kernel_ms": k_ms,
                              "whole_step_GBps": (BYTES_QUERY + BYTES_BUILD) * n / (ms_dev / args.steps * 1e-3) / 1e9},
-                "stage_ms": {"build": st["ms_build"], "query_kernel": k_ms}}
+                "stage_ms": dict({"build": st["ms_build"], "query_kernel": k_ms}, **stage_extra)}
         if not args.no_cpu_baseline and world == 1:
             import oracle
             cpts, sample = cpu_sample_points(args.scan_cfg, args.shrink)
             t = cpu_pass(cpts)
             line["cpu_baseline"] = {"value": cpts.shape[0] / t, "unit": "points/s", "cores": oracle.max_threads(), "kind": "port",
                                     "sample": sample + f"; {t:.1f} s"}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
         torch.cuda.synchronize()
         dist.barrier()

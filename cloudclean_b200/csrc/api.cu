@@ -215,6 +215,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
     const char *sp = getenv("CCG_SPLIT_SPARSE");
     ctx->split_sparse = (sp && sp[0] == '0') ? 0 : 1;
+    const char *kt = getenv("CCG_KNN_TOPK");
+    ctx->knn_use_topk = (kt && kt[0] == '1') ? 1 : 0;
     const char *pc = getenv("CCG_PIPELINE_CHUNKS");
     if (pc) ctx->pipeline_chunks = atoi(pc);
     const char *pm = getenv("CCG_PIPELINE_MIN_POINTS");

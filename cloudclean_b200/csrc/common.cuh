@@ -97,6 +97,7 @@ struct ccg_ctx {
     int collect_stats = 0;
     int pipeline_chunks = 8;         // host-output pipelining of the PCA query (CCG_PIPELINE_CHUNKS; <= 1 disables)
     int pipeline_min_points = 1 << 18;
+    int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
     int split_sparse = 1;    // move isolated points to the end of the order (CCG_SPLIT_SPARSE=0 disables)
     char err[512] = "";
 

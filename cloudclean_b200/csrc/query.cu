@@ -839,8 +839,8 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
 
 template <int K, int MODE>
 __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
-    constexpr int CAP = MODE == MODE_PCA ? LogCap<K>::value : 1;
-    constexpr bool LOG = MODE == MODE_PCA;
+    constexpr int CAP = MODE != MODE_SOR ? LogCap<K>::value : 1;
+    constexpr bool LOG = MODE != MODE_SOR;
     __shared__ WarpScratch3<CAP> s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = P.tile_begin + blockIdx.x * 2 + warp;
@@ -903,7 +903,17 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
         return;
     }
     // pass 2: the neighbour set {d2 <= t} lies in the home leaves and the log
-    const float t = (active && !lone) ? fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX) : -1.f;   // finite: +inf pads never qualify
+    float t = (active && !lone) ? fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX) : -1.f;   // finite: +inf pads never qualify
+    // MODE_KNN (ordered lists): the value list is already the sorted d2 row; a neighbour's slot is the number of list
+    // values below its d2, which is unique as long as no two list values are equal.  Equal values need the
+    // (d2, index) tie-break: those queries go to the exact point kernel, like tie overflow at the k-th value.
+    bool dup = false;
+    if (MODE == MODE_KNN) {
+#pragma unroll
+        for (int i = 1; i < K; ++i)
+            if (i > K - k) dup = dup || (v.key[i] == v.key[i - 1] && v.key[i] != INFINITY);
+        if (dup) t = -1.f;
+    }
     int count = 0;
     float m[9];
 #pragma unroll
@@ -923,11 +933,19 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
                 const int j = __ffs(msk) - 1;
                 msk &= msk - 1;
                 const float4 c = S.w.ws.leaf[j];
-                if (d2_point(q, c) <= t) {
+                const float dd = d2_point(q, c);
+                if (dd <= t) {
                     ++count;
-                    const float dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
-                    m[0] += dx; m[1] += dy; m[2] += dz;
-                    m[3] += dx * dx; m[4] += dx * dy; m[5] += dx * dz; m[6] += dy * dy; m[7] += dy * dz; m[8] += dz * dz;
+                    if (MODE == MODE_KNN) {
+                        int below = 0;
+#pragma unroll
+                        for (int i2 = 0; i2 < K; ++i2) below += v.key[i2] < dd ? 1 : 0;
+                        if (P.idx) P.idx[row * k + (below - (K - k))] = __float_as_int(c.w);
+                    } else {
+                        const float dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
+                        m[0] += dx; m[1] += dy; m[2] += dz;
+                        m[3] += dx * dx; m[4] += dx * dy; m[5] += dx * dz; m[6] += dy * dy; m[7] += dy * dz; m[8] += dz * dz;
+                    }
                 }
             }
         }
@@ -938,19 +956,39 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
         if (e < v.cnt) {
             const unsigned id = v.log[e * 32];
             const float4 c = T.pts[(size_t)S.w.list[id >> 5] * kLeaf + (id & 31u)];
-            if (d2_point(q, c) <= t) {
+            const float dd = d2_point(q, c);
+            if (dd <= t) {
                 ++count;
-                const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
-                m[0] += x; m[1] += y; m[2] += z;
-                m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+                if (MODE == MODE_KNN) {
+                    int below = 0;
+#pragma unroll
+                    for (int i2 = 0; i2 < K; ++i2) below += v.key[i2] < dd ? 1 : 0;
+                    if (P.idx) P.idx[row * k + (below - (K - k))] = __float_as_int(c.w);
+                } else {
+                    const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
+                    m[0] += x; m[1] += y; m[2] += z;
+                    m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
+                }
             }
         }
     }
     if (!active || lone) return;
-    if (count > k) {                                // ties at the k-th distance overflow the list: exact kernel decides
+    if (count > k || dup) {                                // ties at the k-th distance overflow the list: exact kernel decides
         const int slot = atomicAdd(P.defer_count, 1);
         P.defer_list[slot] = qidx;
         P.defer_row[slot] = (long long)row;
+        return;
+    }
+    if (MODE == MODE_KNN) {
+#pragma unroll
+        for (int i = 0; i < K; ++i) {
+            if (i >= K - k) {
+                const int j = i - (K - k);
+                if (P.d2) P.d2[row * k + j] = j < count ? v.key[i] : INFINITY;
+                if (j >= count && P.idx) P.idx[row * k + j] = -1;
+            }
+        }
+        if (P.count) P.count[row] = count;
         return;
     }
     pca_finish(P.pca, q, m, count, row);
@@ -1001,6 +1039,7 @@ template <int K>
 static void launch_sel(const TreeView &T, const TileParams &P, int blocks, int sms, cudaStream_t st) {
     const int ntiles = P.tile_end - P.tile_begin;
     if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
     else k_tile_sel<K, MODE_SOR><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
 }
 
@@ -1021,7 +1060,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.tile_order = a.tile_order;
-    if (a.tile_order && a.mode == MODE_KNN) return set_error(ctx, CCG_ERR_INVALID, "tile_order is only supported by the selection kernel");
+    if (a.tile_order && a.mode == MODE_KNN && ctx->knn_use_topk) return set_error(ctx, CCG_ERR_INVALID, "tile_order is only supported by the selection kernel");
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {
         CCG_CUDA(ctx, cudaMemsetAsync((char *)ctx->scratch.p + 1024, 0, 96, ctx->stream));
@@ -1032,7 +1071,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     TreeView T = ctx->view();
     cudaStream_t st = ctx->stream;
     const int k = a.k;
-    if (a.mode == MODE_KNN) {
+    if (a.mode == MODE_KNN && ctx->knn_use_topk) {
         if (k <= 8) launch_topk<8>(T, P, blocks, st);
         else if (k <= 16) launch_topk<16>(T, P, blocks, st);
         else if (k <= 20) launch_topk<20>(T, P, blocks, st);
@@ -1063,6 +1102,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
             PointParams Q{};
             Q.queries = P.defer_list; Q.nq = 0; Q.nq_dev = P.defer_count; Q.rows = P.defer_row;
             Q.mode = a.mode; Q.k = k; Q.rb = a.rb; Q.list_rows = 0;
+            Q.idx = a.idx; Q.d2 = a.d2;
             Q.count = a.count; Q.pca = P.pca; Q.mean_k = a.mean_k; Q.mean_d = a.mean_d;
             k_point_query<<<ctx->sm_count * 8, 128, 0, st>>>(T, Q);
             ctx->stats.launches++;
