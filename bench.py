@@ -177,7 +177,7 @@ def workload_config(args, n):
     return {"workload": f"config {args.scan_cfg}: synthetic outdoor terrestrial scan {a['scan_w'] // args.shrink}x{a['scan_h'] // args.shrink} rays"
                         f" (seed {a['seed']}), kNN(k={K})+PCA(cov 1/(n-1)) normals/curvature/eigenvalues + 7 eigen features",
             "points": n, "k": K, "shrink": args.shrink,
-            "parallelism": "replicated cloud, query shards by Morton range" if args.gpus > 1 else "single GPU",
+            "parallelism": "replicated cloud, queries sharded by interleaved Morton chunks (8192 pts), rows stored to rank 0 over NVLink" if args.gpus > 1 else "single GPU",
             "l2": "inputs+outputs per step >> 126 MB L2 (no flush needed)"}
 
 
@@ -245,12 +245,21 @@ def main():
     nrm = torch.empty((rows, 4), device=dev)
     feat = torch.empty((rows, 7), device=dev)
     if world > 1:
-        # rank 0's original-order output arrays, mapped as NVLink peer memory on every rank (fused query + scatter)
-        peer = sharding.PeerRows(ctx, n, (3, 4, 7), collector=0)
+        # rank 0's output arrays, mapped as NVLink peer memory on every rank (fused query + store over NVLink).
+        # 2 GPUs: rows go straight to their original index.  More peers: scattered 12-28 byte stores into ONE GPU
+        # reach only ~100 GB/s of NVLink ingress (measured), so rows are stored at their Morton position
+        # (contiguous 384-896 B per warp and array) and rank 0 un-permutes them in its own HBM.
+        staged = world > 2
+        npad = (n + 31) // 32 * 32
+        peer = sharding.PeerRows(ctx, npad if staged else n, (3, 4, 7), collector=0)
         p_eig, p_nrm, p_feat = peer.bufs
         token = torch.zeros(1, device=dev)
         if rank == 0:
-            o_eig, o_nrm, o_feat = (b.tensor(dev) for b in peer.bufs)
+            if staged:
+                s_eig, s_nrm, s_feat = (b.tensor(dev) for b in peer.bufs)
+                o_eig = torch.empty((n, 3), device=dev); o_nrm = torch.empty((n, 4), device=dev); o_feat = torch.empty((n, 7), device=dev)
+            else:
+                o_eig, o_nrm, o_feat = (b.tensor(dev) for b in peer.bufs)
     launches = [0]
     kernel_ms = []
     bcast_ev = []
@@ -271,13 +280,18 @@ def main():
             bcast_ev.append((eb0, eb1))
             ctx.set_cloud(pts)
             launches[0] += ctx.stats()["launches_build"]
-            # every rank answers its Morton range and stores the rows, in original order, straight into rank 0's
+            # every rank answers its interleaved share of the Morton order (8192-point chunks, round robin) and stores the rows, in original order, straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
-            ctx.pca_knn_features_scatter(K, cc.COV_NM1, 0, begin, end, p_eig, p_nrm, p_feat)
+            ctx.pca_knn_features_shard(K, cc.COV_NM1, 0, rank, world, p_eig, p_nrm, p_feat, sorted_rows=staged)
             st = ctx.stats()
             launches[0] += st["launches"]
             kernel_ms.append(st["ms_query"])
             dist.all_reduce(token)
+            if staged and rank == 0:
+                ctx.unpermute(s_eig, o_eig)
+                ctx.unpermute(s_nrm, o_nrm)
+                ctx.unpermute(s_feat, o_feat)
+                launches[0] += 3
 
     # host-buffer variant (e2e): pinned PointXYZI AoS in, pinned outputs out
     if rank == 0:

@@ -28,7 +28,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard",
 ]
 
 
@@ -87,6 +87,7 @@ def load_library():
     L.ccg_pca_knn_features.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp]
     L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
+    L.ccg_pca_knn_features_shard.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, vp]
     L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.ccg_dev_free.argtypes = [vp, vp]
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
@@ -248,6 +249,15 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_scatter(self.h, k, cov_norm, _ptr(vp), formula_set, begin, end, _addr(eig),
                                                         _addr(nrm), _addr(feat)))
+
+    def pca_knn_features_shard(self, k, cov_norm, formula_set, rank, world, eig, nrm, feat, chunk_points=8192, sorted_rows=False,
+                               viewpoint=None):
+        """interleaved shard of the query (chunks rank, rank+world, ... of the Morton order), rows in ORIGINAL order into
+        own or peer device memory — the load-balanced form of pca_knn_features_scatter.  sorted_rows=True: rows at
+        their Morton position instead (coalesced NVLink stores; the collector un-permutes)"""
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+        self._check(self.L.ccg_pca_knn_features_shard(self.h, k, cov_norm, _ptr(vp), formula_set, rank, world, chunk_points,
+                                                      1 if sorted_rows else 0, _addr(eig), _addr(nrm), _addr(feat)))
 
     def voxel_downsample(self, points, resolution, n_floats=None, as_written=True, device_out=None):
         """octreeDownsample (utils.h:16-62): points = the [n, S] float32 array given to set_cloud ->

@@ -341,13 +341,14 @@ static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise
         if (vp) for (int i = 0; i < 3; ++i) a.vp[i] = vp[i];
         a.eig3 = oe.dev<float>(); a.normal4 = on.dev<float>(); a.count = oc.dev<int32_t>();
         a.feat7 = of.dev<float>(); a.formula_set = formula_set;
+        a.shard_world = ctx->shard_world; a.shard_rank = ctx->shard_rank; a.shard_chunk = ctx->shard_chunk;
         PipeOut po[4];
         int npo = 0;
         if (oe.staged) po[npo++] = PipeOut{&oe, 12};
         if (on.staged) po[npo++] = PipeOut{&on, 16};
         if (oc.staged) po[npo++] = PipeOut{&oc, 4};
         if (of.staged) po[npo++] = PipeOut{&of, 28};
-        if (npo > 0 && !sorted_rows && ctx->pipeline_chunks > 1 && !ctx->collect_stats && ctx->n >= (size_t)ctx->pipeline_min_points)
+        if (npo > 0 && !sorted_rows && a.shard_world <= 1 && ctx->pipeline_chunks > 1 && !ctx->collect_stats && ctx->n >= (size_t)ctx->pipeline_min_points)
             CCG_TRY(pipelined_query(ctx, a, po, npo, ctx->pipeline_chunks));
         else
             CCG_TRY(launch_tile_query(ctx, a));
@@ -391,6 +392,21 @@ int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float 
     if ((eig3 && !is_dev(ctx, eig3)) || (normal4 && !is_dev(ctx, normal4)) || (feat7 && !is_dev(ctx, feat7)))
         return set_error(ctx, CCG_ERR_INVALID, "scatter outputs must be device (own or peer) memory");
     return pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, begin, end, 0, eig3, normal4, nullptr, false, feat7, formula_set);
+}
+
+int ccg_pca_knn_features_shard(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
+                               int chunk_points, int sorted_rows, float *eig3, float *normal4, float *feat7) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    if (world < 1 || rank < 0 || rank >= world) return set_error(ctx, CCG_ERR_INVALID, "need 0 <= rank < world");
+    if (chunk_points < 32 || chunk_points % 32) return set_error(ctx, CCG_ERR_INVALID, "chunk_points must be a positive multiple of 32");
+    if ((eig3 && !is_dev(ctx, eig3)) || (normal4 && !is_dev(ctx, normal4)) || (feat7 && !is_dev(ctx, feat7)))
+        return set_error(ctx, CCG_ERR_INVALID, "shard outputs must be device (own or peer) memory");
+    ctx->shard_world = world > 1 ? world : 0; ctx->shard_rank = rank; ctx->shard_chunk = chunk_points / 32;
+    const int rc = pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, 0, ctx->n, sorted_rows ? 1 : 0, eig3, normal4, nullptr, false, feat7,
+                              formula_set);
+    ctx->shard_world = 0; ctx->shard_rank = 0; ctx->shard_chunk = 0;
+    return rc;
 }
 
 int ccg_dev_alloc(ccg_ctx *ctx, size_t bytes, void **out) {

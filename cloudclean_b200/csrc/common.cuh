@@ -97,6 +97,7 @@ struct ccg_ctx {
     int collect_stats = 0;
     int pipeline_chunks = 8;         // host-output pipelining of the PCA query (CCG_PIPELINE_CHUNKS; <= 1 disables)
     int pipeline_min_points = 1 << 18;
+    int shard_world = 0, shard_rank = 0, shard_chunk = 0;   // set by ccg_*_shard around pca_common
     int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
     int split_sparse = 1;    // move isolated points to the end of the order (CCG_SPLIT_SPARSE=0 disables)
     char err[512] = "";
@@ -154,6 +155,9 @@ struct QueryArgs {
     int mean_k; float *mean_d;
     // MODE_PCA / MODE_SOR: optional processing order; begin/end then count 32-query SLOTS of this list (x32), not positions
     const int32_t *tile_order;
+    // interleaved shard (multi-GPU load balance): this call answers the tiles t with (t / shard_chunk) % shard_world ==
+    // shard_rank and ignores begin/end; shard_world <= 1 = off
+    int shard_world, shard_rank, shard_chunk;
 };
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a);
 

@@ -491,6 +491,7 @@ struct TileParams {
     int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
     int *slow_count; int32_t *slow_tiles;                          // k_tile_sel: tiles handed to k_tile_sel_stack
     const int32_t *tile_order;    // k_tile_sel: non-NULL = tile_begin/tile_end index this list of tiles (output pipelining)
+    int shard_world, shard_rank, shard_chunk;   // k_tile_sel: > 1 = slots enumerate the interleaved chunks of one rank
 };
 
 template <int K>
@@ -845,7 +846,14 @@ __global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ Tre
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = P.tile_begin + blockIdx.x * 2 + warp;
     if (slot >= P.tile_end) return;
-    const int tile = P.tile_order ? P.tile_order[slot] : slot;
+    int tile = slot;
+    if (P.tile_order) {
+        tile = P.tile_order[slot];
+    } else if (P.shard_world > 1) {
+        const int c = slot / P.shard_chunk;
+        tile = (c * P.shard_world + P.shard_rank) * P.shard_chunk + (slot - c * P.shard_chunk);
+        if (tile >= T.count[0]) return;
+    }
     WarpScratch3<CAP> &S = s_ws[warp];
     const size_t pos = (size_t)tile * kLeaf + lane;
     const float4 q = T.pts[pos];
@@ -1060,6 +1068,16 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.tile_order = a.tile_order;
+    P.shard_world = a.shard_world; P.shard_rank = a.shard_rank; P.shard_chunk = a.shard_chunk;
+    if (a.shard_world > 1) {
+        if (a.mode == MODE_KNN && ctx->knn_use_topk) return set_error(ctx, CCG_ERR_INVALID, "interleaved shards need the selection kernel");
+        if (a.shard_chunk < 1 || a.shard_rank < 0 || a.shard_rank >= a.shard_world) return set_error(ctx, CCG_ERR_INVALID, "bad shard");
+        const int chunks_total = (ctx->nleaf + a.shard_chunk - 1) / a.shard_chunk;
+        const int mine = a.shard_rank < chunks_total ? (chunks_total - a.shard_rank + a.shard_world - 1) / a.shard_world : 0;
+        if (mine == 0) return CCG_OK;
+        P.tile_begin = 0;
+        P.tile_end = mine * a.shard_chunk;
+    }
     if (a.tile_order && a.mode == MODE_KNN && ctx->knn_use_topk) return set_error(ctx, CCG_ERR_INVALID, "tile_order is only supported by the selection kernel");
     P.stat_scanned = nullptr;
     if (ctx->collect_stats) {

@@ -173,6 +173,18 @@ int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void 
  * after all ranks' calls with one barrier-like collective on the stream (bench.py: a 1-element all_reduce). */
 int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
                                  float *eig3, float *normal4, float *feat7);
+/* Same, for an INTERLEAVED shard instead of one contiguous range: the Morton order is cut into chunks of chunk_points
+ * (a multiple of 32; 8192 is a good value) and rank r answers chunks r, r+world, r+2*world, ...  Query cost per point
+ * varies along the order (volumetric vegetation vs flat walls, the isolated points collected at its end), so equal
+ * contiguous ranges leave one GPU with several times the work of another; interleaving averages that out
+ * (DESIGN.md §5).
+ * sorted_rows = 0: row = original index (12/16/28-byte stores scattered over the collector's arrays: fine inside one
+ * GPU and for 2 GPUs, but measured at only ~100 GB/s of NVLink ingress when 3-7 peers scatter into one GPU).
+ * sorted_rows = 1: row = position in the Morton order (arrays of ceil(n/32)*32 rows): every warp stores 32 consecutive
+ * rows, i.e. 384/512/896 contiguous bytes per array, which crosses NVLink at full packet size; the collector then
+ * runs ccg_unpermute once per array on its own HBM. */
+int ccg_pca_knn_features_shard(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
+                               int chunk_points, int sorted_rows, float *eig3, float *normal4, float *feat7);
 /* Plain cudaMalloc / cudaFree on the ctx's device (IPC handles need an allocation base, which a caching
  * allocator's sub-block is not). */
 int ccg_dev_alloc(ccg_ctx *ctx, size_t bytes, void **out);

@@ -53,3 +53,23 @@ def test_scatter_over_nvlink_peer_memory_two_ranks():
     print(r.stdout[-2000:], r.stderr[-2000:])
     assert r.returncode == 0
     assert "bit-identical=True" in r.stdout
+
+
+@pytest.mark.parametrize("world,chunk", [(2, 32), (3, 256), (8, 8192), (5, 64)])
+def test_interleaved_shards_fill_the_full_result(world, chunk):
+    import torch
+    pts = np.ascontiguousarray(synth.make_scan_np(150, 110, scene="room", seed=9)["points"])
+    n = pts.shape[0]
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        eig, nrm = ctx.pca_knn(20, cc.COV_NM1, device_out=True)
+        feat = ctx.features(eig)
+        rows = sharding.PeerRows(ctx, n, (3, 4, 7))
+        for b_ in rows.bufs:
+            b_.tensor("cuda:0").fill_(-5.0)
+        for r in range(world):
+            ctx.pca_knn_features_shard(20, cc.COV_NM1, 0, r, world, *rows.bufs, chunk_points=chunk)
+        got = [b_.tensor("cuda:0").clone() for b_ in rows.bufs]
+        rows.close()
+    for a, g in zip((eig, nrm, feat), got):
+        assert torch.equal(torch.as_tensor(a).view(torch.int32), g.view(torch.int32))

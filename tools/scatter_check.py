@@ -23,25 +23,43 @@ n = int(nt.item())
 if rank != 0:
     pts = torch.empty((n, 8), device=dev)
 ctx = cc.Context(local)
-peer = sharding.PeerRows(ctx, n, (3, 4, 7), collector=0)
+npad = (n + 31) // 32 * 32
+peer = sharding.PeerRows(ctx, npad, (3, 4, 7), collector=0)
 token = torch.zeros(1, device=dev)
-for it in range(2):
+ok = True
+names = ["contiguous range, original-order rows", "interleaved chunks, original-order rows", "interleaved chunks, Morton-order rows + un-permute"]
+for it in range(3):
+    if rank == 0:
+        for b_ in peer.bufs:
+            b_.tensor(dev).fill_(-3.0)
     dist.broadcast(pts, 0)
     torch.cuda.synchronize()
     ctx.set_cloud(pts)
     b, e, per = sharding.shard_range(n, rank, world)
-    ctx.pca_knn_features_scatter(20, cc.COV_NM1, 0, b, e, *peer.bufs)
+    if it == 0:
+        ctx.pca_knn_features_scatter(20, cc.COV_NM1, 0, b, e, *peer.bufs)
+    elif it == 1:
+        ctx.pca_knn_features_shard(20, cc.COV_NM1, 0, rank, world, *peer.bufs, chunk_points=1024)
+    else:
+        ctx.pca_knn_features_shard(20, cc.COV_NM1, 0, rank, world, *peer.bufs, chunk_points=1024, sorted_rows=True)
     torch.cuda.synchronize()
     dist.all_reduce(token)
     torch.cuda.synchronize()
-ok = True
-if rank == 0:
-    got = [b_.tensor(dev).clone() for b_ in peer.bufs]
-    eig = torch.empty((n, 3), device=dev); nrm = torch.empty((n, 4), device=dev); feat = torch.empty((n, 7), device=dev)
-    ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat)
-    for a, g in zip((eig, nrm, feat), got):
-        same = torch.equal(a.view(torch.int32), g.view(torch.int32))
+    if rank == 0:
+        got = []
+        for b_ in peer.bufs:
+            if it == 2:                        # rows at their Morton position: un-permute on the collector
+                o = torch.empty((n, b_.shape[1]), device=dev)
+                ctx.unpermute(b_.tensor(dev), o)
+            else:
+                o = b_.tensor(dev)[:n].clone()
+            got.append(o)
+        eig = torch.empty((n, 3), device=dev); nrm = torch.empty((n, 4), device=dev); feat = torch.empty((n, 7), device=dev)
+        ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat)
+        same = all(torch.equal(a_.view(torch.int32), g.view(torch.int32)) for a_, g in zip((eig, nrm, feat), got))
+        print(f"scatter check [{names[it]}]: n={n} world={world} same={same}", flush=True)
         ok = ok and same
+if rank == 0:
     print(f"scatter check: n={n} world={world} bit-identical={ok}", flush=True)
 dist.barrier()
 peer.close()
