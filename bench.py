@@ -36,7 +36,7 @@ K = 20
 BYTES_QUERY = 48 + 16 * K          # own point 16 + k x 16 + outputs 32
 BYTES_BUILD = 144
 METRIC = "points/s kNN(k=20)+PCA features, 30M-pt scan"
-CPU_SAMPLE_POINTS = 2_000_000
+CPU_SAMPLE_POINTS = 8_000_000     # ~4 s per pass on 16 host threads; the cpu_baseline leg times 3 passes (~12 s)
 
 
 def _peaks():
@@ -386,9 +386,10 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             import oracle
             cpts, sample = cpu_sample_points(args.scan_cfg, args.shrink)
-            t = cpu_pass(cpts)
-            line["cpu_baseline"] = {"value": cpts.shape[0] / t, "unit": "points/s", "cores": oracle.max_threads(), "kind": "port",
-                                    "sample": sample + f"; {t:.1f} s"}
+            passes = 3
+            t = sum(cpu_pass(cpts) for _ in range(passes))
+            line["cpu_baseline"] = {"value": passes * cpts.shape[0] / t, "unit": "points/s", "cores": oracle.max_threads(), "kind": "port",
+                                    "sample": sample + f"; {passes} passes, {t:.1f} s of CPU work"}
         sys.stdout.flush()
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if world > 1:
