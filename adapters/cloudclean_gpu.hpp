@@ -13,6 +13,7 @@
 //   NormalEstimator::estimateNormals(cloud)                   src/plugins/normalestimation/normalestimation.cpp:268-470
 //   OutlierFilter::filter()  (index list handed to Select)    src/plugins/outlierfilter/outlierfilter.cpp:120-179
 //   octreeDownsample<PointT>(cloud*, resolution, sub_idxs)    src/utilities/utils.h:16-62
+//   MinCut::buildGraph neighbour + weight loop               src/plugins/graphcut/mincut.cpp:458-475,574-585
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
 // plus the two north-star operators that have no reference function (PCL definitions):
@@ -267,6 +268,22 @@ std::vector<PointT> octreeDownsample(Session &s, const PointT *input, size_t n, 
     output.resize((size_t)n_out);
     if (!s.check(ccg_voxel_downsample_fetch(s.ctx(), reinterpret_cast<float *>(output.data())))) output.clear();
     return output;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// kNN graph for MinCut::buildGraph (graphcut/mincut.cpp:458-475) and Flood::flood (flood.cpp:313-356): the neighbour
+// table the reference obtains with one nearestKSearch per node, plus calculateBinaryPotential (mincut.cpp:574-585)
+// per edge.  neighbours / weights are n*k row-major, entry 0 of a row is the node itself (the reference starts its
+// edge loop at 1, :467).  Returns false on failure.
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT>
+bool knnGraph(Session &s, const PointT *points, size_t n, int k, double inverse_sigma, std::vector<int> &neighbours,
+              std::vector<double> &weights) {
+    neighbours.assign(n * (size_t)k, -1);
+    weights.assign(n * (size_t)k, 0.0);
+    if (!s.ok() || !s.setInputCloud(points, n)) return false;
+    if (n == 0) return true;
+    return s.check(ccg_knn_graph(s.ctx(), k, inverse_sigma, reinterpret_cast<int32_t *>(neighbours.data()), weights.data()));
 }
 
 }  // namespace ccgpu

@@ -296,6 +296,28 @@ int main() {
         CHECK(worst <= 1e-5, "voxel means off by %g", worst);
     }
 
+    // ---- knnGraph: MinCut::buildGraph's neighbour loop + calculateBinaryPotential (mincut.cpp:458-475,574-585) ----
+    {
+        const int k = 14; const double inv_sigma = 16.0;
+        std::vector<int> nb; std::vector<double> w;
+        CHECK(knnGraph(s, pts.data(), n, k, inv_sigma, nb, w), "knnGraph failed (%s)", s.lastError().c_str());
+        int bad_idx = 0; double worst = 0;
+        for (size_t i = 0; i < n; ++i)
+            for (int j = 0; j < k; ++j) {
+                const int t = nb[i * k + j];
+                if (t != nbrs[i][j].second) { ++bad_idx; continue; }
+                double d = 0.0;
+                d += (pts[i].x - pts[t].x) * (pts[i].x - pts[t].x);
+                d += (pts[i].y - pts[t].y) * (pts[i].y - pts[t].y);
+                d += (pts[i].z - pts[t].z) * (pts[i].z - pts[t].z);
+                const double ref = std::exp(-(d * inv_sigma));
+                worst = std::max(worst, std::fabs(w[i * k + j] - ref) / ref);
+            }
+        std::printf("knnGraph: %d neighbour mismatches, max relative weight error %.3g\n", bad_idx, worst);
+        CHECK(bad_idx == 0, "%d neighbour entries differ from the (d2, index) order", bad_idx);
+        CHECK(worst <= 1e-14, "edge weights off by %g", worst);
+    }
+
     // ---- error behaviour: empty result + message, no exception, session stays usable ----
     {
         std::vector<PointXYZI> bad(pts.begin(), pts.begin() + 100);

@@ -28,7 +28,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph",
 ]
 
 
@@ -88,6 +88,7 @@ def load_library():
     L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_shard.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, vp]
+    L.ccg_knn_graph.argtypes = [vp, i32, f64, vp, vp]
     L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.ccg_dev_free.argtypes = [vp, vp]
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
@@ -168,7 +169,7 @@ class Context:
         """allocate an output next to the inputs: torch CUDA tensor if the cloud came from one, else numpy"""
         if like_device:
             import torch
-            tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8}[dtype]
+            tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8, np.float64: torch.float64}[dtype]
             return torch.empty(shape, dtype=tdt, device=f"cuda:{self.device}")
         return np.empty(shape, dtype)
 
@@ -258,6 +259,14 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_shard(self.h, k, cov_norm, _ptr(vp), formula_set, rank, world, chunk_points,
                                                       1 if sorted_rows else 0, _addr(eig), _addr(nrm), _addr(feat)))
+
+    def knn_graph(self, k, inverse_sigma, device_out=None):
+        """kNN table + MinCut binary potentials (graphcut/mincut.cpp:458-475,574-585): (idx int32[n,k], weight float64[n,k])"""
+        dev = self.on_device if device_out is None else device_out
+        idx = self._out(dev, (self.n, k), np.int32)
+        w = self._out(dev, (self.n, k), np.float64)
+        self._check(self.L.ccg_knn_graph(self.h, k, float(inverse_sigma), _ptr(idx), _ptr(w)))
+        return idx, w
 
     def voxel_downsample(self, points, resolution, n_floats=None, as_written=True, device_out=None):
         """octreeDownsample (utils.h:16-62): points = the [n, S] float32 array given to set_cloud ->

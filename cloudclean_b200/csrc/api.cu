@@ -118,13 +118,16 @@ __global__ void __launch_bounds__(256) k_tile_minidx(const float4 *__restrict__ 
 
 struct PipeOut { OutBuf *o; size_t row_bytes; };
 
-static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, int chunks) {
+static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, int chunks, size_t *bound_out = nullptr,
+                           int *nch_out = nullptr) {
     const int nleaf = ctx->nleaf;
     const size_t n = ctx->n;
     cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
     if (chunks > 16) chunks = 16;
-    for (int c = 0; c <= 16; ++c)
+    for (int c = 0; c <= 16; ++c) {
         if (!ctx->ev_chunk[c]) CCG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_chunk[c], cudaEventDisableTiming));
+        if (!ctx->ev_copy[c]) CCG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy[c], cudaEventDisableTiming));
+    }
     // tiles ordered by their smallest original index
     const size_t stride = ((size_t)nleaf + 63) & ~(size_t)63;
     CCG_CUDA(ctx, ctx->tmp[3].reserve(stride * 16));
@@ -171,12 +174,33 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
             for (int i = 0; i < nouts; ++i)
                 CCG_CUDA(ctx, cudaMemcpyAsync((char *)outs[i].o->user + r0 * outs[i].row_bytes, (char *)outs[i].o->d + r0 * outs[i].row_bytes,
                                               (r1 - r0) * outs[i].row_bytes, cudaMemcpyDeviceToHost, cs));
+        CCG_CUDA(ctx, cudaEventRecord(ctx->ev_copy[c], cs));       // rows below bound[c + 1] are on the host after this
     }
+    if (bound_out) for (int c = 0; c <= nch; ++c) bound_out[c] = bound[c];
+    if (nch_out) *nch_out = nch;
     ctx->stats.launches = launches;
     for (int i = 0; i < nouts; ++i) outs[i].o->staged = false;          // already shipped: close() has nothing left to do
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[16], cs));
     CCG_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_chunk[16], 0));
     return CCG_OK;
+}
+
+// f3: MinCut::calculateBinaryPotential (graphcut/mincut.cpp:574-585) for every kNN edge: the three squared float
+// differences are accumulated in double, scaled by inverse_sigma and passed through exp(-x) in double.
+__global__ void __launch_bounds__(256) k_binary_potential(const float4 *__restrict__ orig, const int32_t *__restrict__ idx, size_t n, int k,
+                                                          double inverse_sigma, double *__restrict__ weight) {
+    const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * (size_t)k) return;
+    const int j = idx[e];
+    if (j < 0) { weight[e] = 0.0; return; }
+    const float4 a = orig[e / (size_t)k], b = orig[j];
+    const float dx = __fsub_rn(a.x, b.x), dy = __fsub_rn(a.y, b.y), dz = __fsub_rn(a.z, b.z);
+    double d = 0.0;
+    d += (double)__fmul_rn(dx, dx);
+    d += (double)__fmul_rn(dy, dy);
+    d += (double)__fmul_rn(dz, dz);
+    d *= inverse_sigma;
+    weight[e] = exp(-d);
 }
 
 static QueryArgs base_args(ccg_ctx *ctx) {
@@ -236,6 +260,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     for (int i = 0; i < 17; ++i) if (ctx->ev_chunk[i]) cudaEventDestroy(ctx->ev_chunk[i]);
+    for (int i = 0; i < 17; ++i) if (ctx->ev_copy[i]) cudaEventDestroy(ctx->ev_copy[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
@@ -292,6 +317,29 @@ int ccg_knn(ccg_ctx *ctx, int k, int32_t *idx, float *d2) {
     CCG_TRY(launch_tile_query(ctx, a));
     CCG_TRY(query_end(ctx));
     CCG_TRY(oi.close()); CCG_TRY(od.close());
+    return finish_call(ctx);
+}
+
+/* ---- f3: kNN graph for the graph-cut / flood consumers ------------------------------------------------- */
+int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, double *weight) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!idx || !weight) return set_error(ctx, CCG_ERR_INVALID, "idx and weight are required");
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    OutBuf oi, ow;
+    CCG_TRY(oi.open(ctx, 0, idx, n * (size_t)k * 4));
+    CCG_TRY(ow.open(ctx, 1, weight, n * (size_t)k * 8));
+    QueryArgs a = base_args(ctx);
+    a.mode = MODE_KNN; a.k = k; a.idx = oi.dev<int32_t>(); a.d2 = nullptr;
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_query(ctx, a));
+    const size_t edges = n * (size_t)k;
+    k_binary_potential<<<(unsigned)((edges + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), oi.dev<int32_t>(), n, k, inverse_sigma,
+                                                                                 ow.dev<double>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oi.close()); CCG_TRY(ow.close());
     return finish_call(ctx);
 }
 
@@ -593,16 +641,32 @@ int ccg_sor_mask(ccg_ctx *ctx, int mean_k, double stddev_mul, uint8_t *outlier, 
     QueryArgs a = base_args(ctx);
     a.mode = MODE_SOR; a.k = mean_k + 1; a.mean_k = mean_k; a.mean_d = md;
     CCG_TRY(query_begin(ctx));
-    CCG_TRY(launch_tile_query(ctx, a));
     // The threshold is a sum over all points in INDEX ORDER in fp64 (PCL StatisticalOutlierRemoval); a parallel
-    // reduction would round differently, so the n floats go to the host once and are summed sequentially there.
-    // This is the contract's arithmetic, not a fallback: the per-point work stays on the GPU.
+    // reduction would round differently, so the n floats go to the host and are summed sequentially there.
+    // This is the contract's arithmetic, not a fallback: the per-point work stays on the GPU.  On large clouds the
+    // 30-40 ms host loop hides behind the query: tiles run in order of their smallest original index, mean distances
+    // arrive in row-prefix chunks on the copy stream, and the host adds each chunk (in index order) while the GPU works
+    // on the next one.
     CCG_CUDA(ctx, ctx->hpin[0].reserve(n * 4));
-    CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, md, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const float *h = ctx->hpin[0].as<float>();
     double sum = 0.0, sq = 0.0;
-    for (size_t i = 0; i < n; ++i) { sum += (double)h[i]; sq += (double)h[i] * (double)h[i]; }
+    if (ctx->pipeline_chunks > 1 && !ctx->collect_stats && n >= (size_t)ctx->pipeline_min_points) {
+        OutBuf ob;
+        ob.ctx = ctx; ob.user = ctx->hpin[0].p; ob.bytes = n * 4; ob.d = md; ob.staged = true;
+        PipeOut po{&ob, 4};
+        size_t bound[18];
+        int nch = 0;
+        CCG_TRY(pipelined_query(ctx, a, &po, 1, ctx->pipeline_chunks, bound, &nch));
+        for (int c = 0; c < nch; ++c) {
+            CCG_CUDA(ctx, cudaEventSynchronize(ctx->ev_copy[c]));
+            for (size_t i = bound[c]; i < bound[c + 1]; ++i) { sum += (double)h[i]; sq += (double)h[i] * (double)h[i]; }
+        }
+    } else {
+        CCG_TRY(launch_tile_query(ctx, a));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, md, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        for (size_t i = 0; i < n; ++i) { sum += (double)h[i]; sq += (double)h[i] * (double)h[i]; }
+    }
     const double mu = sum / (double)n;
     const double var = n > 1 ? (sq - sum * sum / (double)n) / ((double)n - 1.0) : 0.0;
     const double thr = mu + stddev_mul * sqrt(var > 0 ? var : 0.0);

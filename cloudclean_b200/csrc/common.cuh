@@ -65,7 +65,8 @@ struct ccg_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev[8] = {};
-    cudaEvent_t ev_chunk[17] = {};       // output pipelining (created on first use)
+    cudaEvent_t ev_chunk[17] = {};
+    cudaEvent_t ev_copy[17] = {};        // D2H of chunk c done (host-side consumers, e.g. the SOR index-order sum)       // output pipelining (created on first use)
     const volatile int *cancel = nullptr;
 
     bool has_cloud = false;

@@ -210,6 +210,15 @@ int ccg_voxel_downsample(ccg_ctx *ctx, const void *points, size_t stride_bytes, 
                          int32_t *big_to_small, int64_t *n_out);
 int ccg_voxel_downsample_fetch(ccg_ctx *ctx, float *out_points);
 
+/* ---- f3: kNN graph for the serial graph consumers ---------------------------------------------------------
+ * Replaces the per-node tree queries of MinCut::buildGraph (graphcut/mincut.cpp:458-475, k = 14; the markov copy
+ * at markov/mincut.cpp:461) and hands Flood::flood (flood.cpp:313-356) a precomputed neighbour table: idx is the
+ * ccg_knn table (n*k, self first, ascending (d2, index)), weight (n*k doubles) is calculateBinaryPotential
+ * (mincut.cpp:574-585) of every edge (i, idx[i][j]): exp(-inverse_sigma * (dx*dx + dy*dy + dz*dz)) with the three float
+ * products summed in double.  The reference adds edges for j >= 1 only (:467); weight[i][0] (self) is 1.  The graph
+ * algorithms themselves stay on the CPU. */
+int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, double *weight);
+
 #ifdef __cplusplus
 }
 #endif

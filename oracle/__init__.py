@@ -214,6 +214,19 @@ def voxel_downsample(points, resolution, n_floats=None, as_written=True):
     return out[:nv].copy(), b2s
 
 
+def binary_potential(points, idx, inverse_sigma):
+    """f3 — MinCut::calculateBinaryPotential (graphcut/mincut.cpp:574-585) for every edge (i, idx[i, j]):
+    float differences and float products, summed in double, * inverse_sigma, exp(-x) in double; idx < 0 -> 0."""
+    p = _cloud(points)[:, :3]
+    idx = np.asarray(idx)
+    j = np.where(idx < 0, 0, idx)
+    d = (p[:, None, :] - p[j]).astype(np.float32)
+    sq = (d * d).astype(np.float32)
+    dist = sq[..., 0].astype(np.float64) + sq[..., 1].astype(np.float64) + sq[..., 2].astype(np.float64)
+    w = np.exp(-(dist * float(inverse_sigma)))
+    return np.where(idx < 0, 0.0, w)
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

@@ -368,7 +368,8 @@ def test_pipelined_host_outputs_are_identical(monkeypatch, shuffle, chunks):
             eig = np.full((n, 3), -7.0, np.float32); nrm = np.full((n, 4), -7.0, np.float32); feat = np.full((n, 7), -7.0, np.float32)
             ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat)
             e2, _, cnt = ctx.pca_radius(0.08, 20, device_out=False)
-            return eig, nrm, feat, e2, cnt
+            mask, md = ctx.sor_mask(12, 1.0, device_out=False)        # host sum of the mean distances rides the same chunks
+            return eig, nrm, feat, e2, cnt, mask, md
 
     monkeypatch.setenv("CCG_PIPELINE_CHUNKS", "1")
     ref = run()
@@ -381,6 +382,8 @@ def test_pipelined_host_outputs_are_identical(monkeypatch, shuffle, chunks):
     T = oracle.Tree(pts)
     ri, _ = T.knn(20)
     check_pca(ref[0], ref[1], oracle.pca_lists(pts, ri, cov_norm=1))
+    rmask, rmd, _, _ = T.sor(12, 1.0)
+    assert np.array_equal(got[5], rmask) and np.array_equal(got[6], rmd)
 
 
 # ---- f1: voxel downsample (octreeDownsample, utils.h:16-62) -------------------------------------------------
@@ -421,3 +424,19 @@ def test_voxel_downsample_xyz_only_and_errors(gpu_ctx):
         gpu_ctx.voxel_downsample(pts, 0.0, device_out=False)
     with pytest.raises(cc.CcgError):
         gpu_ctx.voxel_downsample(pts, 0.1, n_floats=4, device_out=False)      # 4 floats do not fit a 12-byte stride
+
+
+# ---- f3: kNN graph with MinCut binary potentials (graphcut/mincut.cpp:458-475, 574-585) ---------------------
+@pytest.mark.parametrize("name", ["uniform", "lattice_ties", "clusters_outliers", "n2"])
+@pytest.mark.parametrize("k,inv_sigma", [(14, 4.0), (8, 250.0)])
+def test_knn_graph(gpu_ctx, name, k, inv_sigma):
+    """Neighbour table bit-exact (same contract as ccg_knn); edge weights within 4 ulp of the numpy restatement
+    (CUDA's double exp is within 1 ulp, numpy/glibc's is correctly rounded)."""
+    pts = SMALL[name]
+    gpu_ctx.set_cloud(pts)
+    idx, w = gpu_ctx.knn_graph(k, inv_sigma, device_out=False)
+    ri, _ = oracle.Tree(pts).knn(k)
+    assert np.array_equal(idx, ri)
+    want = oracle.binary_potential(pts, ri, inv_sigma)
+    assert np.allclose(w, want, rtol=1e-15 * 4, atol=0)
+    assert np.all(w[idx[:, 0] >= 0, 0] == 1.0)          # self edge
