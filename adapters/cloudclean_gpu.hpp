@@ -13,6 +13,7 @@
 //   NormalEstimator::estimateNormals(cloud)                   src/plugins/normalestimation/normalestimation.cpp:268-470
 //   OutlierFilter::filter()  (index list handed to Select)    src/plugins/outlierfilter/outlierfilter.cpp:120-179
 //   octreeDownsample<PointT>(cloud*, resolution, sub_idxs)    src/utilities/utils.h:16-62
+//   normal_stdev<PointT,NormalT> / stdev_dist                 src/utilities/cv.h:123-206, cv.cpp:166-230
 //   MinCut::buildGraph neighbour + weight loop               src/plugins/graphcut/mincut.cpp:458-475,574-585
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
@@ -284,6 +285,26 @@ bool knnGraph(Session &s, const PointT *points, size_t n, int k, double inverse_
     if (!s.ok() || !s.setInputCloud(points, n)) return false;
     if (n == 0) return true;
     return s.check(ccg_knn_graph(s.ctx(), k, inverse_sigma, reinterpret_cast<int32_t *>(neighbours.data()), weights.data()));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// normal_stdev<PointT,NormalT> (cv.h:123-206) and stdev_dist (cv.cpp:166-230): one float per point, arithmetic and
+// quirks as written in the reference (include/ccgpu.h).  max_nn must be in [1, CCG_MAX_K].
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT, class NormalT>
+std::shared_ptr<std::vector<float>> normal_stdev(Session &s, const PointT *cloud, const NormalT *normals, size_t n, double radius, int max_nn) {
+    auto std_devs = std::make_shared<std::vector<float>>(n, 0.f);
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return std_devs;
+    if (!s.check(ccg_normal_stdev(s.ctx(), radius, max_nn, normals, sizeof(NormalT), std_devs->data()))) std_devs->assign(n, 0.f);
+    return std_devs;
+}
+template <class PointT>
+std::shared_ptr<std::vector<float>> stdev_dist(Session &s, const PointT *cloud, size_t n, double radius, int max_nn, bool use_depth = false,
+                                               const float *sensor_origin3 = nullptr) {
+    auto stdevs = std::make_shared<std::vector<float>>(n, 0.f);
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return stdevs;
+    if (!s.check(ccg_stdev_dist(s.ctx(), radius, max_nn, use_depth ? 1 : 0, sensor_origin3, stdevs->data()))) stdevs->assign(n, 0.f);
+    return stdevs;
 }
 
 }  // namespace ccgpu

@@ -318,6 +318,34 @@ int main() {
         CHECK(worst <= 1e-14, "edge weights off by %g", worst);
     }
 
+    // ---- stdev_dist (cv.cpp:166-230): variance of neighbour distances, inclusive radius, float sums in (d2, index) order ----
+    {
+        const double radius = 0.15; const int max_nn = 32;
+        auto got = stdev_dist(s, pts.data(), n, radius, max_nn);
+        const double r2 = radius * radius;
+        int bad = 0;
+        for (size_t i = 0; i < n && got->size() == n; ++i) {
+            float sum = 0.f, sum_sq = 0.f; int m = 0;
+            for (auto &c : nbrs[i]) {
+                if (!((double)c.first <= r2) || m == max_nn) break;
+                const PointXYZI &p = pts[c.second];
+                volatile float dx = p.x - pts[i].x, dy = p.y - pts[i].y, dz = p.z - pts[i].z;
+                volatile float xx = dx * dx, yy = dy * dy, zz = dz * dz;
+                volatile float ss = xx + yy; ss = ss + zz;
+                volatile float dist = std::sqrt((float)ss);
+                sum = sum + dist;
+                volatile float d2v = dist * dist;
+                sum_sq = sum_sq + d2v;
+                ++m;
+            }
+            volatile float s2 = sum * sum; volatile float q = s2 / (float)m; volatile float num = sum_sq - q;
+            const float want = m > 2 ? num / ((float)m - 1.f) : 0.f;
+            if (want != (*got)[i]) ++bad;
+        }
+        std::printf("stdev_dist: %d of %zu differ\n", bad, n);
+        CHECK(bad == 0, "stdev_dist differs at %d points", bad);
+    }
+
     // ---- error behaviour: empty result + message, no exception, session stays usable ----
     {
         std::vector<PointXYZI> bad(pts.begin(), pts.begin() + 100);

@@ -28,7 +28,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist",
 ]
 
 
@@ -89,6 +89,8 @@ def load_library():
     L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_shard.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, vp]
     L.ccg_knn_graph.argtypes = [vp, i32, f64, vp, vp]
+    L.ccg_normal_stdev.argtypes = [vp, f64, i32, vp, sz, vp]
+    L.ccg_stdev_dist.argtypes = [vp, f64, i32, i32, vp, vp]
     L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.ccg_dev_free.argtypes = [vp, vp]
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
@@ -259,6 +261,22 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_shard(self.h, k, cov_norm, _ptr(vp), formula_set, rank, world, chunk_points,
                                                       1 if sorted_rows else 0, _addr(eig), _addr(nrm), _addr(feat)))
+
+    def normal_stdev(self, r, max_nn, normals, device_out=None):
+        """normal_stdev (cv.h:123-206): normals = [n, S>=3] float32 (host numpy or torch CUDA) -> float32[n]"""
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n,), np.float32)
+        stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
+        self._check(self.L.ccg_normal_stdev(self.h, float(r), max_nn, _ptr(normals), stride, _ptr(out)))
+        return out
+
+    def stdev_dist(self, r, max_nn, use_depth=False, centre=None, device_out=None):
+        """stdev_dist (cv.cpp:166-230) -> float32[n]"""
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n,), np.float32)
+        c = None if centre is None else np.ascontiguousarray(centre, np.float32)
+        self._check(self.L.ccg_stdev_dist(self.h, float(r), max_nn, 1 if use_depth else 0, _ptr(c), _ptr(out)))
+        return out
 
     def knn_graph(self, k, inverse_sigma, device_out=None):
         """kNN table + MinCut binary potentials (graphcut/mincut.cpp:458-475,574-585): (idx int32[n,k], weight float64[n,k])"""

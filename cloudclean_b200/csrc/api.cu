@@ -203,6 +203,61 @@ __global__ void __launch_bounds__(256) k_binary_potential(const float4 *__restri
     weight[e] = exp(-d);
 }
 
+// f2: epilogues over capped radius neighbour lists (rows of `k` original indices, ascending (d2, index), `count` valid).
+// normal_stdev (cv.h:123-206), arithmetic as written there: cosine = dot / |neighbour| * |current| (sic, precedence),
+// clamp to [0,1], angle = float(acosf(cosine) / M_PI) [double division], float sums in neighbour order,
+// std = float(sqrt(double(sumsq / m) - pow(double(sum / m), 2))); NaN normals, < 3 neighbours and NaN results give 0.
+__global__ void __launch_bounds__(256) k_normal_stdev(const int32_t *__restrict__ idx, const int32_t *__restrict__ count, size_t n, int k,
+                                                      const char *__restrict__ normals, size_t stride, float *__restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *cur = reinterpret_cast<const float *>(normals + i * stride);
+    const float cx = cur[0], cy = cur[1], cz = cur[2];
+    const int m = count[i];
+    float res = 0.f;
+    if (cx == cx && m >= 3) {
+        const float cn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(cx, cx), __fmul_rn(cy, cy)), __fmul_rn(cz, cz)));
+        float sum = 0.f, sumsq = 0.f;
+        for (int j = 0; j < m; ++j) {
+            const float *nb = reinterpret_cast<const float *>(normals + (size_t)idx[i * k + j] * stride);
+            const float x = nb[0], y = nb[1], z = nb[2];
+            const float dot = __fadd_rn(__fadd_rn(__fmul_rn(x, cx), __fmul_rn(y, cy)), __fmul_rn(z, cz));
+            const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+            float cosine = __fmul_rn(__fdiv_rn(dot, nn), cn);
+            cosine = cosine < 0.f ? 0.f : (cosine > 1.f ? 1.f : cosine);
+            const float angle = (float)((double)acosf(cosine) / 3.14159265358979323846);
+            sum = __fadd_rn(sum, angle);
+            sumsq = __fadd_rn(sumsq, __fmul_rn(angle, angle));
+        }
+        const float fm = (float)m;
+        const double mean = (double)__fdiv_rn(sum, fm);
+        const float sd = (float)sqrt((double)__fdiv_rn(sumsq, fm) - mean * mean);
+        if (sd == sd) res = sd;
+    }
+    out[i] = res;
+}
+// stdev_dist (cv.cpp:166-230): float sums of the neighbour distances (to the query, or to `centre` when use_depth),
+// result = (sum_sq - sum*sum/m) / (m-1) for m > 2 else 0 — a VARIANCE despite the name, kept as written.
+__global__ void __launch_bounds__(256) k_stdev_dist(const float4 *__restrict__ orig, const int32_t *__restrict__ idx,
+                                                    const int32_t *__restrict__ count, size_t n, int k, int use_depth, float3 centre,
+                                                    float *__restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int m = count[i];
+    const float4 q = orig[i];
+    const float rx = use_depth ? centre.x : q.x, ry = use_depth ? centre.y : q.y, rz = use_depth ? centre.z : q.z;
+    float sum = 0.f, sumsq = 0.f;
+    for (int j = 0; j < m; ++j) {
+        const float4 p = orig[idx[i * k + j]];
+        const float dx = __fsub_rn(p.x, rx), dy = __fsub_rn(p.y, ry), dz = __fsub_rn(p.z, rz);
+        const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        sum = __fadd_rn(sum, dist);
+        sumsq = __fadd_rn(sumsq, __fmul_rn(dist, dist));
+    }
+    const float fm = (float)m;
+    out[i] = m > 2 ? __fdiv_rn(__fsub_rn(sumsq, __fdiv_rn(__fmul_rn(sum, sum), fm)), __fsub_rn(fm, 1.f)) : 0.f;
+}
+
 static QueryArgs base_args(ccg_ctx *ctx) {
     QueryArgs a{};
     a.rb = INFINITY; a.begin = 0; a.end = ctx->n; a.sorted_rows = 0;
@@ -340,6 +395,66 @@ int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, doubl
     ctx->stats.launches++;
     CCG_TRY(query_end(ctx));
     CCG_TRY(oi.close()); CCG_TRY(ow.close());
+    return finish_call(ctx);
+}
+
+/* ---- f2: radius-neighbourhood reductions ------------------------------------------------------------------ */
+static int radius_lists_internal(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t **idx, int32_t **count) {
+    if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+    if (max_nn < 1 || max_nn > CCG_MAX_K)
+        return set_error(ctx, CCG_ERR_UNSUPPORTED, "this reduction needs a neighbour cap 1 <= max_nn <= %d (got %d)", CCG_MAX_K, max_nn);
+    const size_t n = ctx->n;
+    CCG_CUDA(ctx, ctx->tmp[2].reserve(n * (size_t)max_nn * 4 + 64));
+    CCG_CUDA(ctx, ctx->tmp[0].reserve(n * 4 + 64));
+    *idx = ctx->tmp[2].as<int32_t>();
+    *count = ctx->tmp[0].as<int32_t>();
+    QueryArgs a = base_args(ctx);
+    a.mode = MODE_KNN; a.k = max_nn; a.rb = radius_bound(r, strict_lt); a.idx = *idx; a.d2 = nullptr; a.count = *count;
+    return launch_tile_query(ctx, a);
+}
+
+int ccg_normal_stdev(ccg_ctx *ctx, double r, int max_nn, const void *normals, size_t stride_bytes, float *out) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!normals || !out) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (stride_bytes < 12 || (stride_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "stride_bytes must be >= 12 and a multiple of 4");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *nd = normals;
+    if (!is_dev(ctx, normals)) {
+        const size_t bytes = (n - 1) * stride_bytes + 12;
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, normals, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        nd = ctx->tmp[1].p;
+    }
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, out, n * 4));
+    CCG_TRY(query_begin(ctx));
+    int32_t *idx, *cnt;
+    CCG_TRY(radius_lists_internal(ctx, r, max_nn, 1, &idx, &cnt));
+    k_normal_stdev<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(idx, cnt, n, max_nn, (const char *)nd, stride_bytes, oo.dev<float>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
+int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const float *centre3, float *out) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!out) return set_error(ctx, CCG_ERR_INVALID, "out is NULL");
+    if (use_depth && !centre3) return set_error(ctx, CCG_ERR_INVALID, "use_depth needs the sensor origin");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, out, n * 4));
+    CCG_TRY(query_begin(ctx));
+    int32_t *idx, *cnt;
+    CCG_TRY(radius_lists_internal(ctx, r, max_nn, 0, &idx, &cnt));
+    const float3 c = centre3 ? make_float3(centre3[0], centre3[1], centre3[2]) : make_float3(0.f, 0.f, 0.f);
+    k_stdev_dist<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), idx, cnt, n, max_nn, use_depth ? 1 : 0, c,
+                                                                       oo.dev<float>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
     return finish_call(ctx);
 }
 

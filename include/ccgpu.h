@@ -219,6 +219,21 @@ int ccg_voxel_downsample_fetch(ccg_ctx *ctx, float *out_points);
  * algorithms themselves stay on the CPU. */
 int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, double *weight);
 
+/* ---- f2: radius-neighbourhood reductions (same search as a2/a3, different epilogue) ------------------------
+ * Both need a neighbour cap 1 <= max_nn <= CCG_MAX_K (featureeval's default is 20, featureeval.cpp:67-68): the
+ * max_nn nearest inside the radius, visited in ascending (d2, index) order.  Arithmetic and quirks are kept as written.
+ * ccg_normal_stdev — normal_stdev<PointT,NormalT> (cv.h:123-206): per point the standard deviation of the normalised
+ *   angle acos(clamp(cos,0,1))/pi between its normal and its neighbours' normals (strict kd-tree radius); `normals` is an
+ *   array of structs whose first three floats are the normal (pcl::Normal: stride 32), host or device, indexed like the
+ *   cloud.  0 for NaN normals, fewer than 3 neighbours and NaN results.  The reference's cosine is
+ *   dot / |neighbour| * |current| (operator precedence, cv.h:181-182) and is reproduced.
+ * ccg_stdev_dist — stdev_dist (cv.cpp:166-230): per point (sum_sq - sum^2/m)/(m-1) of the distances from its
+ *   neighbours (inclusive octree radius) to the point itself, or to centre3 (the sensor origin) when use_depth — a
+ *   variance despite the name (cv.cpp:222-223).  The octree's own cap keeps the first max_nn points in traversal
+ *   order [EXT]; here the cap keeps the nearest, so results agree with the reference wherever the cap does not bind. */
+int ccg_normal_stdev(ccg_ctx *ctx, double r, int max_nn, const void *normals, size_t stride_bytes, float *out);
+int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const float *centre3, float *out);
+
 #ifdef __cplusplus
 }
 #endif

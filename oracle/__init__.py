@@ -227,6 +227,61 @@ def binary_potential(points, idx, inverse_sigma):
     return np.where(idx < 0, 0.0, w)
 
 
+def normal_stdev(points, normals, r, max_nn):
+    """f2 — normal_stdev (cv.h:123-206) as written: strict radius, the max_nn nearest in ascending (d2, index) order,
+    cosine = dot / |neighbour| * |current| (sic), clamp, angle = float(acosf / pi [double]), float sums in neighbour
+    order, std = float(sqrt(double(sumsq/m) - double(sum/m)^2)); 0 for NaN normals, < 3 neighbours, NaN results."""
+    F = np.float32
+    pts = _cloud(points)
+    nr = np.ascontiguousarray(normals, dtype=F)[:, :3]
+    res = Tree(pts).radius(r, cap=max_nn, strict_lt=True)
+    idx, cnt = res["idx"], res["count"]
+    n = pts.shape[0]
+    cur = nr
+    with np.errstate(all="ignore"):
+        cn = np.sqrt(((cur[:, 0] * cur[:, 0]).astype(F) + (cur[:, 1] * cur[:, 1]).astype(F)).astype(F) + (cur[:, 2] * cur[:, 2]).astype(F)).astype(F)
+        s = np.zeros(n, F); sq = np.zeros(n, F)
+        for j in range(max_nn):
+            live = j < cnt
+            nb = nr[np.where(live, idx[:, j], 0)]
+            dot = (((nb[:, 0] * cur[:, 0]).astype(F) + (nb[:, 1] * cur[:, 1]).astype(F)).astype(F) + (nb[:, 2] * cur[:, 2]).astype(F)).astype(F)
+            nn = np.sqrt(((nb[:, 0] * nb[:, 0]).astype(F) + (nb[:, 1] * nb[:, 1]).astype(F)).astype(F) + (nb[:, 2] * nb[:, 2]).astype(F)).astype(F)
+            cosine = ((dot / nn).astype(F) * cn).astype(F)
+            cosine = np.where(cosine < 0, F(0), np.where(cosine > 1, F(1), cosine)).astype(F)       # clamp(): NaN passes through
+            angle = (np.arccos(cosine).astype(F).astype(np.float64) / np.pi).astype(F)
+            s = np.where(live, (s + angle).astype(F), s)
+            sq = np.where(live, (sq + (angle * angle).astype(F)).astype(F), sq)
+        m = cnt.astype(F)
+        mean = (s / m).astype(F).astype(np.float64)
+        sd = np.sqrt((sq / m).astype(F).astype(np.float64) - mean * mean).astype(F)
+    out = np.where((cur[:, 0] == cur[:, 0]) & (cnt >= 3) & (sd == sd), sd, F(0)).astype(F)
+    return out
+
+
+def stdev_dist(points, r, max_nn, use_depth=False, centre=None):
+    """f2 — stdev_dist (cv.cpp:166-230) as written: inclusive radius, the max_nn nearest (see include/ccgpu.h on the
+    octree's own cap), float sums of |p - q| (or |p - centre|), (sum_sq - sum^2/m)/(m-1) for m > 2 else 0."""
+    F = np.float32
+    pts = _cloud(points)
+    xyz = pts[:, :3]
+    res = Tree(pts).radius(r, cap=max_nn, strict_lt=False)
+    idx, cnt = res["idx"], res["count"]
+    n = pts.shape[0]
+    ref = np.broadcast_to(np.asarray(centre, F), (n, 3)) if use_depth else xyz
+    s = np.zeros(n, F); sq = np.zeros(n, F)
+    for j in range(max_nn):
+        live = j < cnt
+        p = xyz[np.where(live, idx[:, j], 0)]
+        d = (p - ref).astype(F)
+        dist = np.sqrt(((d[:, 0] * d[:, 0]).astype(F) + (d[:, 1] * d[:, 1]).astype(F)).astype(F) + (d[:, 2] * d[:, 2]).astype(F)).astype(F)
+        s = np.where(live, (s + dist).astype(F), s)
+        sq = np.where(live, (sq + (dist * dist).astype(F)).astype(F), sq)
+    m = cnt.astype(F)
+    with np.errstate(all="ignore"):
+        var = ((sq - ((s * s).astype(F) / m).astype(F)).astype(F) / (m - F(1)).astype(F)).astype(F)
+    return np.where(cnt > 2, var, F(0)).astype(F)
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

@@ -440,3 +440,51 @@ def test_knn_graph(gpu_ctx, name, k, inv_sigma):
     want = oracle.binary_potential(pts, ri, inv_sigma)
     assert np.allclose(w, want, rtol=1e-15 * 4, atol=0)
     assert np.all(w[idx[:, 0] >= 0, 0] == 1.0)          # self edge
+
+
+# ---- f2: radius-neighbourhood reductions (cv.h:123-206, cv.cpp:166-230) --------------------------------------
+def _scan_with_normals():
+    scan = synth.make_scan_np(100, 80, scene="room", seed=6)
+    pts = np.ascontiguousarray(scan["points"])
+    rng = np.random.default_rng(12)
+    nrm = np.zeros((pts.shape[0], 8), np.float32)                 # pcl::Normal layout, stride 32
+    v = rng.normal(size=(pts.shape[0], 3)).astype(np.float32)
+    v[:, 2] += 3.0                                                # mostly "up", with spread
+    nrm[:, :3] = v / np.linalg.norm(v, axis=1, keepdims=True).astype(np.float32)
+    nrm[::97, :3] = np.nan                                        # the NaN islands the reference skips (cv.h:161-162)
+    return pts, nrm
+
+
+@pytest.mark.parametrize("r,max_nn", [(0.1, 20), (0.3, 64), (0.02, 8)])
+def test_normal_stdev(gpu_ctx, r, max_nn):
+    """Same neighbour lists as the oracle (bit-exact search); the reduction is fp32 as written — acosf differs by an ulp
+    between CUDA and glibc and sqrt(a - b) amplifies that near 0, so the VARIANCE is compared (1e-6 absolute)."""
+    pts, nrm = _scan_with_normals()
+    gpu_ctx.set_cloud(pts)
+    got = gpu_ctx.normal_stdev(r, max_nn, nrm, device_out=False)
+    want = oracle.normal_stdev(pts, nrm, r, max_nn)
+    assert got.shape == want.shape
+    assert np.all(got[::97] == 0)                                 # NaN normal -> skipped -> 0
+    assert np.abs(got.astype(np.float64) ** 2 - want.astype(np.float64) ** 2).max() <= 1e-6
+    if r >= 0.3:
+        assert (want > 0).sum() > want.size // 4
+
+
+@pytest.mark.parametrize("r,max_nn", [(0.1, 20), (0.25, 64)])
+@pytest.mark.parametrize("use_depth", [False, True])
+def test_stdev_dist(gpu_ctx, r, max_nn, use_depth):
+    pts, _ = _scan_with_normals()
+    gpu_ctx.set_cloud(pts)
+    centre = np.array([0.1, -0.2, 0.3], np.float32)
+    got = gpu_ctx.stdev_dist(r, max_nn, use_depth, centre, device_out=False)
+    want = oracle.stdev_dist(pts, r, max_nn, use_depth, centre)
+    assert np.array_equal(got, want)       # fp32 +,*,/,sqrt in the same order on both sides: identical bits
+
+
+def test_reductions_reject_uncapped(gpu_ctx):
+    pts, nrm = _scan_with_normals()
+    gpu_ctx.set_cloud(pts)
+    with pytest.raises(cc.CcgError):
+        gpu_ctx.normal_stdev(0.1, 0, nrm, device_out=False)
+    with pytest.raises(cc.CcgError):
+        gpu_ctx.stdev_dist(0.1, 1000, device_out=False)
