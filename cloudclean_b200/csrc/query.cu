@@ -839,7 +839,7 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
 }
 
 template <int K, int MODE>
-__global__ void __launch_bounds__(64, 10) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+__global__ void __launch_bounds__(64, (K > 32 ? 6 : 10)) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
     constexpr int CAP = MODE != MODE_SOR ? LogCap<K>::value : 1;
     constexpr bool LOG = MODE != MODE_SOR;
     __shared__ WarpScratch3<CAP> s_ws[2];
