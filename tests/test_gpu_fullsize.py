@@ -1,0 +1,149 @@
+"""Parity at BASELINE.json's full sizes (30 M-point config 3, 10 M-point config 2), where the oracle cannot run on the
+whole cloud in seconds: size-independent properties on the complete output, plus an EXACT oracle comparison on a
+spatial sub-box (a query whose k-th neighbour is closer than the box wall has the same neighbours in the sub-cloud
+as in the full cloud, so the oracle on the sub-cloud is the oracle on the full cloud for those queries)."""
+import numpy as np
+import pytest
+
+import cloudclean_b200 as cc
+import oracle
+from cloudclean_b200 import sharding, synth
+
+pytestmark = pytest.mark.gpu
+K = 20
+
+
+def _subbox(pts_t, lo, hi):
+    """indices (torch, ascending) of the points inside the axis-aligned box"""
+    import torch
+    m = ((pts_t[:, 0] >= lo[0]) & (pts_t[:, 0] <= hi[0]) & (pts_t[:, 1] >= lo[1]) & (pts_t[:, 1] <= hi[1])
+         & (pts_t[:, 2] >= lo[2]) & (pts_t[:, 2] <= hi[2]))
+    return torch.nonzero(m).squeeze(1)
+
+
+def _pick_box(pts_t, seed_index, lo_count=20_000, hi_count=300_000):
+    """a cube around point `seed_index`, grown until it holds between lo_count and hi_count points -> (sel, c, half)"""
+    c = pts_t[seed_index, :3].clone()
+    half = 0.05
+    for _ in range(14):
+        sel = _subbox(pts_t, (c - half).tolist(), (c + half).tolist())
+        if sel.numel() >= lo_count:
+            break
+        half *= 1.5
+    if sel.numel() < 2000 or sel.numel() > hi_count:
+        return None, c, half
+    return sel, c, half
+
+
+@pytest.fixture(scope="module")
+def scan30():
+    import torch
+    if torch.cuda.get_device_properties(0).total_memory < 40e9:
+        pytest.skip("needs a large-memory GPU")
+    s = synth.config_scan(3, device="cuda")
+    pts = s["points"].contiguous()
+    ctx = cc.Context(0)
+    ctx.set_cloud(pts)
+    yield pts, ctx
+    ctx.close()
+
+
+def test_full_size_pca_properties_and_shard_identity(scan30):
+    import torch
+    pts, ctx = scan30
+    n = pts.shape[0]
+    assert n > 29_000_000
+    eig = torch.empty((n, 3), device="cuda"); nrm = torch.empty((n, 4), device="cuda"); feat = torch.empty((n, 7), device="cuda")
+    ctx.pca_knn_features_into(K, cc.COV_NM1, 0, eig, nrm, feat)
+    # eigenvalues: finite, descending, non-negative up to fp32 noise relative to lambda0
+    assert torch.isfinite(eig).all()
+    assert (eig[:, 0] >= eig[:, 1]).all() and (eig[:, 1] >= eig[:, 2]).all()
+    assert (eig[:, 2] >= -1e-6 * eig[:, 0]).all()
+    # normals: unit length; curvature = l2 / (l0+l1+l2) in [0, 1/3]
+    ln = torch.linalg.vector_norm(nrm[:, :3].double(), dim=1)
+    assert (ln - 1).abs().max().item() <= 1e-5
+    assert (nrm[:, 3] >= -1e-6).all() and (nrm[:, 3] <= 1 / 3 + 1e-6).all()
+    cur = (eig[:, 2] / eig.sum(1)).clamp(min=0)
+    assert (nrm[:, 3] - cur).abs().max().item() <= 1e-5
+    # fused features = standalone features of the same eigenvalues
+    assert torch.equal(ctx.features(eig).view(torch.int32), feat.view(torch.int32))
+    # every way of cutting the job gives the same bits: 3 interleaved shards, and 4 contiguous Morton ranges
+    rows = sharding.PeerRows(ctx, n, (3, 4, 7))
+    for r in range(3):
+        ctx.pca_knn_features_shard(K, cc.COV_NM1, 0, r, 3, *rows.bufs)
+    for a, b_ in zip((eig, nrm, feat), rows.bufs):
+        assert torch.equal(a.view(torch.int32), b_.tensor("cuda:0").view(torch.int32))
+    for b_ in rows.bufs:
+        b_.tensor("cuda:0").zero_()
+    torch.cuda.synchronize()          # torch's stream and the ctx's own (non-blocking) stream are not ordered
+    for r in range(4):
+        b, e, _ = sharding.shard_range(n, r, 4)
+        ctx.pca_knn_features_scatter(K, cc.COV_NM1, 0, b, e, *rows.bufs)
+    for a, b_ in zip((eig, nrm, feat), rows.bufs):
+        assert torch.equal(a.view(torch.int32), b_.tensor("cuda:0").view(torch.int32))
+    rows.close()
+
+
+def test_full_size_knn_exact_on_a_subbox(scan30):
+    """kNN lists of the 30 M-point cloud, bit-exact against the oracle for every query of a sub-box whose k-th neighbour
+    is closer than the box wall (tens of thousands of queries, walls + vegetation)."""
+    import torch
+    pts, ctx = scan30
+    n = pts.shape[0]
+    idx, d2 = ctx.knn(K)
+    # structural properties on all 30 M rows
+    assert (d2[:, 1:] >= d2[:, :-1]).all()
+    assert (d2[:, 0] == 0).all()
+    assert (idx >= 0).all() and (idx < n).all()
+    same = d2[:, 1:] == d2[:, :-1]
+    assert (~same | (idx[:, 1:] > idx[:, :-1])).all()            # ties ordered by index
+    checked = 0
+    for seed_index in (n // 7, n // 2, (5 * n) // 6, n - 12345):
+        sel, c, half = _pick_box(pts, seed_index)
+        if sel is None:
+            continue
+        sub = pts[sel].cpu().numpy()
+        ri, rd = oracle.Tree(sub).knn(K)
+        # distance from each sub-cloud point to the nearest wall of the box
+        wall = torch.minimum(pts[sel, :3] - (c - half), (c + half) - pts[sel, :3]).min(1).values.cpu().numpy()
+        interior = rd[:, K - 1] < (wall.astype(np.float64) ** 2) * 0.999
+        assert interior.sum() > 500
+        gi = idx[sel].cpu().numpy()[interior]
+        gd = d2[sel].cpu().numpy()[interior]
+        sel_np = sel.cpu().numpy()
+        assert np.array_equal(gi, sel_np[ri[interior]])           # sub-cloud index -> full-cloud index (sel is ascending)
+        assert np.array_equal(gd, rd[interior])
+        checked += int(interior.sum())
+    assert checked > 5000
+
+
+def test_config2_sor_mask_at_full_size():
+    """10 M-point config 2, SOR(k=30, 1 sigma): the mask must equal the contract's arithmetic applied to the returned
+    mean distances (index-order fp64 sums on the host), and the mean distances must be exact on a sub-box."""
+    import torch
+    s = synth.config_scan(2, device="cuda")
+    pts = s["points"].contiguous()
+    n = pts.shape[0]
+    assert n > 9_000_000
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        mask, md = ctx.sor_mask(30, 1.0)
+    h = md.cpu().numpy()
+    d = h.astype(np.float64)
+    # sequential fp64 sums in index order (math.fsum would be a different contract)
+    sm = float(np.add.accumulate(d)[-1]); sq = float(np.add.accumulate(d * d)[-1])
+    mu = sm / n
+    var = (sq - sm * sm / n) / (n - 1.0)
+    thr = mu + 1.0 * np.sqrt(var)
+    assert np.array_equal(mask.cpu().numpy().astype(bool), d > thr)
+    assert 0 < int(mask.sum()) < n // 5
+    sel, c, half = _pick_box(pts, n // 3)
+    assert sel is not None
+    if True:
+        sub = pts[sel].cpu().numpy()
+        _, rmd, _, _ = oracle.Tree(sub).sor(30, 1.0)
+        ri, rd = oracle.Tree(sub).knn(31)
+        wall = torch.minimum(pts[sel, :3] - (c - half), (c + half) - pts[sel, :3]).min(1).values.cpu().numpy()
+        interior = rd[:, 30] < (wall.astype(np.float64) ** 2) * 0.999
+        assert interior.sum() > 500
+        assert np.array_equal(h[sel.cpu().numpy()][interior], rmd[interior])

@@ -25,6 +25,7 @@ def test_scatter_ranges_fill_the_full_result():
         rows = sharding.PeerRows(ctx, n, (3, 4, 7))
         for b_ in rows.bufs:
             b_.tensor("cuda:0").fill_(-5.0)
+        torch.cuda.synchronize()      # torch's stream and the ctx's own (non-blocking) stream are not ordered
         world = 3
         for r in range(world):
             b, e, _ = sharding.shard_range(n, r, world)
@@ -67,6 +68,7 @@ def test_interleaved_shards_fill_the_full_result(world, chunk):
         rows = sharding.PeerRows(ctx, n, (3, 4, 7))
         for b_ in rows.bufs:
             b_.tensor("cuda:0").fill_(-5.0)
+        torch.cuda.synchronize()      # torch's stream and the ctx's own (non-blocking) stream are not ordered
         for r in range(world):
             ctx.pca_knn_features_shard(20, cc.COV_NM1, 0, r, world, *rows.bufs, chunk_points=chunk)
         got = [b_.tensor("cuda:0").clone() for b_ in rows.bufs]
