@@ -8,7 +8,7 @@ One step = one pass of the hot path over the scan through the C ABI of libccgpu.
 N = 1 : `value` = points / step time with the scan ALREADY RESIDENT in HBM (device pointers in, device
         pointers out); `e2e` = the same calls with pinned HOST buffers (H2D of the 32-byte PointXYZI AoS and
         D2H of every output inside the timed region).
-N > 1 : one process per GPU (torchrun).  Rank 0 owns the scan; each step broadcasts it over NCCL, every rank
+N > 1 : one process per GPU (torchrun).  Rank 0 owns the scan; each step broadcasts its xyz(w) (16 B/point) over NCCL, every rank
         builds the identical Morton order, answers its own contiguous range of the sorted order and stores the
         per-point rows, in original order, directly into rank 0's output arrays through NVLink peer memory from
         inside the query kernel (ccg_pca_knn_features_scatter; one 1-element all_reduce as completion barrier) —
@@ -230,8 +230,7 @@ def main():
         nt = torch.tensor([n], device=dev, dtype=torch.int64)
         dist.broadcast(nt, 0)
         n = int(nt.item())
-        if rank != 0:
-            pts = torch.empty((n, 8), device=dev, dtype=torch.float32)
+        pack = torch.empty((n, 4), device=dev, dtype=torch.float32)     # what is replicated: xyz(w), 16 B/point
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
@@ -275,10 +274,12 @@ def main():
         else:
             eb0 = torch.cuda.Event(enable_timing=True); eb1 = torch.cuda.Event(enable_timing=True)
             eb0.record(stream)
-            dist.broadcast(pts, 0)
+            if rank == 0:
+                pack.copy_(pts[:, :4])             # x y z 1 of every PointXYZI: the search needs nothing else
+            dist.broadcast(pack, 0)                # 16 B/point over NVLink instead of the 32-byte struct
             eb1.record(stream)
             bcast_ev.append((eb0, eb1))
-            ctx.set_cloud(pts)
+            ctx.set_cloud(pack)
             launches[0] += ctx.stats()["launches_build"]
             # every rank answers its interleaved share of the Morton order (8192-point chunks, round robin) and stores the rows, in original order, straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
