@@ -178,6 +178,14 @@ class Context:
     def set_stream(self, cuda_stream):
         """run later calls on `cuda_stream` (an int cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream); None = own"""
         self._check(self.L.ccg_set_stream(self.h, C.c_void_p(cuda_stream) if cuda_stream else None))
+        self._own_stream = not cuda_stream
+
+    def _settle(self, *tensors):
+        """The ctx's own stream is non-blocking, i.e. NOT ordered after torch's streams: when a torch CUDA tensor is an
+        INPUT and no shared stream was set, wait for torch's current stream so pending writes to it have landed."""
+        if getattr(self, "_own_stream", True) and any(_is_torch(t) and t.is_cuda for t in tensors):
+            import torch
+            torch.cuda.current_stream(self.device).synchronize()
 
     # ---- cloud -------------------------------------------------------------------------------------
     def set_cloud(self, points):
@@ -194,6 +202,7 @@ class Context:
             assert points.ndim == 2 and points.shape[1] >= 3
             n, stride = points.shape[0], points.strides[0]
             self.on_device = False
+        self._settle(points)
         self._check(self.L.ccg_set_cloud(self.h, _ptr(points), n, stride))
         self.n = n
         return self
@@ -267,6 +276,7 @@ class Context:
         dev = self.on_device if device_out is None else device_out
         out = self._out(dev, (self.n,), np.float32)
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
+        self._settle(normals)
         self._check(self.L.ccg_normal_stdev(self.h, float(r), max_nn, _ptr(normals), stride, _ptr(out)))
         return out
 
@@ -294,6 +304,7 @@ class Context:
         dev = self.on_device if device_out is None else device_out
         b2s = self._out(dev, (self.n,), np.int32)
         nv = C.c_int64(0)
+        self._settle(points)
         self._check(self.L.ccg_voxel_downsample(self.h, _ptr(points), stride, nf, float(resolution), 1 if as_written else 0,
                                                 _ptr(b2s), C.byref(nv)))
         out = self._out(dev, (nv.value, nf), np.float32)
@@ -340,6 +351,7 @@ class Context:
     def features(self, eig3, formula_set=0):
         n = eig3.shape[0]
         out = self._out(_is_torch(eig3) and eig3.is_cuda, (n, 7), np.float32)
+        self._settle(eig3)
         self._check(self.L.ccg_features(self.h, _ptr(eig3), n, formula_set, _ptr(out)))
         return out
 
@@ -388,4 +400,5 @@ class Context:
             row_bytes = (rows_sorted.shape[1] if rows_sorted.dim() == 2 else 1) * rows_sorted.element_size()
         else:
             row_bytes = (rows_sorted.shape[1] if rows_sorted.ndim == 2 else 1) * rows_sorted.itemsize
+        self._settle(rows_sorted)
         self._check(self.L.ccg_unpermute(self.h, _ptr(rows_sorted), row_bytes, _ptr(rows_original)))
