@@ -571,12 +571,11 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 // with one lane per child box then lists every leaf whose box is within the warp's largest bound of the tile
 // box (ballot + popc compaction into shared memory).  Compared with the nearest-first stack walk this costs a
 // few hundred instructions per tile instead of ~100 per visited child, and pass 2 re-uses the list.
-constexpr int kListCap = 512;     // leaves listed per tile (overflow -> stack walk, exact as well)
+constexpr int kListCap = 384;     // leaves listed per tile (overflow -> stack walk, exact as well)
 constexpr int kQueueCap = 128;     // inner nodes per level
 struct WarpScratch2 {
     WarpScratch ws;
     int list[kListCap];
-    int queue[2][kQueueCap];
     float4 sub[16];
 };
 
@@ -585,17 +584,17 @@ struct WarpScratch2 {
 // of 4 consecutive lanes each with that group's own largest bound (w.sub[2g], w.sub[2g+1].w = bound).
 template <bool SUB>
 __device__ __forceinline__ int collect_leaves(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, float rmax,
-                                              WarpScratch2 &w) {
+                                              WarpScratch2 &w, int (*queue)[kQueueCap]) {
     const int lane = threadIdx.x & 31;
     const int top = T.nlevels - 1;
     if (top == 0) return 0;
-    if (lane == 0) w.queue[0][0] = 0;
+    if (lane == 0) queue[0][0] = 0;
     __syncwarp();
     int cur = 0, ncur = 1, nlist = 0;
     for (int lv = top; lv >= 1; --lv) {
         int nnext = 0;
         for (int i = 0; i < ncur; ++i) {
-            const int node = w.queue[cur][i];
+            const int node = queue[cur][i];
             const int c = (node << 5) + lane;
             bool pass = false;
             if (c < T.count[lv - 1]) {
@@ -617,7 +616,7 @@ __device__ __forceinline__ int collect_leaves(const TreeView &T, int tile, const
                 if (pass && nlist + before < kListCap) w.list[nlist + before] = c;
                 nlist += __popc(m);
             } else {
-                if (pass && nnext + before < kQueueCap) w.queue[cur ^ 1][nnext + before] = c;
+                if (pass && nnext + before < kQueueCap) queue[cur ^ 1][nnext + before] = c;
                 nnext += __popc(m);
             }
         }
@@ -720,7 +719,10 @@ template <int CAP>
 struct WarpScratch3 {
     WarpScratch2 w;
     float4 rel[kLeaf];    // staged leaf relative to the tile centre: (P, |P|^2)
-    unsigned short log[CAP * 32];
+    union {               // the breadth-first queues are only live inside collect_leaves, which runs before the first log entry
+        unsigned short log[CAP * 32];
+        int queue[2][kQueueCap];
+    };
 };
 
 // re-score this lane's log entries and keep those still within `limit` (warp-uniform trip count)
@@ -811,10 +813,10 @@ __device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const flo
             }
             const float rmax = warp_max(v.bound);
             if (!(rmax < INFINITY)) return -4;
-            nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w);
+            nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w, S.queue);
             if (nlist < 0) {                    // wide or split tile: describe it by 8 sub-boxes and try again
                 make_sub_boxes(q, v.bound, v.bound >= 0.f, S.w);
-                nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w);
+                nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w, S.queue);
                 if (nlist < 0) return -5;
             }
             total = 3 + nlist;
@@ -839,7 +841,7 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
 }
 
 template <int K, int MODE>
-__global__ void __launch_bounds__(64, (K > 32 ? 6 : 10)) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+__global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
     constexpr int CAP = MODE != MODE_SOR ? LogCap<K>::value : 1;
     constexpr bool LOG = MODE != MODE_SOR;
     __shared__ WarpScratch3<CAP> s_ws[2];
