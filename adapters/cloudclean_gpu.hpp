@@ -307,4 +307,26 @@ std::shared_ptr<std::vector<float>> stdev_dist(Session &s, const PointT *cloud, 
     return stdevs;
 }
 
+// calcDistHist / calcIntensityHist (src/plugins/featureeval/utils.h:18-110, 113-195): one `bins`-bin histogram per point.
+template <class PointT>
+std::shared_ptr<std::vector<std::vector<float>>> calcDistHist(Session &s, const PointT *cloud, size_t n, int bins, double radius, int max_nn) {
+    auto histograms = std::make_shared<std::vector<std::vector<float>>>(n, std::vector<float>((size_t)bins, 0.0f));
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return histograms;
+    std::vector<float> flat(n * (size_t)bins);
+    if (!s.check(ccg_neighbour_hist(s.ctx(), radius, max_nn, bins, 0, nullptr, 0, flat.data()))) return histograms;
+    for (size_t i = 0; i < n; ++i) (*histograms)[i].assign(flat.begin() + i * bins, flat.begin() + (i + 1) * bins);
+    return histograms;
+}
+// PointT must have an `intensity` member (pcl::PointXYZI / PointXYZINormal)
+template <class PointT>
+std::shared_ptr<std::vector<std::vector<float>>> calcIntensityHist(Session &s, const PointT *cloud, size_t n, int bins, double radius,
+                                                                   int max_nn) {
+    auto histograms = std::make_shared<std::vector<std::vector<float>>>(n, std::vector<float>((size_t)bins, 0.0f));
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return histograms;
+    std::vector<float> flat(n * (size_t)bins);
+    if (!s.check(ccg_neighbour_hist(s.ctx(), radius, max_nn, bins, 1, &cloud[0].intensity, sizeof(PointT), flat.data()))) return histograms;
+    for (size_t i = 0; i < n; ++i) (*histograms)[i].assign(flat.begin() + i * bins, flat.begin() + (i + 1) * bins);
+    return histograms;
+}
+
 }  // namespace ccgpu

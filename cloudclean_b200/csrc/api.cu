@@ -258,6 +258,39 @@ __global__ void __launch_bounds__(256) k_stdev_dist(const float4 *__restrict__ o
     out[i] = m > 2 ? __fdiv_rn(__fsub_rn(sumsq, __fdiv_rn(__fmul_rn(sum, sum), fm)), __fsub_rn(fm, 1.f)) : 0.f;
 }
 
+// f2: calcDistHist / calcIntensityHist (featureeval/utils.h:18-110, 113-195): per point a `bins`-bin histogram over its
+// capped strict-radius neighbourhood, every neighbour adding norm_increment = float(1.0 / m).  Distance flavour:
+// bin = int((double(sqrtf(d2)) / radius) * (bins-1)); intensity flavour: bin = int(intensity * float(bins-1)).
+// Fewer than 3 neighbours leave the row at 0.  A bin's value is the same increment added count times, so the result
+// does not depend on the neighbour order.
+__global__ void __launch_bounds__(256) k_neighbour_hist(const float4 *__restrict__ orig, const int32_t *__restrict__ idx,
+                                                        const int32_t *__restrict__ count, size_t n, int k, int bins, int which, double radius,
+                                                        const char *__restrict__ attr, size_t attr_stride, float *__restrict__ hist) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float *row = hist + i * (size_t)bins;
+    for (int b = 0; b < bins; ++b) row[b] = 0.f;
+    const int m = count[i];
+    if (m < 3) return;
+    const float inc = (float)(1.0 / (double)m);
+    const float4 q = orig[i];
+    for (int j = 0; j < m; ++j) {
+        const int t = idx[i * k + j];
+        int bin;
+        if (which == 0) {
+            const float4 p = orig[t];
+            const float dx = __fsub_rn(q.x, p.x), dy = __fsub_rn(q.y, p.y), dz = __fsub_rn(q.z, p.z);
+            const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            bin = (int)(((double)__fsqrt_rn(d2) / radius) * (double)(bins - 1));
+        } else {
+            const float a = *reinterpret_cast<const float *>(attr + (size_t)t * attr_stride);
+            bin = (int)__fmul_rn(a, (float)(bins - 1));
+        }
+        bin = bin < 0 ? 0 : (bin > bins - 1 ? bins - 1 : bin);       // the reference indexes out of bounds for intensities outside [0,1]
+        row[bin] = __fadd_rn(row[bin], inc);
+    }
+}
+
 static QueryArgs base_args(ccg_ctx *ctx) {
     QueryArgs a{};
     a.rb = INFINITY; a.begin = 0; a.end = ctx->n; a.sorted_rows = 0;
@@ -452,6 +485,35 @@ int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const floa
     const float3 c = centre3 ? make_float3(centre3[0], centre3[1], centre3[2]) : make_float3(0.f, 0.f, 0.f);
     k_stdev_dist<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), idx, cnt, n, max_nn, use_depth ? 1 : 0, c,
                                                                        oo.dev<float>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
+int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, const void *attr, size_t attr_stride_bytes, float *hist) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!hist) return set_error(ctx, CCG_ERR_INVALID, "hist is NULL");
+    if (bins < 1 || bins > 4096) return set_error(ctx, CCG_ERR_INVALID, "bins must be in [1,4096]");
+    if (which != 0 && which != 1) return set_error(ctx, CCG_ERR_INVALID, "which must be 0 (distance) or 1 (attribute)");
+    if (which == 1 && (!attr || attr_stride_bytes < 4 || (attr_stride_bytes & 3))) return set_error(ctx, CCG_ERR_INVALID, "attribute array / stride invalid");
+    if (which == 0 && !(r > 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be > 0");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *ad = attr;
+    if (which == 1 && !is_dev(ctx, attr)) {
+        const size_t bytes = (n - 1) * attr_stride_bytes + 4;
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, attr, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        ad = ctx->tmp[1].p;
+    }
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, hist, n * (size_t)bins * 4));
+    CCG_TRY(query_begin(ctx));
+    int32_t *idx, *cnt;
+    CCG_TRY(radius_lists_internal(ctx, r, max_nn, 1, &idx, &cnt));
+    k_neighbour_hist<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), idx, cnt, n, max_nn, bins, which, r,
+                                                                           (const char *)ad, attr_stride_bytes, oo.dev<float>());
     ctx->stats.launches++;
     CCG_TRY(query_end(ctx));
     CCG_TRY(oo.close());

@@ -234,6 +234,14 @@ int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, doubl
 int ccg_normal_stdev(ccg_ctx *ctx, double r, int max_nn, const void *normals, size_t stride_bytes, float *out);
 int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const float *centre3, float *out);
 
+/* ccg_neighbour_hist — calcDistHist (featureeval/utils.h:18-110, which = 0) and calcIntensityHist (:113-195, which = 1):
+ *   hist is n*bins floats; per point, over its capped strict-radius neighbourhood (1 <= max_nn <= CCG_MAX_K), every
+ *   neighbour adds float(1.0/m) to bin int((sqrt(d2)/r)*(bins-1)) [which = 0] or int(attr*(bins-1)) [which = 1, attr =
+ *   one float per point at attr + i*attr_stride_bytes, e.g. &points[0].intensity with stride 32]; rows of points
+ *   with fewer than 3 neighbours stay 0.  Bin indices are clamped to [0, bins-1] (the reference would index out of
+ *   bounds for intensities outside [0,1]). */
+int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, const void *attr, size_t attr_stride_bytes, float *hist);
+
 #ifdef __cplusplus
 }
 #endif

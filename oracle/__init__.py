@@ -282,6 +282,29 @@ def stdev_dist(points, r, max_nn, use_depth=False, centre=None):
     return np.where(cnt > 2, var, F(0)).astype(F)
 
 
+def neighbour_hist(points, r, max_nn, bins, attr=None):
+    """f2 — calcDistHist (attr None) / calcIntensityHist (featureeval/utils.h:18-195) as written: strict radius, the
+    max_nn nearest, < 3 neighbours -> zeros, every neighbour adds float(1.0/m) to its bin (clamped to [0, bins-1])."""
+    F = np.float32
+    pts = _cloud(points)
+    res = Tree(pts).radius(r, cap=max_nn, strict_lt=True)
+    idx, cnt, d2 = res["idx"], res["count"], res["d2"]
+    n = pts.shape[0]
+    hist = np.zeros((n, bins), F)
+    inc = (1.0 / np.maximum(cnt, 1).astype(np.float64)).astype(F)
+    rows = np.arange(n)
+    for j in range(max_nn):
+        live = (j < cnt) & (cnt >= 3)
+        if attr is None:
+            b = ((np.sqrt(np.where(live, d2[:, j], 0).astype(F)).astype(np.float64) / float(r)) * (bins - 1)).astype(np.int64)
+        else:
+            a = np.asarray(attr, F)[np.where(live, idx[:, j], 0)]
+            b = (a * F(bins - 1)).astype(F).astype(np.int64)
+        b = np.clip(b, 0, bins - 1)
+        hist[rows[live], b[live]] = (hist[rows[live], b[live]] + inc[live]).astype(F)
+    return hist
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

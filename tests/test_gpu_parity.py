@@ -488,3 +488,18 @@ def test_reductions_reject_uncapped(gpu_ctx):
         gpu_ctx.normal_stdev(0.1, 0, nrm, device_out=False)
     with pytest.raises(cc.CcgError):
         gpu_ctx.stdev_dist(0.1, 1000, device_out=False)
+
+
+@pytest.mark.parametrize("r,max_nn,bins", [(0.1, 20, 20), (0.3, 64, 8), (0.05, 10, 33)])
+def test_neighbour_histograms(gpu_ctx, r, max_nn, bins):
+    """calcDistHist / calcIntensityHist (featureeval/utils.h:18-195): bit-exact (same increments, same bins)."""
+    pts, _ = _scan_with_normals()
+    gpu_ctx.set_cloud(pts)
+    got_d = gpu_ctx.neighbour_hist(r, max_nn, bins, device_out=False)
+    assert np.array_equal(got_d, oracle.neighbour_hist(pts, r, max_nn, bins))
+    inten = pts[:, 4]                                    # strided view into the PointXYZI array: stride 32 bytes
+    assert inten.strides[0] == 32
+    got_i = gpu_ctx.neighbour_hist(r, max_nn, bins, attr=inten, device_out=False)
+    assert np.array_equal(got_i, oracle.neighbour_hist(pts, r, max_nn, bins, attr=inten))
+    filled = got_d.sum(1) > 0
+    assert np.allclose(got_d[filled].sum(1), 1.0, atol=1e-5) and np.allclose(got_i[filled].sum(1), 1.0, atol=1e-5)
