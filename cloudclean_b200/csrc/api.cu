@@ -144,12 +144,25 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
     CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, nleaf, 0, bits, st));
     ctx->stats.launches += 1 + (bits + 7) / 8 + 1;
     // chunk c = slots [slot[c], slot[c+1]); rows below bound[c+1] are final once it has run
-    int per = ((nleaf + chunks - 1) / chunks + 1) & ~1;
-    if (per < 2) per = 2;
+    // `chunks` equal chunks over the first 88 % of the tiles, then three short ones (6, 4, 2 %): what cannot overlap is the
+    // copy of the LAST chunk's rows, so the last chunk is kept small without paying launch tails on all of them
+    if (chunks > 13) chunks = 13;
     int slot[18]; size_t bound[18];
     int nch = 0;
     slot[0] = 0;
-    while (slot[nch] < nleaf) { slot[nch + 1] = slot[nch] + per < nleaf ? slot[nch] + per : nleaf; ++nch; }
+    {
+        const bool taper = nleaf >= 64;
+        const int main_tiles = taper ? (int)((long long)nleaf * 88 / 100) : nleaf;
+        int per = ((main_tiles + chunks - 1) / chunks + 1) & ~1;
+        if (per < 2) per = 2;
+        while (slot[nch] < main_tiles) { slot[nch + 1] = slot[nch] + per < main_tiles ? slot[nch] + per : main_tiles; ++nch; }
+        if (taper) {
+            const int cut[3] = {(int)((long long)nleaf * 94 / 100) & ~1, (int)((long long)nleaf * 98 / 100) & ~1, nleaf};
+            slot[nch] &= ~1;                                  // chunk starts stay even: two tiles per block
+            for (int i = 0; i < 3; ++i)
+                if (cut[i] > slot[nch]) { slot[nch + 1] = cut[i]; ++nch; }
+        }
+    }
     CCG_CUDA(ctx, ctx->hpin[1].reserve(64 * sizeof(unsigned)));
     unsigned *hb = ctx->hpin[1].as<unsigned>();
     for (int c = 1; c < nch; ++c)
