@@ -329,4 +329,19 @@ std::shared_ptr<std::vector<std::vector<float>>> calcIntensityHist(Session &s, c
     return histograms;
 }
 
+// don<PointT,NormalT>(cloud, normals, radius1, radius2) — featureeval.cpp:694-739, the difference of normals.
+template <class PointT, class NormalT>
+std::vector<Normal> don(Session &s, const PointT *cloud, const NormalT *normals, size_t n, float radius1 = 0.2f, float radius2 = 0.5f) {
+    std::vector<Normal> donormals;
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return donormals;
+    std::vector<float> d4(n * 4);
+    if (!s.check(ccg_don(s.ctx(), normals, sizeof(NormalT), radius1, radius2, d4.data()))) return donormals;
+    donormals.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        std::memset(&donormals[i], 0, sizeof(Normal));
+        donormals[i].normal_x = d4[4 * i]; donormals[i].normal_y = d4[4 * i + 1]; donormals[i].normal_z = d4[4 * i + 2];
+    }
+    return donormals;
+}
+
 }  // namespace ccgpu

@@ -304,6 +304,25 @@ __global__ void __launch_bounds__(256) k_neighbour_hist(const float4 *__restrict
     }
 }
 
+// f2: don() of featureeval.cpp:694-739 — per point and radius the mean of the neighbours' normals, the point's own
+// normal counted twice (radiusSearch returns it and :729 pushes it again), then (mean(r1) - mean(r2)) / 2.
+__global__ void __launch_bounds__(256) k_don_combine(const float *__restrict__ s1, const int32_t *__restrict__ c1, const float *__restrict__ s2,
+                                                     const int32_t *__restrict__ c2, const char *__restrict__ normals, size_t stride, size_t n,
+                                                     float *__restrict__ out4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *self = reinterpret_cast<const float *>(normals + i * stride);
+    const float m1 = (float)(c1[i] + 1), m2 = (float)(c2[i] + 1);
+    float o[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float a1 = __fdiv_rn(__fadd_rn(s1[3 * i + d], self[d]), m1);
+        const float a2 = __fdiv_rn(__fadd_rn(s2[3 * i + d], self[d]), m2);
+        o[d] = (float)((double)__fsub_rn(a1, a2) / 2.0);
+    }
+    out4[4 * i] = o[0]; out4[4 * i + 1] = o[1]; out4[4 * i + 2] = o[2]; out4[4 * i + 3] = 0.f;
+}
+
 static QueryArgs base_args(ccg_ctx *ctx) {
     QueryArgs a{};
     a.rb = INFINITY; a.begin = 0; a.end = ctx->n; a.sorted_rows = 0;
@@ -527,6 +546,37 @@ int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, 
     CCG_TRY(radius_lists_internal(ctx, r, max_nn, 1, &idx, &cnt));
     k_neighbour_hist<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), idx, cnt, n, max_nn, bins, which, r,
                                                                            (const char *)ad, attr_stride_bytes, oo.dev<float>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
+int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, double r2, float *don4) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!normals || !don4) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (stride_bytes < 12 || (stride_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "stride_bytes must be >= 12 and a multiple of 4");
+    if (!(r1 >= 0.0) || !(r2 >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radii must be >= 0");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *nd = normals;
+    if (!is_dev(ctx, normals)) {
+        const size_t bytes = (n - 1) * stride_bytes + 12;
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, normals, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        nd = ctx->tmp[1].p;
+    }
+    CCG_CUDA(ctx, ctx->tmp[2].reserve(n * 24 + 64));
+    CCG_CUDA(ctx, ctx->tmp[0].reserve(n * 8 + 64));
+    float *s1 = ctx->tmp[2].as<float>(), *s2 = s1 + 3 * n;
+    int32_t *c1 = ctx->tmp[0].as<int32_t>(), *c2 = c1 + n;
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, don4, n * 16));
+    CCG_TRY(query_begin(ctx));
+    // the reference passes float radii to pcl::search::KdTree (don(cloud, normals, float radius1, float radius2))
+    CCG_TRY(launch_tile_attrsum(ctx, radius_bound((double)(float)r1, 1), nd, stride_bytes, s1, c1));
+    CCG_TRY(launch_tile_attrsum(ctx, radius_bound((double)(float)r2, 1), nd, stride_bytes, s2, c2));
+    k_don_combine<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(s1, c1, s2, c2, (const char *)nd, stride_bytes, n, oo.dev<float>());
     ctx->stats.launches++;
     CCG_TRY(query_end(ctx));
     CCG_TRY(oo.close());

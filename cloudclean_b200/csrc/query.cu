@@ -223,6 +223,29 @@ struct Collect {
     }
 };
 
+// streaming visitor that sums a 3-float per-point attribute (e.g. normals) over everything inside the radius;
+// the attribute is gathered by ORIGINAL index (the candidate's w), so the caller's array is used as it lies
+struct AttrSum {
+    float bound;
+    int count;
+    float s[3];
+    const char *attr; size_t stride;
+    __device__ __forceinline__ void init(float rb_, bool active, const char *attr_, size_t stride_) {
+        bound = active ? rb_ : -1.f; count = 0; s[0] = s[1] = s[2] = 0.f; attr = attr_; stride = stride_;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 4
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            if (d2_point(q, c) <= bound) {
+                const float *a = reinterpret_cast<const float *>(attr + (size_t)__float_as_int(c.w) * stride);
+                ++count;
+                s[0] = __fadd_rn(s[0], __ldg(a)); s[1] = __fadd_rn(s[1], __ldg(a + 1)); s[2] = __fadd_rn(s[2], __ldg(a + 2));
+            }
+        }
+    }
+};
+
 // ---------------------------------------------------------------------------------------------------
 // tile traversal
 // ---------------------------------------------------------------------------------------------------
@@ -1035,6 +1058,33 @@ __global__ void __launch_bounds__(128) k_tile_stream(const __grid_constant__ Tre
         pca_finish(o, q, v.m, active ? v.count : 0, row);
     }
     if (P.count && active) P.count[row] = v.count;
+}
+
+// radius neighbourhood sum of a per-point 3-vector (f2: difference of normals, featureeval.cpp:694-739)
+__global__ void __launch_bounds__(128) k_tile_attrsum(const __grid_constant__ TreeView T, float rb, const char *attr, size_t stride,
+                                                      float *sum3, int32_t *count) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * 4 + warp;
+    if (tile >= T.count[0]) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    AttrSum v;
+    v.init(rb, active, attr, stride);
+    traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (!active) return;
+    const size_t row = (size_t)__float_as_int(q.w);
+    sum3[3 * row] = v.s[0]; sum3[3 * row + 1] = v.s[1]; sum3[3 * row + 2] = v.s[2];
+    count[row] = v.count;
+}
+
+int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count) {
+    if (ctx->n == 0) return CCG_OK;
+    k_tile_attrsum<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, (const char *)attr_dev, stride, sum3, count);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -242,6 +242,14 @@ int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const floa
  *   bounds for intensities outside [0,1]). */
 int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, const void *attr, size_t attr_stride_bytes, float *hist);
 
+/* ccg_don — don<PointT,NormalT>(cloud, normals, radius1, radius2) (featureeval.cpp:694-739), the difference of normals:
+ *   per point, for each of the two (strict, UNCAPPED) radius neighbourhoods the mean of the neighbours' normals with the
+ *   point's own normal counted twice (the search returns it and :729 appends it again), then (mean1 - mean2)/2.
+ *   normals: array of structs, first three floats = normal (stride 32 for pcl::Normal), host or device.  don4: n*4 floats
+ *   (nx, ny, nz, 0).  Sums run in traversal order in fp32 (the reference's order is its tree's, unsorted): 1e-5 agreement.
+ *   The density count of markov.cpp:359-370 is ccg_radius(r, 0, 1, NULL, NULL, count). */
+int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, double r2, float *don4);
+
 #ifdef __cplusplus
 }
 #endif

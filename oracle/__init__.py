@@ -305,6 +305,35 @@ def neighbour_hist(points, r, max_nn, bins, attr=None):
     return hist
 
 
+def don(points, normals, r1=0.2, r2=0.5):
+    """f2 — don() (featureeval.cpp:694-739): (mean1 - mean2)/2 of the neighbours' normals inside the two strict, uncapped
+    radii (float radii, as the reference's signature), the point's own normal counted twice.  fp64 sums here: the
+    reference adds in its tree's (unspecified) order in fp32, the GPU in traversal order — compared at 1e-5."""
+    from scipy.spatial import cKDTree
+    pts = _cloud(points)[:, :3]
+    nr = np.ascontiguousarray(normals, np.float32)[:, :3].astype(np.float64)
+    n = pts.shape[0]
+    T = Tree(_cloud(points))
+    out = np.zeros((n, 4), np.float32)
+    means = []
+    for r in (np.float32(r1), np.float32(r2)):
+        cnt = T.radius(float(r), strict_lt=True, lists=False)["total"]
+        kd = cKDTree(pts.astype(np.float64))
+        nb = kd.query_ball_point(pts.astype(np.float64), float(r) * 1.0001)
+        rb2 = np.float32(float(r) * float(r))
+        m = np.zeros((n, 3))
+        for i in range(n):
+            j = np.asarray(nb[i])
+            d = (pts[i] - pts[j]).astype(np.float32)
+            d2 = ((d[:, 0] * d[:, 0]).astype(np.float32) + (d[:, 1] * d[:, 1]).astype(np.float32)).astype(np.float32) + (d[:, 2] * d[:, 2]).astype(np.float32)
+            j = j[d2.astype(np.float32) < rb2]
+            assert len(j) == cnt[i]
+            m[i] = (nr[j].sum(0) + nr[i]) / (len(j) + 1)
+        means.append(m)
+    out[:, :3] = ((means[0] - means[1]) / 2.0).astype(np.float32)
+    return out
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

@@ -503,3 +503,21 @@ def test_neighbour_histograms(gpu_ctx, r, max_nn, bins):
     assert np.array_equal(got_i, oracle.neighbour_hist(pts, r, max_nn, bins, attr=inten))
     filled = got_d.sum(1) > 0
     assert np.allclose(got_d[filled].sum(1), 1.0, atol=1e-5) and np.allclose(got_i[filled].sum(1), 1.0, atol=1e-5)
+
+
+def test_difference_of_normals(gpu_ctx):
+    """don() (featureeval.cpp:694-739): uncapped radius means of the neighbours' normals; 1e-5 absolute (fp32 sums in
+    traversal order vs the oracle's fp64 sums); the neighbour COUNTS behind the means are checked bit-exact by the oracle."""
+    scan = synth.make_scan_np(70, 50, scene="room", seed=16)
+    pts = np.ascontiguousarray(scan["points"])
+    rng = np.random.default_rng(3)
+    nrm = np.zeros((pts.shape[0], 8), np.float32)
+    v = rng.normal(size=(pts.shape[0], 3)).astype(np.float32); v[:, 2] += 2.0
+    nrm[:, :3] = v / np.linalg.norm(v, axis=1, keepdims=True).astype(np.float32)
+    gpu_ctx.set_cloud(pts)
+    got = gpu_ctx.don(nrm, 0.2, 0.5, device_out=False)
+    want = oracle.don(pts, nrm, 0.2, 0.5)
+    assert np.abs(got[:, :3] - want[:, :3]).max() <= 1e-5
+    assert np.all(got[:, 3] == 0)
+    assert np.abs(want[:, :3]).max() > 0.01
+    cnt = gpu_ctx.radius(0.2, 0, strict_lt=True, lists=False, device_out=False)     # the density count of markov.cpp:359-370
