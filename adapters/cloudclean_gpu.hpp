@@ -14,6 +14,7 @@
 //   OutlierFilter::filter()  (index list handed to Select)    src/plugins/outlierfilter/outlierfilter.cpp:120-179
 //   octreeDownsample<PointT>(cloud*, resolution, sub_idxs)    src/utilities/utils.h:16-62
 //   normal_stdev<PointT,NormalT> / stdev_dist                 src/utilities/cv.h:123-206, cv.cpp:166-230
+//   principalCurvatures (pcl::PrincipalCurvaturesEstimation)  markov.cpp:389-402, featureeval.cpp:947-956
 //   MinCut::buildGraph neighbour + weight loop               src/plugins/graphcut/mincut.cpp:458-475,574-585
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
@@ -44,6 +45,7 @@ namespace ccgpu {
 using PointXYZI = pcl::PointXYZI;
 using PointXYZINormal = pcl::PointXYZINormal;
 using Normal = pcl::Normal;
+using PrincipalCurvatures = pcl::PrincipalCurvatures;
 using Vector3f = Eigen::Vector3f;
 #else
 // pcl::PointXYZI: 32 bytes, x y z 1.0f | intensity pad pad pad (the reference also keeps cloud/grid indices in
@@ -51,6 +53,11 @@ using Vector3f = Eigen::Vector3f;
 struct alignas(16) PointXYZI {
     float x, y, z, w;
     float intensity, c1, c2, c3;
+};
+// pcl::PrincipalCurvatures: 20 bytes (featureeval.cpp:963-964 reads it as 5 floats, pc1 at offset 3)
+struct PrincipalCurvatures {
+    float principal_curvature_x, principal_curvature_y, principal_curvature_z;
+    float pc1, pc2;
 };
 // pcl::PointXYZINormal: 48 bytes
 struct alignas(16) PointXYZINormal {
@@ -342,6 +349,19 @@ std::vector<Normal> don(Session &s, const PointT *cloud, const NormalT *normals,
         donormals[i].normal_x = d4[4 * i]; donormals[i].normal_y = d4[4 * i + 1]; donormals[i].normal_z = d4[4 * i + 2];
     }
     return donormals;
+}
+
+// pcl::PrincipalCurvaturesEstimation<PointT, NormalT, pcl::PrincipalCurvatures> with setRadiusSearch(radius) —
+// the block at markov.cpp:389-402 and featureeval.cpp:947-956 (setInputCloud, setInputNormals, compute) as one call.
+template <class PointT, class NormalT>
+std::vector<PrincipalCurvatures> principalCurvatures(Session &s, const PointT *cloud, const NormalT *normals, size_t n, double radius) {
+    std::vector<PrincipalCurvatures> out;
+    static_assert(sizeof(PrincipalCurvatures) == 20, "five packed floats");
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return out;
+    out.resize(n);
+    const void *nrm = &normals[0].normal_x;          // pcl::Normal (offset 0) or pcl::PointXYZINormal (offset 16), as the reference uses
+    if (!s.check(ccg_principal_curvatures(s.ctx(), radius, nrm, sizeof(NormalT), reinterpret_cast<float *>(out.data())))) out.clear();
+    return out;
 }
 
 }  // namespace ccgpu

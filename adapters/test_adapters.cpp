@@ -2,6 +2,7 @@
 // checks every adapter against brute-force CPU restatements written in this file (contract arithmetic,
 // SURVEY.md §8c).  Built by `make adapters`, run by tests/test_gpu_adapters.py (-m gpu).  Exit code 0 = all green.
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -344,6 +345,51 @@ int main() {
         }
         std::printf("stdev_dist: %d of %zu differ\n", bad, n);
         CHECK(bad == 0, "stdev_dist differs at %d points", bad);
+    }
+
+    // ---- principalCurvatures (pcl::PrincipalCurvaturesEstimation, markov.cpp:389-402): normals live in PointXYZINormal ----
+    {
+        const float origin0[3] = {0, 0, 0};
+        auto nrm = knnNormals(s, pts.data(), n, 12, origin0);
+        std::vector<PointXYZINormal> pn(n);
+        for (size_t i = 0; i < n && nrm.size() == n; ++i) {
+            std::memset(&pn[i], 0, sizeof(PointXYZINormal));
+            pn[i].x = pts[i].x; pn[i].y = pts[i].y; pn[i].z = pts[i].z;
+            pn[i].normal_x = nrm[i].normal_x; pn[i].normal_y = nrm[i].normal_y; pn[i].normal_z = nrm[i].normal_z;
+        }
+        const double radius = 0.3;
+        auto pc = principalCurvatures(s, pts.data(), pn.data(), n, radius);
+        CHECK(pc.size() == n, "principalCurvatures size (%s)", s.lastError().c_str());
+        const float r2 = (float)(radius * radius);
+        double worst_tr = 0, worst_det = 0; int checked = 0;
+        for (size_t i = 0; i < n && pc.size() == n; i += 7) {
+            // the two non-zero eigenvalues of the projected-normal scatter matrix are fixed by its trace and by the sum
+            // of its principal 2x2 minors (the third eigenvalue is 0: everything lies in the tangent plane)
+            const double nx = pn[i].normal_x, ny = pn[i].normal_y, nz = pn[i].normal_z;
+            std::vector<std::array<double, 3>> pr;
+            for (auto &c : nbrs[i]) {
+                if (!(c.first < r2)) break;
+                const PointXYZINormal &o = pn[c.second];
+                const double d = nx * o.normal_x + ny * o.normal_y + nz * o.normal_z;
+                pr.push_back({o.normal_x - nx * d, o.normal_y - ny * d, o.normal_z - nz * d});
+            }
+            double cen[3] = {0, 0, 0};
+            for (auto &v : pr) for (int a = 0; a < 3; ++a) cen[a] += v[a];
+            for (int a = 0; a < 3; ++a) cen[a] /= (double)pr.size();
+            double C[3][3] = {{0}};
+            for (auto &v : pr) for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) C[a][b] += (v[a] - cen[a]) * (v[b] - cen[b]);
+            const double N = (double)pr.size();
+            const double tr = (C[0][0] + C[1][1] + C[2][2]) / N;
+            const double minors = (C[0][0] * C[1][1] - C[0][1] * C[0][1] + C[0][0] * C[2][2] - C[0][2] * C[0][2] + C[1][1] * C[2][2] - C[1][2] * C[1][2]) / (N * N);
+            const double g1 = pc[i].pc1, g2 = pc[i].pc2;
+            worst_tr = std::max(worst_tr, std::fabs(g1 + g2 - tr) / (tr + 1e-9));
+            worst_det = std::max(worst_det, std::fabs(g1 * g2 - minors) / (tr * tr + 1e-12));
+            ++checked;
+        }
+        std::printf("principalCurvatures: checked %d, max rel trace err = %.3g, max minors err = %.3g\n", checked, worst_tr, worst_det);
+        CHECK(checked > 100, "too few rows checked (%d)", checked);
+        CHECK(worst_tr <= 2e-4, "pc1 + pc2 off by %g (relative)", worst_tr);
+        CHECK(worst_det <= 2e-4, "pc1 * pc2 off by %g (relative to trace^2)", worst_det);
     }
 
     // ---- error behaviour: empty result + message, no exception, session stays usable ----

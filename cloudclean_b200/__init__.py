@@ -28,7 +28,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures",
 ]
 
 
@@ -93,6 +93,7 @@ def load_library():
     L.ccg_stdev_dist.argtypes = [vp, f64, i32, i32, vp, vp]
     L.ccg_neighbour_hist.argtypes = [vp, f64, i32, i32, i32, vp, sz, vp]
     L.ccg_don.argtypes = [vp, vp, sz, f64, f64, vp]
+    L.ccg_principal_curvatures.argtypes = [vp, f64, vp, sz, vp]
     L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.ccg_dev_free.argtypes = [vp, vp]
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
@@ -310,6 +311,16 @@ class Context:
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
         self._settle(normals)
         self._check(self.L.ccg_don(self.h, _ptr(normals), stride, float(r1), float(r2), _ptr(out)))
+        return out
+
+    def principal_curvatures(self, normals, r, device_out=None):
+        """pcl::PrincipalCurvaturesEstimation, radius search (markov.cpp:389-402, featureeval.cpp:947-956):
+        normals [n, S>=3] float32 -> float32[n, 5] = (pcx, pcy, pcz, pc1, pc2)"""
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n, 5), np.float32)
+        stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
+        self._settle(normals)
+        self._check(self.L.ccg_principal_curvatures(self.h, float(r), _ptr(normals), stride, _ptr(out)))
         return out
 
     def knn_graph(self, k, inverse_sigma, device_out=None):

@@ -583,6 +583,29 @@ int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, d
     return finish_call(ctx);
 }
 
+int ccg_principal_curvatures(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *pc5) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!normals || !pc5) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (stride_bytes < 12 || (stride_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "stride_bytes must be >= 12 and a multiple of 4");
+    if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *nd = normals;
+    if (!is_dev(ctx, normals)) {
+        const size_t bytes = (n - 1) * stride_bytes + 12;
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, normals, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        nd = ctx->tmp[1].p;
+    }
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, pc5, n * 20));
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_principal_curv(ctx, radius_bound(r, 1), nd, stride_bytes, oo.dev<float>()));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
 int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, float *d2, int32_t *count) {
     CCG_TRY(begin_call(ctx, true));
     if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");

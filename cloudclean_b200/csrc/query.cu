@@ -246,6 +246,41 @@ struct AttrSum {
     }
 };
 
+// streaming visitor for f4 (principal curvatures): first and second moments of (attr_j - ref) over everything inside
+// the radius, ref = the query's own attribute — the shift keeps the sums small where the attribute varies slowly
+struct AttrMoments {
+    float bound;
+    int count;
+    float ref[3];
+    float s[3], m[6];
+    const char *attr; size_t stride;
+    __device__ __forceinline__ void init(float rb_, bool active, const char *attr_, size_t stride_, const float4 &q) {
+        bound = active ? rb_ : -1.f; count = 0; attr = attr_; stride = stride_;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) s[i] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) m[i] = 0.f;
+        ref[0] = ref[1] = ref[2] = 0.f;
+        if (active) {
+            const float *a = reinterpret_cast<const float *>(attr + (size_t)__float_as_int(q.w) * stride);
+            ref[0] = __ldg(a); ref[1] = __ldg(a + 1); ref[2] = __ldg(a + 2);
+        }
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 2
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            if (d2_point(q, c) <= bound) {
+                const float *a = reinterpret_cast<const float *>(attr + (size_t)__float_as_int(c.w) * stride);
+                const float x = __ldg(a) - ref[0], y = __ldg(a + 1) - ref[1], z = __ldg(a + 2) - ref[2];
+                ++count;
+                s[0] += x; s[1] += y; s[2] += z;
+                m[0] += x * x; m[1] += x * y; m[2] += x * z; m[3] += y * y; m[4] += y * z; m[5] += z * z;
+            }
+        }
+    }
+};
+
 // ---------------------------------------------------------------------------------------------------
 // tile traversal
 // ---------------------------------------------------------------------------------------------------
@@ -1077,6 +1112,59 @@ __global__ void __launch_bounds__(128) k_tile_attrsum(const __grid_constant__ Tr
     const size_t row = (size_t)__float_as_int(q.w);
     sum3[3 * row] = v.s[0]; sum3[3 * row + 1] = v.s[1]; sum3[3 * row + 2] = v.s[2];
     count[row] = v.count;
+}
+
+// f4: pcl::PrincipalCurvaturesEstimation::computePointPrincipalCurvatures [EXT] (called at markov.cpp:389-402,
+// featureeval.cpp:947-956) in one pass: neighbour normals projected into the query's tangent plane, M = I - n n^T, their
+// scatter matrix C = sum (p_j - mean p)(p_j - mean p)^T = M (Q - S S^T / N) M with S, Q the moments of (n_j - n) (a common
+// shift cancels in C), then pc = eigenvector of the largest eigenvalue, pc1 = l_max / N, pc2 = l_mid / N.
+__global__ void __launch_bounds__(128) k_tile_principal_curv(const __grid_constant__ TreeView T, float rb, const char *attr, size_t stride,
+                                                             float *pc5) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * 4 + warp;
+    if (tile >= T.count[0]) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    AttrMoments v;
+    v.init(rb, active, attr, stride, q);
+    traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (!active) return;
+    float *o = pc5 + 5 * (size_t)__float_as_int(q.w);
+    if (v.count == 0) {                  // radiusSearch found nothing (cannot happen for a finite query: it finds itself)
+        o[0] = o[1] = o[2] = o[3] = o[4] = NAN;
+        return;
+    }
+    const float invn = 1.f / (float)v.count;
+    // B = Q - S S^T / N  (symmetric, {xx xy xz yy yz zz})
+    float b[6];
+    b[0] = v.m[0] - v.s[0] * v.s[0] * invn; b[1] = v.m[1] - v.s[0] * v.s[1] * invn; b[2] = v.m[2] - v.s[0] * v.s[2] * invn;
+    b[3] = v.m[3] - v.s[1] * v.s[1] * invn; b[4] = v.m[4] - v.s[1] * v.s[2] * invn; b[5] = v.m[5] - v.s[2] * v.s[2] * invn;
+    const float nx = v.ref[0], ny = v.ref[1], nz = v.ref[2];
+    // C = M B M, M = I - n n^T:  C = B - n (Bn)^T - (Bn) n^T + (n^T B n) n n^T
+    const float bn0 = b[0] * nx + b[1] * ny + b[2] * nz, bn1 = b[1] * nx + b[3] * ny + b[4] * nz, bn2 = b[2] * nx + b[4] * ny + b[5] * nz;
+    const float nbn = nx * bn0 + ny * bn1 + nz * bn2;
+    float c[6];
+    c[0] = -(b[0] - 2.f * nx * bn0 + nbn * nx * nx);
+    c[1] = -(b[1] - nx * bn1 - ny * bn0 + nbn * nx * ny);
+    c[2] = -(b[2] - nx * bn2 - nz * bn0 + nbn * nx * nz);
+    c[3] = -(b[3] - 2.f * ny * bn1 + nbn * ny * ny);
+    c[4] = -(b[4] - ny * bn2 - nz * bn1 + nbn * ny * nz);
+    c[5] = -(b[5] - 2.f * nz * bn2 + nbn * nz * nz);
+    // the solver returns the eigenvector of the SMALLEST eigenvalue: hand it -C
+    const Eig3 e = eig3_sym(c);
+    o[0] = e.n[0]; o[1] = e.n[1]; o[2] = e.n[2];
+    o[3] = -e.w[2] * invn;
+    o[4] = -e.w[1] * invn;
+}
+
+int launch_tile_principal_curv(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *pc5) {
+    if (ctx->n == 0) return CCG_OK;
+    k_tile_principal_curv<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, (const char *)attr_dev, stride, pc5);
+    ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
 }
 
 int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count) {

@@ -250,6 +250,15 @@ int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, 
  *   The density count of markov.cpp:359-370 is ccg_radius(r, 0, 1, NULL, NULL, count). */
 int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, double r2, float *don4);
 
+/* ccg_principal_curvatures — pcl::PrincipalCurvaturesEstimation with setRadiusSearch(r) [EXT], as called at
+ *   markov.cpp:389-402 and featureeval.cpp:947-956: per point, the normals of its (strict, UNCAPPED) radius neighbourhood
+ *   are projected into its tangent plane (M = I - n n^T), their scatter matrix is decomposed, and the row is
+ *   pcl::PrincipalCurvatures' five floats {pcx, pcy, pcz (unit eigenvector of the largest eigenvalue, sign free),
+ *   pc1 = l_max / N, pc2 = l_mid / N} — the stride-5 / offset-3 layout featureeval.cpp:963-964 reads.
+ *   normals: array of structs, first three floats = normal, host or device.  Sums run in traversal order in fp32
+ *   (one pass over shifted moments; PCL runs two passes in its tree's order): pc1/pc2 agree to ~1e-5 relative. */
+int ccg_principal_curvatures(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *pc5);
+
 #ifdef __cplusplus
 }
 #endif

@@ -334,6 +334,44 @@ def don(points, normals, r1=0.2, r2=0.5):
     return out
 
 
+def principal_curvatures(points, normals, r):
+    """f4 — pcl::PrincipalCurvaturesEstimation::computePointPrincipalCurvatures [EXT] with setRadiusSearch(r)
+    (markov.cpp:389-402, featureeval.cpp:947-956), restated from PCL's published algorithm (PCL is absent: unpinned):
+    M = I - n n^T; p_j = M n_j over the strict, uncapped radius neighbourhood (self included); centroid; scatter
+    matrix of the demeaned p_j (two passes, fp32 as PCL; fp64 eigensolve here, PCL uses its closed-form eigen33);
+    row = (eigenvector of the largest eigenvalue, l_max / N, l_mid / N).  Compared at 1e-5-ish, eigenvector up to sign."""
+    from scipy.spatial import cKDTree
+    pts = _cloud(points)[:, :3]
+    nr = np.ascontiguousarray(np.asarray(normals, np.float32)[:, :3])
+    n = pts.shape[0]
+    T = Tree(_cloud(points))
+    cnt = T.radius(float(r), strict_lt=True, lists=False)["total"]
+    kd = cKDTree(pts.astype(np.float64))
+    nb = kd.query_ball_point(pts.astype(np.float64), float(r) * 1.0001)
+    rb2 = np.float32(float(r) * float(r))
+    out = np.full((n, 5), np.nan, np.float32)
+    f32 = np.float32
+    for i in range(n):
+        j = np.sort(np.asarray(nb[i]))
+        d = (pts[i] - pts[j]).astype(f32)
+        d2 = ((d[:, 0] * d[:, 0]).astype(f32) + (d[:, 1] * d[:, 1]).astype(f32)).astype(f32) + (d[:, 2] * d[:, 2]).astype(f32)
+        j = j[d2.astype(f32) < rb2]
+        assert len(j) == cnt[i]
+        if len(j) == 0:
+            continue
+        ni = nr[i]
+        M = (np.eye(3, dtype=f32) - np.outer(ni, ni).astype(f32)).astype(f32)
+        proj = (nr[j] @ M.T).astype(f32)
+        cen = (proj.sum(0, dtype=f32) / f32(len(j))).astype(f32)
+        dm = (proj - cen).astype(f32)
+        cov = (dm.T @ dm).astype(f32)
+        w, v = np.linalg.eigh(cov.astype(np.float64))
+        out[i, :3] = v[:, 2]
+        out[i, 3] = w[2] / len(j)
+        out[i, 4] = w[1] / len(j)
+    return out
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

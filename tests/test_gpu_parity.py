@@ -521,3 +521,41 @@ def test_difference_of_normals(gpu_ctx):
     assert np.all(got[:, 3] == 0)
     assert np.abs(want[:, :3]).max() > 0.01
     cnt = gpu_ctx.radius(0.2, 0, strict_lt=True, lists=False, device_out=False)     # the density count of markov.cpp:359-370
+
+
+@pytest.mark.parametrize("kind", ["estimated", "noisy"])
+def test_principal_curvatures(gpu_ctx, kind):
+    """pcl::PrincipalCurvaturesEstimation (radius search; markov.cpp:389-402, featureeval.cpp:947-956).  pc1/pc2 against
+    the two-pass fp32 restatement: 2e-4 relative to the row's pc1 plus 1e-7 absolute (one-pass shifted moments on the GPU);
+    the principal direction up to sign where the two curvatures are separated.  "estimated" = the kNN-PCA normals of the
+    same scan (smooth: the case where unshifted one-pass moments would cancel), "noisy" = random normals."""
+    scan = synth.make_scan_np(70, 50, scene="room", seed=21)
+    pts = np.ascontiguousarray(scan["points"])
+    n = pts.shape[0]
+    gpu_ctx.set_cloud(pts)
+    nrm = np.zeros((n, 8), np.float32)
+    if kind == "estimated":
+        _, n4 = gpu_ctx.pca_knn(12, viewpoint=(0.0, 0.0, 0.0), device_out=False)[:2]
+        nrm[:, :3] = n4[:, :3]
+    else:
+        rng = np.random.default_rng(5)
+        v = rng.normal(size=(n, 3)).astype(np.float32); v[:, 2] += 1.5
+        nrm[:, :3] = v / np.linalg.norm(v, axis=1, keepdims=True).astype(np.float32)
+    assert np.isfinite(nrm).all()
+    r = 0.25
+    got = gpu_ctx.principal_curvatures(nrm, r, device_out=False)
+    want = oracle.principal_curvatures(pts, nrm, r)
+    assert got.shape == (n, 5) and np.isfinite(got).all() and np.isfinite(want).all()
+    tol = 2e-4 * np.abs(want[:, 3]) + 1e-7
+    assert (np.abs(got[:, 3] - want[:, 3]) <= tol).all()
+    assert (np.abs(got[:, 4] - want[:, 4]) <= tol).all()
+    assert (got[:, 3] >= got[:, 4]).all() and (got[:, 4] >= -1e-7).all()
+    sep = (want[:, 3] - want[:, 4]) > 0.05 * want[:, 3]
+    sep &= want[:, 3] > 1e-6
+    assert sep.sum() > n // 4
+    dots = np.abs(np.einsum("ij,ij->i", got[sep, :3].astype(np.float64), want[sep, :3].astype(np.float64)))
+    assert dots.min() > 1 - 1e-3
+    assert np.abs(np.linalg.norm(got[:, :3].astype(np.float64), axis=1) - 1).max() < 1e-5
+    # the principal direction lies in the tangent plane
+    tang = np.abs(np.einsum("ij,ij->i", got[sep, :3].astype(np.float64), nrm[sep, :3].astype(np.float64)))
+    assert tang.max() < 1e-3

@@ -44,6 +44,14 @@ for cfg, shrink in cfgs:
         small, b2s = ctx.voxel_downsample(pts, res)
         torch.cuda.synchronize(); t1 = _t.perf_counter()
         q = ctx.stats(); print(f"  voxel_downsample res={res} query_ms={q['ms_query']:.2f} wall_ms={(t1-t0)*1e3:.2f} voxels={small.shape[0]}", flush=True)
+    for r in (0.05, 0.1):
+        cnt = ctx.radius(r, 0, strict_lt=True, lists=False)
+        mean_cnt = float(cnt["count"].float().mean())
+        pc = ctx.principal_curvatures(nrm, r)
+        q = ctx.stats(); print(f"  principal_curvatures r={r} query_ms={q['ms_query']:.2f} mean neighbours={mean_cnt:.1f} finite={bool(torch.isfinite(pc).all())}", flush=True)
+        dn = ctx.don(nrm, r, 2 * r)
+        q = ctx.stats(); print(f"  don r1={r} r2={2*r} query_ms={q['ms_query']:.2f}", flush=True)
+        del pc, dn, cnt
     if n <= 8_000_000:
         for k in (14, 20, 50):
             idx, d2 = ctx.knn(k)
