@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libccgpu.so")
 COV_SCATTER, COV_NM1, COV_N = 0, 1, 2
 MAX_K = 64
 
+ERR_INVALID, ERR_CUDA, ERR_NO_CLOUD, ERR_NONFINITE, ERR_UNSUPPORTED, ERR_CANCELLED = -1, -2, -3, -4, -5, -6
 ERRORS = {0: "CCG_OK", -1: "CCG_ERR_INVALID", -2: "CCG_ERR_CUDA", -3: "CCG_ERR_NO_CLOUD", -4: "CCG_ERR_NONFINITE",
           -5: "CCG_ERR_UNSUPPORTED", -6: "CCG_ERR_CANCELLED"}
 
@@ -28,7 +29,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
 ]
 
 
@@ -36,6 +37,13 @@ class CcgError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"{ERRORS.get(code, code)}: {msg}")
         self.code = code
+
+
+class PtxInfo(C.Structure):
+    """ccg_ptx_info (include/ccgpu.h)"""
+    _fields_ = [("file_width", C.c_int32), ("file_height", C.c_int32), ("scan_width", C.c_int32), ("scan_height", C.c_int32),
+                ("has_rgb", C.c_int32), ("sensor_origin", C.c_float * 3), ("orientation", C.c_float * 9),
+                ("lines", C.c_int64), ("sampled", C.c_int64), ("points", C.c_int64), ("body_offset", C.c_size_t)]
 
 
 class Stats(C.Structure):
@@ -94,6 +102,10 @@ def load_library():
     L.ccg_neighbour_hist.argtypes = [vp, f64, i32, i32, i32, vp, sz, vp]
     L.ccg_don.argtypes = [vp, vp, sz, f64, f64, vp]
     L.ccg_principal_curvatures.argtypes = [vp, f64, vp, sz, vp]
+    L.ccg_ptx_parse.argtypes = [vp, vp, sz, i32, C.POINTER(PtxInfo)]
+    L.ccg_ptx_load.argtypes = [vp, C.c_char_p, i32, C.POINTER(PtxInfo)]
+    L.ccg_ptx_fetch.argtypes = [vp, vp, vp]
+    L.ccg_ptx_set_cloud.argtypes = [vp]
     L.ccg_dev_alloc.argtypes = [vp, sz, C.POINTER(vp)]
     L.ccg_dev_free.argtypes = [vp, vp]
     L.ccg_ipc_export.argtypes = [vp, vp, vp]
@@ -346,6 +358,41 @@ class Context:
         if nv.value:
             self._check(self.L.ccg_voxel_downsample_fetch(self.h, _ptr(out)))
         return out, b2s
+
+    # ---- f4: PTX ingest (PointCloud::load_ptx, pointcloud.cpp:127-330) ---------------------------------
+    def _ptx_result(self, info, device_out):
+        n = int(info.points)
+        pts = self._out(device_out, (n, 8), np.float32)
+        c2g = self._out(device_out, (n,), np.int32)
+        if n:
+            self._check(self.L.ccg_ptx_fetch(self.h, _ptr(pts), _ptr(c2g)))
+        return {"points": pts, "cloud_to_grid": c2g, "file_width": info.file_width, "file_height": info.file_height,
+                "scan_width": info.scan_width, "scan_height": info.scan_height, "has_rgb": bool(info.has_rgb),
+                "origin": np.array(info.sensor_origin[:], np.float32), "matrix": np.array(info.orientation[:], np.float32),
+                "lines": int(info.lines), "sampled": int(info.sampled), "body_offset": int(info.body_offset)}
+
+    def ptx_parse(self, data, decimation_factor=1, device_out=False):
+        """data: the file's bytes (bytes / numpy uint8 / torch uint8 CUDA tensor) -> dict (points [n, 8], cloud_to_grid, header)"""
+        info = PtxInfo()
+        if isinstance(data, (bytes, bytearray, memoryview)):
+            data = np.frombuffer(data, np.uint8)
+        nbytes = data.numel() if _is_torch(data) else data.size
+        self._settle(data)
+        self._check(self.L.ccg_ptx_parse(self.h, _ptr(data), nbytes, decimation_factor, C.byref(info)))
+        return self._ptx_result(info, device_out)
+
+    def ptx_load(self, filename, decimation_factor=1, device_out=False):
+        """load_ptx(filename, decimation_factor): mmap + GPU parse"""
+        info = PtxInfo()
+        self._check(self.L.ccg_ptx_load(self.h, str(filename).encode(), decimation_factor, C.byref(info)))
+        return self._ptx_result(info, device_out)
+
+    def ptx_set_cloud(self, n):
+        """make the rows of the last ptx_parse / ptx_load the ctx's cloud (device-resident, no host trip)"""
+        self._check(self.L.ccg_ptx_set_cloud(self.h))
+        self.n = n
+        self.on_device = True
+        return self
 
     def dev_alloc(self, nbytes):
         p = C.c_void_p()

@@ -376,6 +376,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     ctx->raw.release(); ctx->orig.release(); ctx->sorted.release();
     for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
     ctx->vox_out.release();
+    ctx->ptx_bytes.release(); ctx->ptx_starts.release(); ctx->ptx_points.release(); ctx->ptx_c2g.release();
     ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release();
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);

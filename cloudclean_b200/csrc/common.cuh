@@ -90,6 +90,8 @@ struct ccg_ctx {
     ccg::DevBuf tmp[4];      // per-call temporaries
     ccg::DevBuf vox_out;     // result of the last ccg_voxel_downsample: float[vox_n * vox_nf]
     int64_t vox_n = 0; int vox_nf = 0;
+    ccg::DevBuf ptx_bytes, ptx_starts, ptx_points, ptx_c2g;   // last ccg_ptx_parse: file bytes, line starts, 32-byte rows, cloud_to_grid_map
+    int64_t ptx_n = 0;
     ccg::DevBuf defer;       // [count | query list | output rows] of queries deferred to the exact point kernel
     ccg::HostBuf hpin[2];    // pinned bounce buffers
     float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};

@@ -219,3 +219,42 @@ def read_ptx(path):
     pts[:, 3] = 1.0
     pts[:, 4] = rows[keep, 3]
     return dict(points=pts, cloud_to_grid=np.nonzero(keep)[0].astype(np.int32), scan_w=w, scan_h=h, scene="ptx")
+
+
+def write_ptx(path, width, height, seed=0, rgb=False, zero_fraction=0.1, crlf=False, style="fixed", missing_lines=0,
+              trailing_blank_lines=0, final_newline=True):
+    """A synthetic Leica PTX file (the format PointCloud::load_ptx reads, pointcloud.cpp:127-330): 10 header lines
+    (columns, rows, scanner position, 3x3 axes, 4x4 transform) and width*height body lines "x y z intensity [r g b]".
+    style: "fixed" = %.6f like scanner exports, "mixed" = a mix of %.6f / %g / %e / integers / signs / padding.
+    zero_fraction of the lines are "0 0 0 0.5" (no return).  Returns the number of body lines written."""
+    rng = np.random.default_rng(seed)
+    eol = "\r\n" if crlf else "\n"
+    n = width * height - missing_lines
+    xyz = rng.normal(size=(n, 3)) * np.array([12.0, 9.0, 2.5])
+    inten = rng.random(n)
+    zero = rng.random(n) < zero_fraction
+    lines = []
+    head = [f"{width}", f"{height}", "1.250000 -2.500000 0.125000", "1.000000 0.000000 0.000000", "0.000000 1.000000 0.000000",
+            "0.000000 0.000000 1.000000", "1.000000 0.000000 0.000000 0.000000", "0.000000 1.000000 0.000000 0.000000",
+            "0.000000 0.000000 1.000000 0.000000", "1.250000 -2.500000 0.125000 1.000000"]
+    fmts = ["%.6f", "%g", "%e", "%.3f", "%+.5f", "%.9f", "%.12g"]
+    for i in range(n):
+        if zero[i]:
+            toks = ["0", "0", "0", "0.500000"] if style == "fixed" else ["0.000000", "-0", "0e0", "0.5"]
+        elif style == "fixed":
+            toks = ["%.6f" % v for v in (*xyz[i], inten[i])]
+        else:
+            toks = [fmts[int(rng.integers(len(fmts)))] % v for v in (*xyz[i], inten[i])]
+            if i % 17 == 3:
+                toks[0] = str(int(xyz[i, 0] * 1000))            # integers
+            if i % 29 == 5:
+                toks[1] = "%.4E" % (xyz[i, 1] * 1e-7)            # upper-case exponent, small magnitude
+        if rgb:
+            toks += [str(int(c)) for c in rng.integers(0, 256, 3)]
+        sep = " " if style == "fixed" or i % 13 else "  "
+        lines.append(sep.join(toks) + (" " if style == "mixed" and not rgb and i % 11 == 1 else ""))
+    body = eol.join(lines)
+    text = eol.join(head) + eol + body + (eol if final_newline else "") + eol * trailing_blank_lines
+    with open(path, "w", newline="") as f:
+        f.write(text)
+    return n

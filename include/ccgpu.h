@@ -259,6 +259,45 @@ int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, d
  *   (one pass over shifted moments; PCL runs two passes in its tree's order): pc1/pc2 agree to ~1e-5 relative. */
 int ccg_principal_curvatures(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *pc5);
 
+/* ---- f4: PTX ingest (PointCloud::load_ptx, src/model/pointcloud.cpp:127-330) -------------------------------
+ * The reference reads the Leica PTX ASCII format with one fscanf per line — for 10^7..10^8 lines the user's longest
+ * wait.  Here the 10 header lines are read on the host and the body is parsed on the GPU (one thread per line, decimal
+ * -> float conversions correctly rounded like strtof; line starts, line numbers and cloud indices by device scans).
+ *   bytes/nbytes         the whole file as it lies on disk (host pointer — e.g. an mmap — or device pointer)
+ *   decimation_factor    1 or even (:130); lines with (row+1)%d != 0 or (col+1)%d != 0 are skipped (:223-230),
+ *                        row = line / file_width, col = line % file_width exactly as written there
+ *   result (kept in the ctx until the next parse): n = info->points rows of 32 bytes = pcl::PointXYZI as load_ptx
+ *     leaves it {x, y, z, 1.0f, intensity, 0, float(index in the cloud), float(index in the sampled grid)} (:284-286;
+ *     the reference leaves data_c[1] uninitialised, here it is 0) and cloud_to_grid_map int32[n] (:287).
+ *     (0,0,0) returns are dropped (:263-265); at most file_width*file_height lines are read; a file that ends
+ *     early fails with CCG_ERR_INVALID ("File read fail at line", :232-235) exactly when the reference does: when a
+ *     sampled line is reached after the stream already reported end-of-file (one missing last sampled line can slip
+ *     through as a plain failed fscanf, :240-246 — then the cloud is one point short, as there).
+ *   differences, all refusals instead of guesses: a sampled line that is not "x y z intensity" (+ "r g b" when the
+ *     first body line has 7 space-separated tokens, :199-216) fails the call with CCG_ERR_INVALID and the line number
+ *     (the reference would continue from the middle of that line); numbers with more than 19 significant digits,
+ *     magnitude outside [1e-37, 3e38], nan/inf/hex floats fail with CCG_ERR_UNSUPPORTED.  Blank lines are ignored.
+ *     The bounding box of :268-281 (which writes the maxima into min_bounding_box_) is not produced.
+ * ccg_ptx_load = open + mmap + ccg_ptx_parse (what load_ptx(filename, decimation_factor) becomes);
+ * ccg_ptx_fetch copies the rows / the map out (either may be NULL; host or device destinations);
+ * ccg_ptx_set_cloud makes the parsed rows the ctx's cloud (ccg_set_cloud on the device-resident rows, no host trip). */
+typedef struct ccg_ptx_info {
+    int32_t file_width, file_height;      /* header lines 1-2 */
+    int32_t scan_width, scan_height;      /* file_* / decimation_factor (:157-158) */
+    int32_t has_rgb;                      /* first body line had 7 tokens */
+    float sensor_origin[3];               /* header line 3 (:161-162) */
+    float orientation[9];                 /* header lines 4-6 row-major as read; the reference stores
+                                             Quaternionf(orientation^T) (:167-172) */
+    int64_t lines;                        /* non-blank body lines found */
+    int64_t sampled;                      /* lines that passed the decimation rule (sampled_idx at the end) */
+    int64_t points;                       /* rows of the cloud */
+    size_t body_offset;                   /* byte offset of the first body line */
+} ccg_ptx_info;
+int ccg_ptx_parse(ccg_ctx *ctx, const void *bytes, size_t nbytes, int decimation_factor, ccg_ptx_info *info);
+int ccg_ptx_load(ccg_ctx *ctx, const char *filename, int decimation_factor, ccg_ptx_info *info);
+int ccg_ptx_fetch(ccg_ctx *ctx, void *points32, int32_t *cloud_to_grid);
+int ccg_ptx_set_cloud(ccg_ctx *ctx);
+
 #ifdef __cplusplus
 }
 #endif

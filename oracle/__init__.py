@@ -372,6 +372,41 @@ def principal_curvatures(points, normals, r):
     return out
 
 
+def load_ptx(filename, decimation_factor=1):
+    """f4 — PointCloud::load_ptx (pointcloud.cpp:127-330) through the same stdio calls (oracle/ccoracle.c cco_load_ptx):
+    -> dict(points float32[n, 8], cloud_to_grid int32[n], file_width, file_height, has_rgb, sampled, origin[3], matrix[9])"""
+    import ctypes as C
+    L = lib()
+    L.cco_load_ptx.restype = C.c_longlong
+    L.cco_load_ptx.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]
+    hdr = np.zeros(4, np.int64)
+    pose = np.zeros(12, np.float32)
+    cap = 1
+    for _ in range(2):
+        pts = np.zeros((cap, 8), np.float32)
+        c2g = np.zeros(cap, np.int32)
+        n = L.cco_load_ptx(str(filename).encode(), int(decimation_factor), _p(pts), _p(c2g), cap, _p(hdr), _p(pose))
+        if n < 0:
+            raise IOError("cco_load_ptx failed (%d)" % n)
+        if n <= cap:
+            break
+        cap = int(n)
+    return {"points": pts[:n].copy(), "cloud_to_grid": c2g[:n].copy(), "file_width": int(hdr[0]), "file_height": int(hdr[1]),
+            "has_rgb": bool(hdr[2]), "sampled": int(hdr[3]), "origin": pose[:3].copy(), "matrix": pose[3:].copy()}
+
+
+def strtof_batch(tokens):
+    """glibc strtof on a list of decimal strings -> float32[n] (what fscanf("%f") computes)"""
+    import ctypes as C
+    L = lib()
+    L.cco_strtof_batch.restype = None
+    L.cco_strtof_batch.argtypes = [C.c_char_p, C.c_int, C.c_void_p]
+    blob = b"\0".join(t.encode() for t in tokens) + b"\0"
+    out = np.zeros(len(tokens), np.float32)
+    L.cco_strtof_batch(blob, len(tokens), _p(out))
+    return out
+
+
 def eig3_f64(a6):
     a = np.ascontiguousarray(a6, np.float64)
     w = np.empty(3, np.float64)

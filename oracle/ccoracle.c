@@ -776,3 +776,78 @@ int cco_max_threads(void) {
     return 1;
 #endif
 }
+
+/* ---------------------------------------------------------------------------------------------------
+ * f4 — PointCloud::load_ptx (src/model/pointcloud.cpp:127-330) restated with the same stdio calls in the same order:
+ * fscanf("%d %d") (:149), three + nine "%f" (:161-170), five fgets (:175-180), strtok(" ") token count of the first
+ * body line (:199-216), then per sample: the decimation test with an fgets skip (:219-230), fscanf("%f %f %f %f\n")
+ * (:237), fgets of the rest when rgb (:253-256), the (0,0,0) drop (:263-265) and the row {x,y,z,1, intensity, 0,
+ * float(cloud index), float(grid index)} + cloud_to_grid_map (:284-287).  A failed fscanf without a stream error
+ * `continue`s (:240-246) exactly as there.  Test infrastructure only.
+ * out_points: cap rows of 8 floats; returns the number of rows (or -1 when the file cannot be opened, -2 on the
+ * reference's hard failure path); hdr = {file_width, file_height, has_rgb, sampled_idx}, pose = origin[3] + matrix[9]. */
+#include <stdio.h>
+#include <locale.h>
+long long cco_load_ptx(const char *filename, int decimation_factor, float *out_points, int32_t *c2g, long long cap,
+                       long long *hdr, float *pose) {
+    setlocale(LC_NUMERIC, "C");
+    FILE *pfile = fopen(filename, "r");
+    if (!pfile) return -1;
+    int file_width = 0, file_height = 0;
+    if (fscanf(pfile, "%d %d", &file_width, &file_height) != 2) { fclose(pfile); return -2; }
+    if (fscanf(pfile, "%f %f %f", &pose[0], &pose[1], &pose[2]) != 3) { fclose(pfile); return -2; }
+    for (int i = 0; i < 9; i++)
+        if (fscanf(pfile, "%f", &pose[3 + i]) != 1) { fclose(pfile); return -2; }
+    char buff[1024];
+    for (int i = 0; i < 5; i++)
+        if (!fgets(buff, 1024, pfile)) break;
+    long file_pos = ftell(pfile);
+    int tokens = 0;
+    if (fgets(buff, 1024, pfile)) {
+        for (char *ch = strtok(buff, " "); ch; ch = strtok(NULL, " ")) ++tokens;
+    }
+    const int has_rgb = tokens == 7;
+    fseek(pfile, file_pos, SEEK_SET);
+    const long long line_count = (long long)file_width * (long long)file_height;
+    long long file_sample_idx = 0, n = 0;
+    unsigned int sampled_idx = 0;
+    while (file_sample_idx < line_count) {
+        const long long row = file_sample_idx / file_width, col = file_sample_idx % file_width;
+        file_sample_idx++;
+        if ((row + 1) % decimation_factor != 0 || (col + 1) % decimation_factor != 0) {
+            if (!fgets(buff, 1024, pfile)) { /* end of file: the reference keeps looping */ }
+            continue;
+        }
+        if (ferror(pfile) || feof(pfile)) { fclose(pfile); hdr[0] = file_width; hdr[1] = file_height; hdr[2] = has_rgb; hdr[3] = sampled_idx; return -2; }
+        float x, y, z, intensity;
+        const int filled = fscanf(pfile, "%f %f %f %f\n", &x, &y, &z, &intensity);
+        if (filled != 4) {
+            if (ferror(pfile)) { fclose(pfile); return -2; }
+            continue;
+        }
+        if (has_rgb)
+            if (!fgets(buff, 1024, pfile)) { /* last line without newline */ }
+        sampled_idx++;
+        if (x == 0 && y == 0 && z == 0) continue;
+        if (n < cap) {
+            float *o = out_points + 8 * n;
+            o[0] = x; o[1] = y; o[2] = z; o[3] = 1.0f;
+            o[4] = intensity; o[5] = 0.0f; o[6] = (float)(size_t)n; o[7] = (float)(sampled_idx - 1);
+            c2g[n] = (int32_t)(sampled_idx - 1);
+        }
+        n++;
+    }
+    fclose(pfile);
+    hdr[0] = file_width; hdr[1] = file_height; hdr[2] = has_rgb; hdr[3] = sampled_idx;
+    return n;
+}
+
+/* strtof on a batch of NUL-separated tokens (the reference's "%f" conversions are glibc's strtof) */
+void cco_strtof_batch(const char *tokens, int count, float *out) {
+    setlocale(LC_NUMERIC, "C");
+    const char *p = tokens;
+    for (int i = 0; i < count; i++) {
+        out[i] = strtof(p, NULL);
+        p += strlen(p) + 1;
+    }
+}

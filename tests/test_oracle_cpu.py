@@ -186,3 +186,33 @@ def test_voxel_downsample_oracle_vs_numpy(res):
         assert np.array_equal(means[v], acc * np.float32(1.0 / len(sel)))
     plain, _ = oracle.voxel_downsample(pts, res, as_written=False)
     assert np.allclose(plain[:, 3], 1.0)
+
+
+def test_load_ptx_restatement_against_a_line_by_line_reading(tmp_path):
+    """oracle.load_ptx (stdio calls in the reference's order) against an independent reading of the same file: split
+    lines, strtof per token, decimation rule and (0,0,0) drop of pointcloud.cpp:219-287"""
+    from cloudclean_b200 import synth
+    for dec, rgb, style in ((1, False, "fixed"), (2, True, "mixed"), (4, False, "mixed")):
+        path = tmp_path / "scan.ptx"
+        w, h = 23, 31
+        synth.write_ptx(path, w, h, seed=dec, rgb=rgb, style=style)
+        res = oracle.load_ptx(path, dec)
+        lines = path.read_text().split("\n")
+        assert res["file_width"] == w and res["file_height"] == h and res["has_rgb"] == rgb
+        assert np.array_equal(res["origin"], np.array([1.25, -2.5, 0.125], np.float32))
+        assert np.array_equal(res["matrix"], np.eye(3, dtype=np.float32).ravel())
+        body = lines[10:10 + w * h]
+        rows, c2g, sampled = [], [], 0
+        for ln, text in enumerate(body):
+            row, col = ln // w, ln % w
+            if (row + 1) % dec or (col + 1) % dec:
+                continue
+            v = oracle.strtof_batch(text.split()[:4])
+            sampled += 1
+            if v[0] == 0 and v[1] == 0 and v[2] == 0:
+                continue
+            rows.append([v[0], v[1], v[2], 1.0, v[3], 0.0, float(len(rows)), float(sampled - 1)])
+            c2g.append(sampled - 1)
+        assert res["sampled"] == sampled
+        assert np.array_equal(res["points"].view(np.int32), np.array(rows, np.float32).view(np.int32))
+        assert np.array_equal(res["cloud_to_grid"], np.array(c2g, np.int32))
