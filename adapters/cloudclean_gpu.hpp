@@ -15,6 +15,7 @@
 //   octreeDownsample<PointT>(cloud*, resolution, sub_idxs)    src/utilities/utils.h:16-62
 //   normal_stdev<PointT,NormalT> / stdev_dist                 src/utilities/cv.h:123-206, cv.cpp:166-230
 //   principalCurvatures (pcl::PrincipalCurvaturesEstimation)  markov.cpp:389-402, featureeval.cpp:947-956
+//   PointCloud::load_ptx(filename, decimation_factor)         src/model/pointcloud.cpp:127-330
 //   MinCut::buildGraph neighbour + weight loop               src/plugins/graphcut/mincut.cpp:458-475,574-585
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
@@ -362,6 +363,37 @@ std::vector<PrincipalCurvatures> principalCurvatures(Session &s, const PointT *c
     const void *nrm = &normals[0].normal_x;          // pcl::Normal (offset 0) or pcl::PointXYZINormal (offset 16), as the reference uses
     if (!s.check(ccg_principal_curvatures(s.ctx(), radius, nrm, sizeof(NormalT), reinterpret_cast<float *>(out.data())))) out.clear();
     return out;
+}
+
+// PointCloud::load_ptx(filename, decimation_factor) — src/model/pointcloud.cpp:127-330.  Everything the method leaves in
+// the PointCloud object: points (with data_c[2..3] = cloud / grid index, :284-285), cloud_to_grid_map_, scan_width_ /
+// scan_height_, sensor_origin_ and the 3x3 axes (the caller stores Quaternionf(orientation^T), :167-172).  ok == false
+// mirrors `return false` (file cannot be opened, read or parsed; the message is in Session::lastError()).
+struct PtxCloud {
+    bool ok = false;
+    std::vector<PointXYZI> points;
+    std::vector<int> cloud_to_grid_map;
+    int scan_width = 0, scan_height = 0;
+    float sensor_origin[4] = {0, 0, 0, 0};
+    float orientation[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+};
+inline PtxCloud load_ptx(Session &s, const char *filename, int decimation_factor = 1, bool keep_as_session_cloud = false) {
+    PtxCloud c;
+    static_assert(sizeof(PointXYZI) == 32, "pcl::PointXYZI is 32 bytes");
+    if (!s.ok()) return c;
+    ccg_ptx_info info;
+    if (!s.check(ccg_ptx_load(s.ctx(), filename, decimation_factor, &info))) return c;
+    c.points.resize((size_t)info.points);
+    c.cloud_to_grid_map.resize((size_t)info.points);
+    static_assert(sizeof(int) == sizeof(int32_t), "cloud_to_grid_map_ is std::vector<int>");
+    if (info.points && !s.check(ccg_ptx_fetch(s.ctx(), c.points.data(), reinterpret_cast<int32_t *>(c.cloud_to_grid_map.data())))) return c;
+    // the parsed rows are already on the device: raw-ABI feature calls that follow a load can skip their upload
+    if (keep_as_session_cloud && info.points && !s.check(ccg_ptx_set_cloud(s.ctx()))) return c;
+    c.scan_width = info.scan_width; c.scan_height = info.scan_height;
+    for (int i = 0; i < 3; ++i) c.sensor_origin[i] = info.sensor_origin[i];
+    for (int i = 0; i < 9; ++i) c.orientation[i] = info.orientation[i];
+    c.ok = true;
+    return c;
 }
 
 }  // namespace ccgpu

@@ -392,6 +392,39 @@ int main() {
         CHECK(worst_det <= 2e-4, "pc1 * pc2 off by %g (relative to trace^2)", worst_det);
     }
 
+    // ---- load_ptx (pointcloud.cpp:127-330): write the test scan as a PTX file, read it back through the GPU parser ----
+    {
+        const char *path = "/tmp/ccgpu_adapter_test.ptx";
+        FILE *f = std::fopen(path, "w");
+        CHECK(f != nullptr, "cannot write %s", path);
+        if (f) {
+            std::fprintf(f, "%d\n%d\n0.5 0.25 -1.5\n1 0 0\n0 1 0\n0 0 1\n1 0 0 0\n0 1 0 0\n0 0 1 0\n0.5 0.25 -1.5 1\n", W, H);
+            size_t next = 0;
+            for (int g = 0; g < W * H; ++g) {
+                if (next < n && c2g[next] == g) { std::fprintf(f, "%.9g %.9g %.9g %.9g\n", pts[next].x, pts[next].y, pts[next].z, pts[next].intensity); ++next; }
+                else std::fprintf(f, "0 0 0 0.5\n");
+            }
+            std::fclose(f);
+            PtxCloud pc = load_ptx(s, path, 1, true);
+            CHECK(pc.ok, "load_ptx failed: %s", s.lastError().c_str());
+            CHECK(pc.points.size() == n && pc.scan_width == W && pc.scan_height == H, "load_ptx: %zu points, %d x %d", pc.points.size(), pc.scan_width, pc.scan_height);
+            CHECK(pc.sensor_origin[0] == 0.5f && pc.sensor_origin[1] == 0.25f && pc.sensor_origin[2] == -1.5f, "sensor origin");
+            int bad = 0;
+            for (size_t i = 0; i < pc.points.size() && i < n; ++i) {
+                // %.9g round-trips a float exactly, so the parsed rows must equal the cloud bit for bit
+                if (pc.points[i].x != pts[i].x || pc.points[i].y != pts[i].y || pc.points[i].z != pts[i].z || pc.points[i].intensity != pts[i].intensity) ++bad;
+                if (pc.cloud_to_grid_map[i] != c2g[i]) ++bad;
+                if (pc.points[i].w != 1.f) ++bad;
+            }
+            std::printf("load_ptx: %zu points, %d mismatches\n", pc.points.size(), bad);
+            CHECK(bad == 0, "load_ptx: %d rows differ", bad);
+            PtxCloud half = load_ptx(s, path, 2);
+            CHECK(half.ok && half.scan_width == W / 2 && half.scan_height == H / 2, "decimated load_ptx");
+            CHECK(!load_ptx(s, "/tmp/ccgpu_no_such_file.ptx").ok && !s.lastError().empty(), "missing file must fail with a message");
+            std::remove(path);
+        }
+    }
+
     // ---- error behaviour: empty result + message, no exception, session stays usable ----
     {
         std::vector<PointXYZI> bad(pts.begin(), pts.begin() + 100);

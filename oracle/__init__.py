@@ -395,6 +395,17 @@ def load_ptx(filename, decimation_factor=1):
             "has_rgb": bool(hdr[2]), "sampled": int(hdr[3]), "origin": pose[:3].copy(), "matrix": pose[3:].copy()}
 
 
+def write_ptx(filename, rows8, width, height):
+    """bench/test infrastructure: a PTX file of width*height lines from [n, 8] float32 rows (NaN x or i >= n -> "0 0 0")"""
+    import ctypes as C
+    L = lib()
+    L.cco_write_ptx.restype = C.c_longlong
+    L.cco_write_ptx.argtypes = [C.c_char_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int]
+    rows8 = np.ascontiguousarray(rows8, np.float32)
+    assert rows8.ndim == 2 and rows8.shape[1] == 8
+    return L.cco_write_ptx(str(filename).encode(), _p(rows8), rows8.shape[0], int(width), int(height))
+
+
 def strtof_batch(tokens):
     """glibc strtof on a list of decimal strings -> float32[n] (what fscanf("%f") computes)"""
     import ctypes as C

@@ -851,3 +851,22 @@ void cco_strtof_batch(const char *tokens, int count, float *out) {
         p += strlen(p) + 1;
     }
 }
+
+/* writes a PTX file from rows of 8 floats (x y z - intensity ...) — test/bench infrastructure for full-size files:
+ * width*height body lines "%.6f %.6f %.6f %.6f", rows beyond n (or flagged by a NaN x) become "0 0 0 0.500000" */
+long long cco_write_ptx(const char *filename, const float *rows8, long long n, int width, int height) {
+    FILE *f = fopen(filename, "w");
+    if (!f) return -1;
+    static char big[1 << 22];
+    setvbuf(f, big, _IOFBF, sizeof(big));
+    fprintf(f, "%d\n%d\n0.000000 0.000000 0.000000\n1.000000 0.000000 0.000000\n0.000000 1.000000 0.000000\n0.000000 0.000000 1.000000\n", width, height);
+    fprintf(f, "1.000000 0.000000 0.000000 0.000000\n0.000000 1.000000 0.000000 0.000000\n0.000000 0.000000 1.000000 0.000000\n0.000000 0.000000 0.000000 1.000000\n");
+    const long long total = (long long)width * height;
+    for (long long i = 0; i < total; i++) {
+        const float *r = rows8 + 8 * i;
+        if (i < n && r[0] == r[0]) fprintf(f, "%.6f %.6f %.6f %.6f\n", (double)r[0], (double)r[1], (double)r[2], (double)r[4]);
+        else fputs("0 0 0 0.500000\n", f);
+    }
+    fclose(f);
+    return total;
+}
