@@ -16,6 +16,7 @@
 //   normal_stdev<PointT,NormalT> / stdev_dist                 src/utilities/cv.h:123-206, cv.cpp:166-230
 //   principalCurvatures (pcl::PrincipalCurvaturesEstimation)  markov.cpp:389-402, featureeval.cpp:947-956
 //   PointCloud::load_ptx(filename, decimation_factor)         src/model/pointcloud.cpp:127-330
+//   fpfh (pcl::FPFHEstimation, radius search)                 src/plugins/featureeval/featureeval.cpp:925-932
 //   MinCut::buildGraph neighbour + weight loop               src/plugins/graphcut/mincut.cpp:458-475,574-585
 //   Markov::mkFeatureVector eigen block                       src/plugins/markov/markov.cpp:449-475
 //   FeatureEval::pca_eigen_value_ratio / plane similarity     src/plugins/featureeval/featureeval.cpp:1104-1137,1201-1220
@@ -362,6 +363,22 @@ std::vector<PrincipalCurvatures> principalCurvatures(Session &s, const PointT *c
     out.resize(n);
     const void *nrm = &normals[0].normal_x;          // pcl::Normal (offset 0) or pcl::PointXYZINormal (offset 16), as the reference uses
     if (!s.check(ccg_principal_curvatures(s.ctx(), radius, nrm, sizeof(NormalT), reinterpret_cast<float *>(out.data())))) out.clear();
+    return out;
+}
+
+// pcl::FPFHEstimation<PointT, NormalT, pcl::FPFHSignature33> with setRadiusSearch(radius) — the block at
+// featureeval.cpp:925-932 as one call; rows are pcl::FPFHSignature33 (float histogram[33]).
+struct FPFHSignature33 {
+    float histogram[33];
+};
+template <class PointT, class NormalT>
+std::vector<FPFHSignature33> fpfh(Session &s, const PointT *cloud, const NormalT *normals, size_t n, double radius) {
+    std::vector<FPFHSignature33> out;
+    static_assert(sizeof(FPFHSignature33) == 132, "33 packed floats");
+    if (!s.ok() || !s.setInputCloud(cloud, n) || n == 0) return out;
+    out.resize(n);
+    const void *nrm = &normals[0].normal_x;
+    if (!s.check(ccg_fpfh(s.ctx(), radius, nrm, sizeof(NormalT), reinterpret_cast<float *>(out.data()), nullptr))) out.clear();
     return out;
 }
 

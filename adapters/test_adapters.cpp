@@ -392,6 +392,24 @@ int main() {
         CHECK(worst_det <= 2e-4, "pc1 * pc2 off by %g (relative to trace^2)", worst_det);
     }
 
+    // ---- fpfh (featureeval.cpp:925-932): structural checks (the numerical comparison lives in tests/test_gpu_parity.py) ----
+    {
+        const float origin0[3] = {0, 0, 0};
+        auto nrm = knnNormals(s, pts.data(), n, 12, origin0);
+        auto sig = fpfh(s, pts.data(), nrm.data(), n, 0.3);
+        CHECK(sig.size() == n, "fpfh size (%s)", s.lastError().c_str());
+        int full = 0, empty = 0, other = 0;
+        for (size_t i = 0; i < sig.size(); ++i) {
+            double g[3] = {0, 0, 0};
+            for (int b = 0; b < 33; ++b) g[b / 11] += sig[i].histogram[b];
+            if (std::fabs(g[0] - 100) < 1e-2 && std::fabs(g[1] - 100) < 1e-2 && std::fabs(g[2] - 100) < 1e-2) ++full;
+            else if (g[0] == 0 && g[1] == 0 && g[2] == 0) ++empty;
+            else ++other;
+        }
+        std::printf("fpfh: %d rows sum to 100 per group, %d empty (isolated points), %d other\n", full, empty, other);
+        CHECK(other == 0 && full > (int)n / 2, "fpfh rows must be normalised to 100 per group or empty (%d / %d / %d)", full, empty, other);
+    }
+
     // ---- load_ptx (pointcloud.cpp:127-330): write the test scan as a PTX file, read it back through the GPU parser ----
     {
         const char *path = "/tmp/ccgpu_adapter_test.ptx";

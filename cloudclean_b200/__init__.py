@@ -29,7 +29,7 @@ SYMBOLS = [
     "ccg_features", "ccg_eigen_scalar", "ccg_sor_mask", "ccg_radius_count_mask", "ccg_grid_normals",
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
-    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
+    "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_fpfh", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
 ]
 
 
@@ -102,6 +102,7 @@ def load_library():
     L.ccg_neighbour_hist.argtypes = [vp, f64, i32, i32, i32, vp, sz, vp]
     L.ccg_don.argtypes = [vp, vp, sz, f64, f64, vp]
     L.ccg_principal_curvatures.argtypes = [vp, f64, vp, sz, vp]
+    L.ccg_fpfh.argtypes = [vp, f64, vp, sz, vp, vp]
     L.ccg_ptx_parse.argtypes = [vp, vp, sz, i32, C.POINTER(PtxInfo)]
     L.ccg_ptx_load.argtypes = [vp, C.c_char_p, i32, C.POINTER(PtxInfo)]
     L.ccg_ptx_fetch.argtypes = [vp, vp, vp]
@@ -334,6 +335,17 @@ class Context:
         self._settle(normals)
         self._check(self.L.ccg_principal_curvatures(self.h, float(r), _ptr(normals), stride, _ptr(out)))
         return out
+
+    def fpfh(self, normals, r, want_spfh=False, device_out=None):
+        """pcl::FPFHEstimation, radius search (featureeval.cpp:925-932): normals [n, S>=3] float32 -> float32[n, 33]
+        (and the SPFH rows [n, 33] when want_spfh)"""
+        dev = self.on_device if device_out is None else device_out
+        out = self._out(dev, (self.n, 33), np.float32)
+        sp = self._out(dev, (self.n, 33), np.float32) if want_spfh else None
+        stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
+        self._settle(normals)
+        self._check(self.L.ccg_fpfh(self.h, float(r), _ptr(normals), stride, _ptr(out), _ptr(sp)))
+        return (out, sp) if want_spfh else out
 
     def knn_graph(self, k, inverse_sigma, device_out=None):
         """kNN table + MinCut binary potentials (graphcut/mincut.cpp:458-475,574-585): (idx int32[n,k], weight float64[n,k])"""

@@ -607,6 +607,33 @@ int ccg_principal_curvatures(ccg_ctx *ctx, double r, const void *normals, size_t
     return finish_call(ctx);
 }
 
+int ccg_fpfh(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *fpfh33, float *spfh33) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!normals || !fpfh33) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    if (stride_bytes < 12 || (stride_bytes & 3)) return set_error(ctx, CCG_ERR_INVALID, "stride_bytes must be >= 12 and a multiple of 4");
+    if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+    const size_t n = ctx->n;
+    if (n == 0) return CCG_OK;
+    const void *nd = normals;
+    if (!is_dev(ctx, normals)) {
+        const size_t bytes = (n - 1) * stride_bytes + 12;
+        CCG_CUDA(ctx, ctx->tmp[1].reserve(bytes + 16));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[1].p, normals, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        nd = ctx->tmp[1].p;
+    }
+    OutBuf of, os;
+    CCG_TRY(of.open(ctx, 0, fpfh33, n * 132));
+    float *spfh_dev = nullptr;
+    if (spfh33) { CCG_TRY(os.open(ctx, 1, spfh33, n * 132)); spfh_dev = os.dev<float>(); }
+    else { CCG_CUDA(ctx, ctx->tmp[2].reserve(n * 132 + 64)); spfh_dev = ctx->tmp[2].as<float>(); }
+    CCG_TRY(query_begin(ctx));
+    CCG_TRY(launch_tile_fpfh(ctx, radius_bound(r, 1), nd, stride_bytes, spfh_dev, of.dev<float>()));
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(of.close());
+    if (spfh33) CCG_TRY(os.close());
+    return finish_call(ctx);
+}
+
 int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, float *d2, int32_t *count) {
     CCG_TRY(begin_call(ctx, true));
     if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");

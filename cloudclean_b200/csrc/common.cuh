@@ -190,6 +190,7 @@ int launch_point_query(ccg_ctx *ctx, const PointArgs &a);
 
 int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count);
 int launch_tile_principal_curv(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *pc5);
+int launch_tile_fpfh(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *spfh33, float *fpfh33);
 int launch_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out);
 int launch_eigen_scalar(ccg_ctx *ctx, const float *eig3, size_t n, int which, float *out);
 int launch_unpermute(ccg_ctx *ctx, const void *in, size_t row_bytes, void *out);

@@ -281,6 +281,105 @@ struct AttrMoments {
     }
 };
 
+// f4 (FPFH, pass 1): pcl::computePairFeatures [EXT] for the pair (query p1/n1, candidate p2/n2) -> (f1, f2, f3); false when
+// the points coincide or the Darboux frame is undefined
+__device__ __forceinline__ bool pair_features(const float4 &p1, const float n1[3], const float4 &p2, const float n2[3],
+                                              float &f1, float &f2, float &f3) {
+    float dx = p2.x - p1.x, dy = p2.y - p1.y, dz = p2.z - p1.z;
+    const float f4 = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (f4 == 0.f) return false;
+    float ax = n1[0], ay = n1[1], az = n1[2], bx = n2[0], by = n2[1], bz = n2[2];
+    const float angle1 = (ax * dx + ay * dy + az * dz) / f4;
+    const float angle2 = (bx * dx + by * dy + bz * dz) / f4;
+    if (acosf(fabsf(angle1)) > acosf(fabsf(angle2))) {          // the source is the point whose normal is closer to the line
+        float t;
+        t = ax; ax = bx; bx = t; t = ay; ay = by; by = t; t = az; az = bz; bz = t;
+        dx = -dx; dy = -dy; dz = -dz;
+        f3 = -angle2;
+    } else f3 = angle1;
+    // v = dp x n1, w = n1 x v
+    float vx = dy * az - dz * ay, vy = dz * ax - dx * az, vz = dx * ay - dy * ax;
+    const float vn = sqrtf(vx * vx + vy * vy + vz * vz);
+    if (vn == 0.f) return false;
+    vx /= vn; vy /= vn; vz /= vn;
+    const float wx = ay * vz - az * vy, wy = az * vx - ax * vz, wz = ax * vy - ay * vx;
+    f2 = vx * bx + vy * by + vz * bz;
+    f1 = atan2f(wx * bx + wy * by + wz * bz, ax * bx + ay * by + az * bz);
+    return true;
+}
+
+// SPFH of pcl::FPFHEstimation::computeSPFHSignature [EXT]: 3 x 11 bins per query, counts kept per lane in shared memory
+// (hist[bin * 32 + lane]: one bank per lane), scaled by 100 / (N - 1) afterwards
+struct Spfh {
+    float bound;
+    int count;
+    int self;
+    float nrm[3];
+    const char *attr; size_t stride;
+    unsigned *hist;              // this lane's column of the warp's [33][32] table
+    __device__ __forceinline__ void init(float rb_, bool active, const char *attr_, size_t stride_, const float4 &q, unsigned *hist_) {
+        bound = active ? rb_ : -1.f; count = 0; attr = attr_; stride = stride_; hist = hist_;
+        self = __float_as_int(q.w);
+        nrm[0] = nrm[1] = nrm[2] = 0.f;
+        if (active) {
+            const float *a = reinterpret_cast<const float *>(attr + (size_t)self * stride);
+            nrm[0] = __ldg(a); nrm[1] = __ldg(a + 1); nrm[2] = __ldg(a + 2);
+        }
+#pragma unroll
+        for (int b = 0; b < 33; ++b) hist[b * 32] = 0;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            if (d2_point(q, c) <= bound) {
+                ++count;
+                const int other = __float_as_int(c.w);
+                if (other == self) continue;
+                const float *a = reinterpret_cast<const float *>(attr + (size_t)other * stride);
+                const float n2[3] = {__ldg(a), __ldg(a + 1), __ldg(a + 2)};
+                float f1, f2, f3;
+                if (!pair_features(q, nrm, c, n2, f1, f2, f3)) continue;
+                // bin arithmetic in double as PCL writes it (M_PI and 1.0 / 0.5 are double literals; d_pi_ is a float)
+                const float d_pi = 1.0f / (2.0f * 3.14159274101257324f);
+                int b1 = (int)floor(11.0 * (((double)f1 + 3.14159265358979323846) * (double)d_pi));
+                int b2 = (int)floor(11.0 * (((double)f2 + 1.0) * 0.5));
+                int b3 = (int)floor(11.0 * (((double)f3 + 1.0) * 0.5));
+                b1 = b1 < 0 ? 0 : (b1 > 10 ? 10 : b1);
+                b2 = b2 < 0 ? 0 : (b2 > 10 ? 10 : b2);
+                b3 = b3 < 0 ? 0 : (b3 > 10 ? 10 : b3);
+                hist[b1 * 32] += 1; hist[(11 + b2) * 32] += 1; hist[(22 + b3) * 32] += 1;
+            }
+        }
+    }
+};
+
+// FPFH pass 2 (weightPointSPFHSignature [EXT]): sum of the neighbours' SPFH rows weighted by 1 / d2, d2 == 0 skipped
+struct FpfhSum {
+    float bound;
+    int count;
+    float acc[33];
+    const float *spfh;
+    __device__ __forceinline__ void init(float rb_, bool active, const float *spfh_) {
+        bound = active ? rb_ : -1.f; count = 0; spfh = spfh_;
+#pragma unroll
+        for (int b = 0; b < 33; ++b) acc[b] = 0.f;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            const float d2 = d2_point(q, c);
+            if (d2 <= bound) {
+                ++count;
+                if (d2 == 0.f) continue;
+                const float w = 1.0f / d2;
+                const float *row = spfh + (size_t)__float_as_int(c.w) * 33;
+#pragma unroll
+                for (int b = 0; b < 33; ++b) acc[b] += __ldg(row + b) * w;
+            }
+        }
+    }
+};
+
 // ---------------------------------------------------------------------------------------------------
 // tile traversal
 // ---------------------------------------------------------------------------------------------------
@@ -1163,6 +1262,62 @@ int launch_tile_principal_curv(ccg_ctx *ctx, float rb, const void *attr_dev, siz
     if (ctx->n == 0) return CCG_OK;
     k_tile_principal_curv<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, (const char *)attr_dev, stride, pc5);
     ctx->stats.launches++;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+
+// f4: pcl::FPFHEstimation with setRadiusSearch(r) [EXT] (featureeval.cpp:925-932) in two traversals
+__global__ void __launch_bounds__(128) k_tile_spfh(const __grid_constant__ TreeView T, float rb, const char *attr, size_t stride, float *spfh33) {
+    __shared__ WarpScratch s_ws[4];
+    __shared__ unsigned s_hist[4][33 * 32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * 4 + warp;
+    if (tile >= T.count[0]) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    Spfh v;
+    v.init(rb, active, attr, stride, q, &s_hist[warp][lane]);
+    traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (!active) return;
+    float *o = spfh33 + 33 * (size_t)__float_as_int(q.w);
+    const float incr = 100.0f / (float)(v.count - 1);            // computeSPFHSignature: 100 / (indices.size() - 1)
+#pragma unroll
+    for (int b = 0; b < 33; ++b) {
+        const unsigned c = v.hist[b * 32];
+        o[b] = c ? (float)c * incr : 0.f;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_tile_fpfh(const __grid_constant__ TreeView T, float rb, const float *spfh33, float *fpfh33) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * 4 + warp;
+    if (tile >= T.count[0]) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    FpfhSum v;
+    v.init(rb, active, spfh33);
+    traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (!active) return;
+    float *o = fpfh33 + 33 * (size_t)__float_as_int(q.w);
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+        float sum = 0.f;
+#pragma unroll
+        for (int b = 0; b < 11; ++b) sum += v.acc[g * 11 + b];
+        const float sc = sum != 0.f ? 100.0f / sum : 0.f;
+#pragma unroll
+        for (int b = 0; b < 11; ++b) o[g * 11 + b] = v.acc[g * 11 + b] * sc;
+    }
+}
+
+int launch_tile_fpfh(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *spfh33, float *fpfh33) {
+    if (ctx->n == 0) return CCG_OK;
+    k_tile_spfh<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, (const char *)attr_dev, stride, spfh33);
+    k_tile_fpfh<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, spfh33, fpfh33);
+    ctx->stats.launches += 2;
     CCG_CUDA(ctx, cudaGetLastError());
     return CCG_OK;
 }

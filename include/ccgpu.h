@@ -259,6 +259,15 @@ int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, d
  *   (one pass over shifted moments; PCL runs two passes in its tree's order): pc1/pc2 agree to ~1e-5 relative. */
 int ccg_principal_curvatures(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *pc5);
 
+/* ccg_fpfh — pcl::FPFHEstimation<.., pcl::FPFHSignature33> with setRadiusSearch(r) [EXT], as called at
+ *   featureeval.cpp:925-932: pass 1, per point the SPFH (3 x 11 bins of the Darboux pair features f1 = atan2(w.n2, n1.n2),
+ *   f2 = v.n2, f3 = n1.d/|d| against every other point of its strict, UNCAPPED radius neighbourhood, increments of
+ *   100/(N-1)); pass 2, per point the sum of its neighbours' SPFH rows weighted by 1/d2 (d2 = 0 skipped, so the point's own
+ *   SPFH does not enter — as PCL), each group of 11 normalised to sum 100.  fpfh33: n*33 floats (pcl::FPFHSignature33);
+ *   spfh33 (optional, n*33): the pass-1 rows.  Pair arithmetic in fp32, bin indices in double as PCL writes them; a pair
+ *   whose feature lies within rounding of a bin edge may land in the adjacent bin (statistical agreement, see the test). */
+int ccg_fpfh(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, float *fpfh33, float *spfh33);
+
 /* ---- f4: PTX ingest (PointCloud::load_ptx, src/model/pointcloud.cpp:127-330) -------------------------------
  * The reference reads the Leica PTX ASCII format with one fscanf per line — for 10^7..10^8 lines the user's longest
  * wait.  Here the 10 header lines are read on the host and the body is parsed on the GPU (one thread per line, decimal

@@ -372,6 +372,90 @@ def principal_curvatures(points, normals, r):
     return out
 
 
+def _radius_lists(points, r):
+    """strict, uncapped radius neighbourhoods under the contract's fp32 d2 (index order) -> (list of index arrays, list of d2)"""
+    from scipy.spatial import cKDTree
+    pts = _cloud(points)[:, :3]
+    n = pts.shape[0]
+    T = Tree(_cloud(points))
+    cnt = T.radius(float(r), strict_lt=True, lists=False)["total"]
+    p64 = pts.astype(np.float64)
+    nb = cKDTree(p64).query_ball_point(p64, float(r) * 1.0001)
+    rb2 = np.float32(float(r) * float(r))
+    f32 = np.float32
+    idxs, d2s = [], []
+    for i in range(n):
+        j = np.sort(np.asarray(nb[i]))
+        d = (pts[i] - pts[j]).astype(f32)
+        d2 = ((d[:, 0] * d[:, 0]).astype(f32) + (d[:, 1] * d[:, 1]).astype(f32)).astype(f32) + (d[:, 2] * d[:, 2]).astype(f32)
+        d2 = d2.astype(f32)
+        keep = d2 < rb2
+        assert int(keep.sum()) == cnt[i]
+        idxs.append(j[keep]); d2s.append(d2[keep])
+    return idxs, d2s
+
+
+def fpfh(points, normals, r):
+    """f4 — pcl::FPFHEstimation with setRadiusSearch(r) [EXT] (featureeval.cpp:925-932), restated from PCL's published
+    algorithm (PCL is absent: unpinned): computePairFeatures, computeSPFHSignature (increments of 100/(N-1), bins
+    floor(11*(f1+pi)/(2pi)), floor(11*(f2+1)/2), floor(11*(f3+1)/2) clamped), weightPointSPFHSignature (weights 1/d2,
+    d2 == 0 skipped, groups normalised to 100).  fp32 pair arithmetic, vectorised over a point's neighbours.
+    -> (fpfh float32[n, 33], spfh float32[n, 33])"""
+    f32 = np.float32
+    pts = _cloud(points)[:, :3]
+    nr = np.ascontiguousarray(np.asarray(normals, f32)[:, :3])
+    n = pts.shape[0]
+    idxs, d2s = _radius_lists(points, r)
+    spfh = np.zeros((n, 33), f32)
+    d_pi = f32(1.0) / (f32(2.0) * f32(np.pi))
+    for i in range(n):
+        j = idxs[i]
+        N = len(j)
+        j = j[j != i]
+        if len(j) == 0:
+            continue
+        dp = (pts[j] - pts[i]).astype(f32)
+        f4 = np.sqrt((dp * dp).sum(1, dtype=f32)).astype(f32)
+        ok = f4 != 0
+        j, dp, f4 = j[ok], dp[ok], f4[ok]
+        n1 = np.broadcast_to(nr[i], dp.shape).copy()
+        n2 = nr[j].copy()
+        a1 = ((n1 * dp).sum(1, dtype=f32) / f4).astype(f32)
+        a2 = ((n2 * dp).sum(1, dtype=f32) / f4).astype(f32)
+        sw = np.arccos(np.abs(a1)).astype(f32) > np.arccos(np.abs(a2)).astype(f32)
+        n1s = np.where(sw[:, None], n2, n1); n2s = np.where(sw[:, None], n1, n2)
+        dps = np.where(sw[:, None], -dp, dp)
+        f3 = np.where(sw, -a2, a1).astype(f32)
+        v = np.cross(dps, n1s).astype(f32)
+        vn = np.sqrt((v * v).sum(1, dtype=f32)).astype(f32)
+        ok = vn != 0
+        v = (v[ok] / vn[ok, None]).astype(f32); n1s, n2s, f3 = n1s[ok], n2s[ok], f3[ok]
+        w = np.cross(n1s, v).astype(f32)
+        f2 = (v * n2s).sum(1, dtype=f32)
+        f1 = np.arctan2((w * n2s).sum(1, dtype=f32), (n1s * n2s).sum(1, dtype=f32)).astype(f32)
+        b1 = np.clip(np.floor(11.0 * ((f1.astype(np.float64) + np.pi) * float(d_pi))).astype(int), 0, 10)
+        b2 = np.clip(np.floor(11.0 * ((f2.astype(np.float64) + 1.0) * 0.5)).astype(int), 0, 10)
+        b3 = np.clip(np.floor(11.0 * ((f3.astype(np.float64) + 1.0) * 0.5)).astype(int), 0, 10)
+        incr = f32(100.0) / f32(N - 1)
+        spfh[i, :11] = np.bincount(b1, minlength=11).astype(f32) * incr
+        spfh[i, 11:22] = np.bincount(b2, minlength=11).astype(f32) * incr
+        spfh[i, 22:] = np.bincount(b3, minlength=11).astype(f32) * incr
+    out = np.zeros((n, 33), f32)
+    for i in range(n):
+        j, d2 = idxs[i], d2s[i]
+        ok = d2 != 0
+        j, d2 = j[ok], d2[ok]
+        if len(j) == 0:
+            continue
+        wgt = (f32(1.0) / d2).astype(f32)
+        acc = (spfh[j] * wgt[:, None]).sum(0, dtype=np.float64)
+        for g in range(3):
+            sm = acc[11 * g:11 * g + 11].sum()
+            if sm != 0:
+                out[i, 11 * g:11 * g + 11] = (acc[11 * g:11 * g + 11] * (100.0 / sm)).astype(f32)
+    return out, spfh
+
+
 def load_ptx(filename, decimation_factor=1):
     """f4 — PointCloud::load_ptx (pointcloud.cpp:127-330) through the same stdio calls (oracle/ccoracle.c cco_load_ptx):
     -> dict(points float32[n, 8], cloud_to_grid int32[n], file_width, file_height, has_rgb, sampled, origin[3], matrix[9])"""

@@ -559,3 +559,43 @@ def test_principal_curvatures(gpu_ctx, kind):
     # the principal direction lies in the tangent plane
     tang = np.abs(np.einsum("ij,ij->i", got[sep, :3].astype(np.float64), nrm[sep, :3].astype(np.float64)))
     assert tang.max() < 1e-3
+
+
+def test_fpfh(gpu_ctx):
+    """pcl::FPFHEstimation (radius search; featureeval.cpp:925-932) against the oracle's restatement.  SPFH rows are integer
+    counts x 100/(N-1): a row either matches to fp32 rounding or a pair sat within rounding of a bin edge (sinf/atan2f/
+    acosf differ by an ulp between CUDA and numpy) — such rows must be rare and differ by whole increments only.  FPFH rows
+    (weighted sums of ~N SPFH rows) then agree to a small L1 distance."""
+    scan = synth.make_scan_np(60, 40, scene="room", seed=23)
+    pts = np.ascontiguousarray(scan["points"])
+    n = pts.shape[0]
+    gpu_ctx.set_cloud(pts)
+    _, n4 = gpu_ctx.pca_knn(12, viewpoint=(0.0, 0.0, 0.0), device_out=False)[:2]
+    nrm = np.zeros((n, 8), np.float32)
+    nrm[:, :3] = n4[:, :3]
+    r = 0.3
+    got, got_s = gpu_ctx.fpfh(nrm, r, want_spfh=True, device_out=False)
+    want, want_s = oracle.fpfh(pts, nrm, r)
+    assert got.shape == (n, 33) and np.isfinite(got).all()
+    cnt = gpu_ctx.radius(r, 0, strict_lt=True, lists=False, device_out=False)["count"]
+    lone = cnt < 2                                            # nothing but the point itself inside r: all-zero rows, as PCL
+    assert lone.mean() < 0.5 and np.all(got[lone] == 0) and np.all(got_s[lone] == 0)
+    # every group of a non-empty row sums to 100 (SPFH: up to skipped degenerate pairs)
+    for g in range(3):
+        assert np.abs(got[~lone, 11 * g:11 * g + 11].sum(1) - 100).max() < 1e-2
+        assert (got_s[:, 11 * g:11 * g + 11].sum(1) <= 100 + 1e-3).all()
+    incr = 100.0 / np.maximum(cnt - 1, 1)
+    diff_s = np.abs(got_s.astype(np.float64) - want_s)
+    rows_off = (diff_s > 1e-3 * incr[:, None]).any(1)
+    assert rows_off.mean() < 0.05, rows_off.mean()
+    # where a row differs it does so by whole pair increments moved to an adjacent bin: L1 per group is a multiple of 2*incr
+    assert (diff_s.sum(1) <= 6.5 * 3 * incr).all()
+    l1 = np.abs(got.astype(np.float64) - want).sum(1)
+    # a flipped pair in a neighbour's SPFH moves 100/(N_j - 1) of that row; it shows in the FPFH in proportion to that
+    # neighbour's weight, so only sparse neighbourhoods can be far off: bound the dense ones, count the rest
+    dense = cnt >= 30
+    assert np.median(l1) < 1e-2 and np.quantile(l1, 0.99) < 0.5, (np.median(l1), np.quantile(l1, 0.99))
+    assert dense.sum() > 200 and l1[dense].max() < 5.0, (dense.sum(), l1[dense].max())
+    assert (l1 > 1.0).mean() < 0.01, (l1 > 1.0).mean()
+    # the descriptor is informative on this scene (not all mass in one bin)
+    assert (got[~lone] > 1.0).sum(1).mean() > 3.3

@@ -51,6 +51,10 @@ for cfg, shrink in cfgs:
         q = ctx.stats(); print(f"  principal_curvatures r={r} query_ms={q['ms_query']:.2f} mean neighbours={mean_cnt:.1f} finite={bool(torch.isfinite(pc).all())}", flush=True)
         dn = ctx.don(nrm, r, 2 * r)
         q = ctx.stats(); print(f"  don r1={r} r2={2*r} query_ms={q['ms_query']:.2f}", flush=True)
+        if r <= 0.05:
+            fp = ctx.fpfh(nrm, r)
+            q = ctx.stats(); print(f"  fpfh r={r} query_ms={q['ms_query']:.2f}", flush=True)
+            del fp
         del pc, dn, cnt
     if n <= 8_000_000:
         for k in (14, 20, 50):
