@@ -7,13 +7,14 @@
 // wall-clock wait (10^7..10^8 fscanf calls).
 //
 // Here the header (10 lines) is read on the host and the body is parsed on the device:
-//   1. line starts           flagged select over the bytes (segments of 2^30 bytes, 64-bit offsets)
-//   2. k_ptx_parse           one thread per line: four correctly rounded decimal -> float conversions
+//   1. k_ptx_count + scan    line starts per 16 KB segment of the body -> first line number of every segment
+//   2. k_ptx_parse           one block per segment: bytes staged in shared memory, each thread parses the lines that start
+//                            in its 64-byte chunk: four correctly rounded decimal -> float conversions per line
 //   3. exclusive scan        non-blank lines -> line number (row, column of the scan grid)
 //   4. k_ptx_classify        decimation, (0,0,0) test, first malformed sampled line
 //   5. exclusive scan        kept lines -> index in the cloud
 //   6. k_ptx_emit            32-byte pcl::PointXYZI rows + cloud_to_grid_map, in file order
-// Everything streams: bytes once from HBM (L1 serves the per-thread byte loads), 21 B of temporaries per line, 36 B out.
+// Everything streams: the bytes twice from HBM (coalesced), 34 B of temporaries per line, 36 B out.
 //
 // Decimal conversion: sign, up to 19 significant digits and a decimal exponent give V = m * 10^e exactly; a double
 // estimate of V is within a few ulp, so (float)estimate is the correctly rounded result unless the estimate lies within
@@ -22,6 +23,8 @@
 // what fscanf("%f") uses.  More than 19 significant digits, magnitudes outside [1e-37, 3e38] (other than 0), "nan",
 // "inf" and hex floats are reported as unsupported (the line number is returned) — never guessed.
 #include "common.cuh"
+#include <cub/block/block_reduce.cuh>
+#include <cub/block/block_scan.cuh>
 #include <cub/device/device_reduce.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
@@ -139,7 +142,8 @@ __device__ __forceinline__ int decimal_to_float(unsigned long long m, int e10, b
 }
 
 // one "%f" of fscanf restricted to plain decimal notation; p advances past the token
-__device__ __forceinline__ int parse_float(const unsigned char *__restrict__ b, size_t &p, size_t end, bool force_exact, float &out) {
+template <class Bytes>
+__device__ __forceinline__ int parse_float(const Bytes &b, size_t &p, size_t end, bool force_exact, float &out) {
     while (p < end && is_blank(b[p])) ++p;
     if (p >= end) return kLineBlank;                             // no token left on this line
     bool neg = false;
@@ -185,43 +189,106 @@ __device__ __forceinline__ int parse_float(const unsigned char *__restrict__ b, 
     return kLineOk;
 }
 
-// one thread per line: "x y z intensity" (+ "r g b" ignored when has_rgb, pointcloud.cpp:253-256)
-__global__ void __launch_bounds__(256) k_ptx_parse(const unsigned char *__restrict__ bytes, size_t nbytes, const unsigned long long *__restrict__ starts,
-                                                   size_t nlines, int has_rgb, int force_exact, float4 *__restrict__ vals,
-                                                   unsigned char *__restrict__ status) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nlines) return;
-    size_t p = starts[i];
-    size_t end = i + 1 < nlines ? (size_t)starts[i + 1] : nbytes;
-    while (end > p && (bytes[end - 1] == '\n' || is_blank(bytes[end - 1]))) --end;
+// ---------------------------------------------------------------------------------------------------
+// the body is cut into segments of kSeg bytes; one block per segment
+// ---------------------------------------------------------------------------------------------------
+constexpr int kSeg = 16384;          // bytes per block
+constexpr int kChunk = 64;           // bytes per thread (256 threads)
+constexpr int kTail = 512;           // bytes staged beyond the segment: lines that start in it and end within kTail stay in smem
+// shared-memory image of bytes [seg0 - 1, seg0 + kSeg + kTail): one padding word after every 16 so that threads walking
+// their own 64-byte chunk hit distinct banks
+__device__ __forceinline__ int sidx(int o) { return o + ((o >> 6) << 2); }
+constexpr int kStageBytes = kSeg + kTail + 1;
+constexpr int kStageAlloc = kStageBytes + ((kStageBytes >> 6) << 2) + 8;
+
+struct GlobalBytes {
+    const unsigned char *b;
+    __device__ __forceinline__ unsigned char operator[](size_t g) const { return __ldg(b + g); }
+};
+struct StagedBytes {                 // g = absolute offset; valid for g in [org, org + kStageBytes)
+    const unsigned char *s;
+    size_t org;
+    __device__ __forceinline__ unsigned char operator[](size_t g) const { return s[sidx((int)(g - org))]; }
+};
+
+// line starts per segment: g is a start iff g == body or bytes[g-1] == '\n'
+__global__ void __launch_bounds__(256) k_ptx_count(const unsigned char *__restrict__ bytes, size_t body, size_t nbytes, unsigned *__restrict__ counts) {
+    const size_t seg0 = body + (size_t)blockIdx.x * kSeg;
+    const size_t seg1 = (seg0 + kSeg) < nbytes ? (seg0 + kSeg) : nbytes;
+    unsigned c = 0;
+    for (size_t g = seg0 + threadIdx.x; g < seg1; g += 256) c += (g == body || __ldg(bytes + g - 1) == '\n') ? 1u : 0u;
+    typedef cub::BlockReduce<unsigned, 256> Reduce;
+    __shared__ typename Reduce::TempStorage tmp;
+    const unsigned total = Reduce(tmp).Sum(c);
+    if (threadIdx.x == 0) counts[blockIdx.x] = total;
+}
+
+template <class Bytes>
+__device__ __forceinline__ void parse_line(const Bytes &b, size_t p, size_t end, int has_rgb, bool force_exact, float4 &out, unsigned char &status) {
+    while (end > p && (b[end - 1] == '\n' || is_blank(b[end - 1]))) --end;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     int st = kLineOk;
     if (p >= end) st = kLineBlank;
     for (int t = 0; t < 4 && st == kLineOk; ++t) {
-        const int s = parse_float(bytes, p, end, force_exact != 0, v[t]);
-        st = s == kLineBlank ? kLineMalformed : s;               // fewer than four numbers
+        const int r = parse_float(b, p, end, force_exact, v[t]);
+        st = r == kLineBlank ? kLineMalformed : r;               // fewer than four numbers
     }
     if (st == kLineOk && !has_rgb) {
-        while (p < end && is_blank(bytes[p])) ++p;
+        while (p < end && is_blank(b[p])) ++p;
         if (p < end) st = kLineMalformed;                        // the reference's next fscanf would start mid-line
     }
-    vals[i] = make_float4(v[0], v[1], v[2], v[3]);
-    status[i] = (unsigned char)st;
+    out = make_float4(v[0], v[1], v[2], v[3]);
+    status = (unsigned char)st;
 }
 
-struct IsLineStart {               // on the byte offset g itself
-    const unsigned char *bytes;
-    unsigned long long first;       // offset of the first body byte (always a line start)
-    __host__ __device__ __forceinline__ bool operator()(unsigned long long g) const { return g == first || bytes[g - 1] == '\n'; }
-};
-struct LineStartCount {
-    const unsigned char *bytes;
-    unsigned long long first;
-    __host__ __device__ __forceinline__ unsigned long long operator()(unsigned long long g) const { return (g == first || bytes[g - 1] == '\n') ? 1ull : 0ull; }
-};
-struct AddBase {
-    unsigned long long base;
-    __host__ __device__ __forceinline__ unsigned long long operator()(unsigned long long i) const { return base + i; }
+// one block per segment: stage the bytes in shared memory (coalesced), every thread finds the line starts of its 64-byte
+// chunk, a block scan ranks them, and the thread parses the lines that start in its chunk: "x y z intensity" (+ "r g b"
+// ignored when has_rgb, pointcloud.cpp:253-256).  Lines running past the staged tail are parsed from global memory.
+__global__ void __launch_bounds__(256) k_ptx_parse(const unsigned char *__restrict__ bytes, size_t body, size_t nbytes,
+                                                   const unsigned long long *__restrict__ seg_base, int has_rgb, int force_exact,
+                                                   float4 *__restrict__ vals, unsigned char *__restrict__ status) {
+    __shared__ __align__(16) unsigned char s_bytes[kStageAlloc];
+    typedef cub::BlockScan<unsigned, 256> Scan;
+    __shared__ typename Scan::TempStorage s_scan;
+    const size_t seg0 = body + (size_t)blockIdx.x * kSeg;
+    const size_t seg1 = (seg0 + kSeg) < nbytes ? (seg0 + kSeg) : nbytes;
+    const size_t org = seg0 - 1;                                  // body >= 1: the header precedes it
+    const size_t stage_end = (org + kStageBytes) < nbytes ? (org + kStageBytes) : nbytes;
+    for (size_t g = org + threadIdx.x; g < stage_end; g += 256) s_bytes[sidx((int)(g - org))] = __ldg(bytes + g);
+    __syncthreads();
+    const StagedBytes sb{s_bytes, org};
+    const GlobalBytes gb{bytes};
+    // starts inside this thread's chunk
+    const size_t c0 = seg0 + (size_t)threadIdx.x * kChunk;
+    const size_t c1 = (c0 + kChunk) < seg1 ? (c0 + kChunk) : seg1;
+    unsigned long long mask = 0;
+    for (size_t g = c0; g < c1; ++g)
+        if (g == body || sb[g - 1] == '\n') mask |= 1ull << (int)(g - c0);
+    unsigned rank = 0;
+    Scan(s_scan).ExclusiveSum((unsigned)__popcll(mask), rank);
+    unsigned long long out = seg_base[blockIdx.x] + rank;
+    while (mask) {
+        const int bit = __ffsll((long long)mask) - 1;
+        mask &= mask - 1;
+        const size_t p = c0 + (size_t)bit;
+        // end of the line: the next newline (exclusive of it), searched in the staged image first
+        size_t e = p;
+        while (e < stage_end && sb[e] != '\n') ++e;
+        float4 v; unsigned char st;
+        if (e < stage_end || stage_end == nbytes) {
+            parse_line(sb, p, e, has_rgb, force_exact != 0, v, st);
+        } else {
+            while (e < nbytes && gb[e] != '\n') ++e;
+            parse_line(gb, p, e, has_rgb, force_exact != 0, v, st);
+        }
+        vals[out] = v;
+        status[out] = st;
+        ++out;
+    }
+}
+
+struct ToU64 {
+    __host__ __device__ __forceinline__ unsigned long long operator()(unsigned v) const { return (unsigned long long)v; }
 };
 struct NonBlank {
     const unsigned char *status;
@@ -453,56 +520,34 @@ int ptx_parse(ccg_ctx *ctx, const void *bytes, size_t nbytes, int dec, ccg_ptx_i
         db = ctx->ptx_bytes.as<unsigned char>();
     }
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev[4], st));
-    // 1. line starts, segment by segment (cub item counts are ints)
+    // 1. line starts per 16 KB segment -> first line number of every segment
     CCG_CUDA(ctx, ctx->scratch.reserve(256));
-    unsigned long long *d_num = ctx->scratch.as<unsigned long long>();          // [0] selected, [1] first_bad, [2] sampled
-    const size_t seg = (size_t)1 << 30;
-    size_t nlines = 0;
-    // upper bound on lines: count the newlines first (one streaming pass), then select into an exact-size array
+    unsigned long long *d_num = ctx->scratch.as<unsigned long long>();          // [0] unused, [1] first_bad, [2] sampled
+    const size_t nseg = (nbytes - body + kSeg - 1) / kSeg;
+    if (nseg >= ((size_t)1 << 31)) return set_error(ctx, CCG_ERR_UNSUPPORTED, "PTX body too large (%zu bytes)", nbytes - body);
+    CCG_CUDA(ctx, ctx->ptx_starts.reserve(nseg * 12 + 64));
+    unsigned long long *seg_base = ctx->ptx_starts.as<unsigned long long>();
+    unsigned *seg_count = reinterpret_cast<unsigned *>(seg_base + nseg);
+    k_ptx_count<<<(unsigned)nseg, 256, 0, st>>>(db, body, nbytes, seg_count);
     {
-        size_t total = 0;
-        for (size_t b0 = body; b0 < nbytes; b0 += seg) {
-            const int items = (int)((nbytes - b0) < seg ? (nbytes - b0) : seg);
-            cub::CountingInputIterator<unsigned long long> cnt((unsigned long long)b0);
-            cub::TransformInputIterator<unsigned long long, LineStartCount, cub::CountingInputIterator<unsigned long long>> ones(
-                cnt, LineStartCount{db, (unsigned long long)body});
-            size_t tb = 0;
-            CCG_CUDA(ctx, cub::DeviceReduce::Sum(nullptr, tb, ones, d_num, items, st));
-            CCG_CUDA(ctx, ctx->sort_tmp.reserve(tb));
-            CCG_CUDA(ctx, cub::DeviceReduce::Sum(ctx->sort_tmp.p, tb, ones, d_num, items, st));
-            unsigned long long got = 0;
-            CCG_CUDA(ctx, cudaMemcpyAsync(&got, d_num, 8, cudaMemcpyDeviceToHost, st));
-            CCG_CUDA(ctx, cudaStreamSynchronize(st));
-            total += (size_t)got;
-            ctx->stats.launches += 2;
-        }
-        nlines = total;
+        cub::TransformInputIterator<unsigned long long, ToU64, const unsigned *> it(seg_count, ToU64());
+        size_t tb = 0;
+        CCG_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tb, it, seg_base, (int)nseg, st));
+        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tb));
+        CCG_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->sort_tmp.p, tb, it, seg_base, (int)nseg, st));
     }
+    size_t nlines = 0;
+    {
+        unsigned long long last_base = 0; unsigned last_count = 0;
+        CCG_CUDA(ctx, cudaMemcpyAsync(&last_base, seg_base + (nseg - 1), 8, cudaMemcpyDeviceToHost, st));
+        CCG_CUDA(ctx, cudaMemcpyAsync(&last_count, seg_count + (nseg - 1), 4, cudaMemcpyDeviceToHost, st));
+        CCG_CUDA(ctx, cudaStreamSynchronize(st));
+        nlines = (size_t)(last_base + last_count);
+    }
+    ctx->stats.launches += 3;
     if (nlines == 0) return CCG_OK;
     if (nlines >= ((size_t)1 << 31)) return set_error(ctx, CCG_ERR_UNSUPPORTED, "PTX body has %zu lines (limit 2^31)", nlines);
-    CCG_CUDA(ctx, ctx->ptx_starts.reserve(nlines * 8 + 64));
-    unsigned long long *starts = ctx->ptx_starts.as<unsigned long long>();
-    {
-        size_t filled = 0;
-        for (size_t b0 = body; b0 < nbytes; b0 += seg) {
-            const int items = (int)((nbytes - b0) < seg ? (nbytes - b0) : seg);
-            cub::CountingInputIterator<unsigned long long> cnt(0);
-            cub::TransformInputIterator<unsigned long long, AddBase, cub::CountingInputIterator<unsigned long long>> vals_it(cnt, AddBase{(unsigned long long)b0});
-            IsLineStart pred_g{db, (unsigned long long)body};
-            size_t tb = 0;
-            CCG_CUDA(ctx, cub::DeviceSelect::If(nullptr, tb, vals_it, starts + filled, d_num, items, pred_g, st));
-            CCG_CUDA(ctx, ctx->sort_tmp.reserve(tb));
-            CCG_CUDA(ctx, cub::DeviceSelect::If(ctx->sort_tmp.p, tb, vals_it, starts + filled, d_num, items, pred_g, st));
-            ctx->stats.launches += 2;
-            if (b0 + seg < nbytes) {
-                unsigned long long got = 0;
-                CCG_CUDA(ctx, cudaMemcpyAsync(&got, d_num, 8, cudaMemcpyDeviceToHost, st));
-                CCG_CUDA(ctx, cudaStreamSynchronize(st));
-                filled += (size_t)got;
-            }
-        }
-    }
-    // 2. parse every line
+    // 2. parse every line (segment by segment, bytes staged in shared memory)
     const unsigned grid = (unsigned)((nlines + 255) / 256);
     CCG_CUDA(ctx, ctx->tmp[0].reserve(nlines * 16 + 64));
     CCG_CUDA(ctx, ctx->tmp[1].reserve(nlines * 2 + 64));
@@ -513,7 +558,7 @@ int ptx_parse(ccg_ctx *ctx, const void *bytes, size_t nbytes, int dec, ccg_ptx_i
     unsigned long long *lineno = ctx->tmp[2].as<unsigned long long>();
     long long *grid_index = ctx->tmp[3].as<long long>();
     const char *fe = getenv("CCG_PTX_FORCE_EXACT");
-    k_ptx_parse<<<grid, 256, 0, st>>>(db, nbytes, starts, nlines, info->has_rgb, fe && atoi(fe) ? 1 : 0, vals, status);
+    k_ptx_parse<<<(unsigned)nseg, 256, 0, st>>>(db, body, nbytes, seg_base, info->has_rgb, fe && atoi(fe) ? 1 : 0, vals, status);
     // 3. line numbers (blank lines do not count)
     {
         cub::CountingInputIterator<unsigned long long> cnt(0);

@@ -286,7 +286,8 @@ int ccg_fpfh(ccg_ctx *ctx, double r, const void *normals, size_t stride_bytes, f
  *     first body line has 7 space-separated tokens, :199-216) fails the call with CCG_ERR_INVALID and the line number
  *     (the reference would continue from the middle of that line); numbers with more than 19 significant digits,
  *     magnitude outside [1e-37, 3e38], nan/inf/hex floats fail with CCG_ERR_UNSUPPORTED.  Blank lines are ignored.
- *     The bounding box of :268-281 (which writes the maxima into min_bounding_box_) is not produced.
+ *     Lines may have any length (the reference's fgets(buff, 1024) splits lines beyond 1023 characters when it skips
+ *     them).  The bounding box of :268-281 (which writes the maxima into min_bounding_box_) is not produced.
  * ccg_ptx_load = open + mmap + ccg_ptx_parse (what load_ptx(filename, decimation_factor) becomes);
  * ccg_ptx_fetch copies the rows / the map out (either may be NULL; host or device destinations);
  * ccg_ptx_set_cloud makes the parsed rows the ctx's cloud (ccg_set_cloud on the device-resident rows, no host trip). */
