@@ -31,6 +31,7 @@
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
 
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <chrono>
@@ -190,34 +191,59 @@ __device__ __forceinline__ int parse_float(const Bytes &b, size_t &p, size_t end
 }
 
 // ---------------------------------------------------------------------------------------------------
-// the body is cut into segments of kSeg bytes; one block per segment
+// The body is cut into segments of kSeg bytes on a 16-byte aligned grid (base_al = the aligned address at or below the
+// first body byte); one block per segment, one 60-byte chunk per thread (15 words: an odd word stride, so threads
+// reading their own chunk from shared memory hit distinct banks without padding).
 // ---------------------------------------------------------------------------------------------------
-constexpr int kSeg = 16384;          // bytes per block
-constexpr int kChunk = 64;           // bytes per thread (256 threads)
-constexpr int kTail = 512;           // bytes staged beyond the segment: lines that start in it and end within kTail stay in smem
-// shared-memory image of bytes [seg0 - 1, seg0 + kSeg + kTail): one padding word after every 16 so that threads walking
-// their own 64-byte chunk hit distinct banks
-__device__ __forceinline__ int sidx(int o) { return o + ((o >> 6) << 2); }
-constexpr int kStageBytes = kSeg + kTail + 1;
-constexpr int kStageAlloc = kStageBytes + ((kStageBytes >> 6) << 2) + 8;
+constexpr int kThreads = 256;
+constexpr int kChunk = 60;
+constexpr int kSeg = kThreads * kChunk;      // 15360
+constexpr int kLead = 16;                     // bytes staged in front of the segment (the previous byte decides a line start)
+constexpr int kTail = 512;                    // bytes staged beyond it: lines that end within kTail are parsed from shared memory
+constexpr int kStage = kLead + kSeg + kTail;  // 15888, a multiple of 16
+constexpr int kListCap = 2048;                // line starts kept per segment (a valid line has >= 8 bytes: <= 1920)
 
 struct GlobalBytes {
     const unsigned char *b;
     __device__ __forceinline__ unsigned char operator[](size_t g) const { return __ldg(b + g); }
 };
-struct StagedBytes {                 // g = absolute offset; valid for g in [org, org + kStageBytes)
+struct StagedBytes {                 // g = absolute offset; valid for g in [org, org + kStage)
     const unsigned char *s;
     size_t org;
-    __device__ __forceinline__ unsigned char operator[](size_t g) const { return s[sidx((int)(g - org))]; }
+    __device__ __forceinline__ unsigned char operator[](size_t g) const { return s[g - org]; }
 };
 
-// line starts per segment: g is a start iff g == body or bytes[g-1] == '\n'
-__global__ void __launch_bounds__(256) k_ptx_count(const unsigned char *__restrict__ bytes, size_t body, size_t nbytes, unsigned *__restrict__ counts) {
-    const size_t seg0 = body + (size_t)blockIdx.x * kSeg;
-    const size_t seg1 = (seg0 + kSeg) < nbytes ? (seg0 + kSeg) : nbytes;
-    unsigned c = 0;
-    for (size_t g = seg0 + threadIdx.x; g < seg1; g += 256) c += (g == body || __ldg(bytes + g - 1) == '\n') ? 1u : 0u;
-    typedef cub::BlockReduce<unsigned, 256> Reduce;
+// bit j of the result: a line starts at byte c0 + j (0 <= j < 60), i.e. byte c0 + j - 1 is '\n' or c0 + j == body; only
+// starts inside [lo, hi) count.  chunk = address of byte c0 (4-byte aligned; shared or global), chunk[-1] is readable.
+__device__ __forceinline__ unsigned long long chunk_starts(const unsigned char *chunk, size_t c0, size_t body, size_t lo, size_t hi) {
+    if (c0 >= hi || c0 + kChunk <= lo) return 0ull;
+    const unsigned *w = reinterpret_cast<const unsigned *>(chunk);
+    const int nwords = (int)(((hi - c0) < (size_t)kChunk ? (hi - c0) : (size_t)kChunk) + 3) >> 2;
+    unsigned long long nl = 0;
+#pragma unroll
+    for (int i = 0; i < kChunk / 4; ++i) {
+        if (i < nwords) {
+            const unsigned x = w[i] ^ 0x0a0a0a0au;
+            const unsigned m = ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);      // 0x80 in every byte that was '\n'
+            const unsigned nib = (((m >> 7) * 0x00204081u) >> 21) & 0xfu;
+            nl |= (unsigned long long)nib << (4 * i);
+        }
+    }
+    unsigned long long st = ((nl << 1) | (chunk[-1] == '\n' ? 1ull : 0ull)) & ((1ull << kChunk) - 1);
+    if (body >= c0 && body < c0 + kChunk) st |= 1ull << (int)(body - c0);
+    if (c0 < lo) st &= ~0ull << (int)(lo - c0);
+    if (c0 + kChunk > hi) st &= (1ull << (int)(hi - c0)) - 1;
+    return st;
+}
+
+__global__ void __launch_bounds__(kThreads) k_ptx_count(const unsigned char *__restrict__ bytes, size_t base_al, size_t body, size_t nbytes,
+                                                        unsigned *__restrict__ counts) {
+    const size_t seg_a = base_al + (size_t)blockIdx.x * kSeg;
+    const size_t lo = seg_a > body ? seg_a : body;
+    const size_t hi = (seg_a + kSeg) < nbytes ? (seg_a + kSeg) : nbytes;
+    const size_t c0 = seg_a + (size_t)threadIdx.x * kChunk;
+    const unsigned c = (unsigned)__popcll(chunk_starts(bytes + c0, c0, body, lo, hi));
+    typedef cub::BlockReduce<unsigned, kThreads> Reduce;
     __shared__ typename Reduce::TempStorage tmp;
     const unsigned total = Reduce(tmp).Sum(c);
     if (threadIdx.x == 0) counts[blockIdx.x] = total;
@@ -241,49 +267,76 @@ __device__ __forceinline__ void parse_line(const Bytes &b, size_t p, size_t end,
     status = (unsigned char)st;
 }
 
-// one block per segment: stage the bytes in shared memory (coalesced), every thread finds the line starts of its 64-byte
-// chunk, a block scan ranks them, and the thread parses the lines that start in its chunk: "x y z intensity" (+ "r g b"
-// ignored when has_rgb, pointcloud.cpp:253-256).  Lines running past the staged tail are parsed from global memory.
-__global__ void __launch_bounds__(256) k_ptx_parse(const unsigned char *__restrict__ bytes, size_t body, size_t nbytes,
-                                                   const unsigned long long *__restrict__ seg_base, int has_rgb, int force_exact,
-                                                   float4 *__restrict__ vals, unsigned char *__restrict__ status) {
-    __shared__ __align__(16) unsigned char s_bytes[kStageAlloc];
-    typedef cub::BlockScan<unsigned, 256> Scan;
+// line [p, e) -> vals/status[row]; e = position of the terminating '\n' or nbytes
+__device__ __forceinline__ void parse_and_store(const StagedBytes &sb, const GlobalBytes &gb, size_t p, size_t e, size_t stage_end,
+                                                int has_rgb, bool force_exact, float4 *vals, unsigned char *status, unsigned long long row) {
+    float4 v; unsigned char st;
+    if (e <= stage_end) parse_line(sb, p, e, has_rgb, force_exact, v, st);
+    else parse_line(gb, p, e, has_rgb, force_exact, v, st);
+    vals[row] = v;
+    status[row] = st;
+}
+
+__device__ __forceinline__ size_t find_newline(const StagedBytes &sb, const GlobalBytes &gb, size_t from, size_t stage_end, size_t nbytes) {
+    size_t e = from;
+    while (e < stage_end && sb[e] != '\n') ++e;
+    if (e == stage_end && stage_end < nbytes) { while (e < nbytes && gb[e] != '\n') ++e; }
+    return e;
+}
+
+// One block per segment: the bytes are staged in shared memory with 16-byte loads, every thread finds the line starts of its
+// chunk with word arithmetic, a block scan ranks them, the starts go to a shared list and the lines are dealt out round
+// robin (thread t takes lines t, t + 256, ...), so lanes stay busy whatever the line lengths: "x y z intensity" (+ "r g b"
+// ignored when has_rgb, pointcloud.cpp:253-256).  A line that runs past the staged tail is parsed from global memory; a
+// segment with more starts than the list holds (a flood of blank lines) keeps the lines with the thread that found them.
+__global__ void __launch_bounds__(kThreads) k_ptx_parse(const unsigned char *__restrict__ bytes, size_t base_al, size_t body, size_t nbytes,
+                                                        const unsigned long long *__restrict__ seg_base, int has_rgb, int force_exact,
+                                                        float4 *__restrict__ vals, unsigned char *__restrict__ status) {
+    __shared__ __align__(16) unsigned char s_bytes[kStage];
+    __shared__ unsigned short s_starts[kListCap];
+    typedef cub::BlockScan<unsigned, kThreads> Scan;
     __shared__ typename Scan::TempStorage s_scan;
-    const size_t seg0 = body + (size_t)blockIdx.x * kSeg;
-    const size_t seg1 = (seg0 + kSeg) < nbytes ? (seg0 + kSeg) : nbytes;
-    const size_t org = seg0 - 1;                                  // body >= 1: the header precedes it
-    const size_t stage_end = (org + kStageBytes) < nbytes ? (org + kStageBytes) : nbytes;
-    for (size_t g = org + threadIdx.x; g < stage_end; g += 256) s_bytes[sidx((int)(g - org))] = __ldg(bytes + g);
+    const size_t seg_a = base_al + (size_t)blockIdx.x * kSeg;
+    const size_t org = seg_a - kLead;                             // 16-byte aligned address, >= 0 (checked by the host)
+    const size_t stage_end = (org + kStage) < nbytes ? (org + kStage) : nbytes;
+    {
+        // every 16-byte vector that holds at least one valid byte lies inside the allocation (aligned, granule >= 16)
+        const uint4 *src = reinterpret_cast<const uint4 *>(bytes + org);
+        const int nvec = (int)((stage_end - org + 15) >> 4);
+        for (int v = threadIdx.x; v < nvec; v += kThreads) reinterpret_cast<uint4 *>(s_bytes)[v] = __ldg(src + v);
+    }
     __syncthreads();
     const StagedBytes sb{s_bytes, org};
     const GlobalBytes gb{bytes};
-    // starts inside this thread's chunk
-    const size_t c0 = seg0 + (size_t)threadIdx.x * kChunk;
-    const size_t c1 = (c0 + kChunk) < seg1 ? (c0 + kChunk) : seg1;
-    unsigned long long mask = 0;
-    for (size_t g = c0; g < c1; ++g)
-        if (g == body || sb[g - 1] == '\n') mask |= 1ull << (int)(g - c0);
-    unsigned rank = 0;
-    Scan(s_scan).ExclusiveSum((unsigned)__popcll(mask), rank);
-    unsigned long long out = seg_base[blockIdx.x] + rank;
-    while (mask) {
-        const int bit = __ffsll((long long)mask) - 1;
-        mask &= mask - 1;
-        const size_t p = c0 + (size_t)bit;
-        // end of the line: the next newline (exclusive of it), searched in the staged image first
-        size_t e = p;
-        while (e < stage_end && sb[e] != '\n') ++e;
-        float4 v; unsigned char st;
-        if (e < stage_end || stage_end == nbytes) {
-            parse_line(sb, p, e, has_rgb, force_exact != 0, v, st);
-        } else {
-            while (e < nbytes && gb[e] != '\n') ++e;
-            parse_line(gb, p, e, has_rgb, force_exact != 0, v, st);
+    const size_t lo = seg_a > body ? seg_a : body;
+    const size_t hi = (seg_a + kSeg) < nbytes ? (seg_a + kSeg) : nbytes;
+    const size_t c0 = seg_a + (size_t)threadIdx.x * kChunk;
+    unsigned long long mask = chunk_starts(s_bytes + kLead + threadIdx.x * kChunk, c0, body, lo, hi);
+    unsigned rank = 0, total = 0;
+    Scan(s_scan).ExclusiveSum((unsigned)__popcll(mask), rank, total);
+    const unsigned long long row0 = seg_base[blockIdx.x];
+    const bool fe = force_exact != 0;
+    if (total <= (unsigned)kListCap) {
+        unsigned r = rank;
+        while (mask) {
+            const int bit = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            s_starts[r++] = (unsigned short)(kLead + threadIdx.x * kChunk + bit);
         }
-        vals[out] = v;
-        status[out] = st;
-        ++out;
+        __syncthreads();
+        for (unsigned i = threadIdx.x; i < total; i += kThreads) {
+            const size_t p = org + s_starts[i];
+            const size_t e = i + 1 < total ? org + s_starts[i + 1] - 1 : find_newline(sb, gb, p, stage_end, nbytes);
+            parse_and_store(sb, gb, p, e, stage_end, has_rgb, fe, vals, status, row0 + i);
+        }
+    } else {
+        unsigned long long row = row0 + rank;
+        while (mask) {
+            const int bit = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            const size_t p = c0 + (size_t)bit;
+            parse_and_store(sb, gb, p, find_newline(sb, gb, p, stage_end, nbytes), stage_end, has_rgb, fe, vals, status, row++);
+        }
     }
 }
 
@@ -523,12 +576,15 @@ int ptx_parse(ccg_ctx *ctx, const void *bytes, size_t nbytes, int dec, ccg_ptx_i
     // 1. line starts per 16 KB segment -> first line number of every segment
     CCG_CUDA(ctx, ctx->scratch.reserve(256));
     unsigned long long *d_num = ctx->scratch.as<unsigned long long>();          // [0] unused, [1] first_bad, [2] sampled
-    const size_t nseg = (nbytes - body + kSeg - 1) / kSeg;
+    // segment grid on 16-byte aligned addresses (vector loads); the header always leaves room for the 16 staged lead bytes
+    const size_t base_al = body - (size_t)((reinterpret_cast<uintptr_t>(db) + body) & 15);
+    if (base_al < (size_t)kLead) return set_error(ctx, CCG_ERR_INVALID, "PTX header shorter than %d bytes", 2 * kLead);
+    const size_t nseg = (nbytes - base_al + kSeg - 1) / kSeg;
     if (nseg >= ((size_t)1 << 31)) return set_error(ctx, CCG_ERR_UNSUPPORTED, "PTX body too large (%zu bytes)", nbytes - body);
     CCG_CUDA(ctx, ctx->ptx_starts.reserve(nseg * 12 + 64));
     unsigned long long *seg_base = ctx->ptx_starts.as<unsigned long long>();
     unsigned *seg_count = reinterpret_cast<unsigned *>(seg_base + nseg);
-    k_ptx_count<<<(unsigned)nseg, 256, 0, st>>>(db, body, nbytes, seg_count);
+    k_ptx_count<<<(unsigned)nseg, kThreads, 0, st>>>(db, base_al, body, nbytes, seg_count);
     {
         cub::TransformInputIterator<unsigned long long, ToU64, const unsigned *> it(seg_count, ToU64());
         size_t tb = 0;
@@ -558,7 +614,7 @@ int ptx_parse(ccg_ctx *ctx, const void *bytes, size_t nbytes, int dec, ccg_ptx_i
     unsigned long long *lineno = ctx->tmp[2].as<unsigned long long>();
     long long *grid_index = ctx->tmp[3].as<long long>();
     const char *fe = getenv("CCG_PTX_FORCE_EXACT");
-    k_ptx_parse<<<(unsigned)nseg, 256, 0, st>>>(db, body, nbytes, seg_base, info->has_rgb, fe && atoi(fe) ? 1 : 0, vals, status);
+    k_ptx_parse<<<(unsigned)nseg, kThreads, 0, st>>>(db, base_al, body, nbytes, seg_base, info->has_rgb, fe && atoi(fe) ? 1 : 0, vals, status);
     // 3. line numbers (blank lines do not count)
     {
         cub::CountingInputIterator<unsigned long long> cnt(0);

@@ -222,3 +222,17 @@ def test_ptx_lines_longer_than_the_staged_tail(gpu_ctx, tmp_path):
     synth.write_ptx(clean, 40, 60, seed=5)
     want = oracle.load_ptx(clean, 2)
     _same(gpu_ctx.ptx_load(path, 2), want)
+
+
+def test_ptx_flood_of_blank_lines(gpu_ctx, tmp_path):
+    """thousands of consecutive blank lines (whitespace to fscanf) put more line starts into one 15 KB segment than its
+    shared list holds: the kernel's per-thread path must give the same rows"""
+    path = tmp_path / "scan.ptx"
+    synth.write_ptx(path, 40, 60, seed=6)
+    lines = path.read_text().split("\n")
+    lines[700:700] = [""] * 5000
+    lines[1500:1500] = [" ", "\t", ""] * 900
+    path.write_text("\n".join(lines))
+    got = gpu_ctx.ptx_load(path, 1)
+    _same(got, oracle.load_ptx(path, 1))
+    assert got["lines"] == 2400
