@@ -49,6 +49,12 @@ __constant__ double c_pow10[65] = {
     1e34, 1e35, 1e36, 1e37, 1e38, 1e39, 1e40, 1e41, 1e42, 1e43, 1e44, 1e45, 1e46, 1e47, 1e48, 1e49, 1e50,
     1e51, 1e52, 1e53, 1e54, 1e55, 1e56, 1e57, 1e58, 1e59, 1e60, 1e61, 1e62, 1e63, 1e64};
 
+__constant__ double c_inv_pow10[65] = {
+    1e-0,  1e-1,  1e-2,  1e-3,  1e-4,  1e-5,  1e-6,  1e-7,  1e-8,  1e-9,  1e-10, 1e-11, 1e-12, 1e-13, 1e-14, 1e-15, 1e-16,
+    1e-17, 1e-18, 1e-19, 1e-20, 1e-21, 1e-22, 1e-23, 1e-24, 1e-25, 1e-26, 1e-27, 1e-28, 1e-29, 1e-30, 1e-31, 1e-32, 1e-33,
+    1e-34, 1e-35, 1e-36, 1e-37, 1e-38, 1e-39, 1e-40, 1e-41, 1e-42, 1e-43, 1e-44, 1e-45, 1e-46, 1e-47, 1e-48, 1e-49, 1e-50,
+    1e-51, 1e-52, 1e-53, 1e-54, 1e-55, 1e-56, 1e-57, 1e-58, 1e-59, 1e-60, 1e-61, 1e-62, 1e-63, 1e-64};
+
 // ---------------------------------------------------------------------------------------------------
 // exact comparison  m * 10^e10  <=>  K * 2^p   (K < 2^26) with 320-bit unsigned integers
 // ---------------------------------------------------------------------------------------------------
@@ -114,7 +120,8 @@ __device__ __forceinline__ bool is_digit(unsigned char c) { return c >= '0' && c
 __device__ __forceinline__ int decimal_to_float(unsigned long long m, int e10, bool force_exact, float &out) {
     if (e10 > 64 || e10 < -64) return kLineUnsupported;
     const double dm = (double)m;                                  // rounds when m >= 2^53: inside the error budget below
-    const double d = e10 >= 0 ? dm * c_pow10[e10] : dm / c_pow10[-e10];
+    // a multiplication by the rounded reciprocal instead of a division: one more rounding (2^-53), far inside the budget
+    const double d = e10 >= 0 ? dm * c_pow10[e10] : dm * c_inv_pow10[-e10];
     if (!(d >= 1e-37 && d <= 3e38)) return kLineUnsupported;
     // d = V (1 + eps), |eps| < 2^-50.  Bits of d below the float mantissa: 29; the midpoint pattern is 1 << 28.
     const unsigned long long bits = (unsigned long long)__double_as_longlong(d);
@@ -143,8 +150,8 @@ __device__ __forceinline__ int decimal_to_float(unsigned long long m, int e10, b
 }
 
 // one "%f" of fscanf restricted to plain decimal notation; p advances past the token
-template <class Bytes>
-__device__ __forceinline__ int parse_float(const Bytes &b, size_t &p, size_t end, bool force_exact, float &out) {
+template <class Bytes, class Idx>
+__device__ __forceinline__ int parse_float(const Bytes &b, Idx &p, Idx end, bool force_exact, float &out) {
     while (p < end && is_blank(b[p])) ++p;
     if (p >= end) return kLineBlank;                             // no token left on this line
     bool neg = false;
@@ -171,7 +178,7 @@ __device__ __forceinline__ int parse_float(const Bytes &b, size_t &p, size_t end
     }
     if (!any) return kLineMalformed;                             // "nan", "inf", stray text
     if (p < end && (b[p] == 'e' || b[p] == 'E')) {
-        size_t s = p + 1;
+        Idx s = p + 1;
         bool eneg = false;
         if (s < end && (b[s] == '-' || b[s] == '+')) { eneg = b[s] == '-'; ++s; }
         if (s >= end || !is_digit(b[s])) return kLineMalformed;
@@ -207,10 +214,14 @@ struct GlobalBytes {
     const unsigned char *b;
     __device__ __forceinline__ unsigned char operator[](size_t g) const { return __ldg(b + g); }
 };
-struct StagedBytes {                 // g = absolute offset; valid for g in [org, org + kStage)
+struct StagedBytes {                 // the shared-memory image of bytes [org, org + kStage)
     const unsigned char *s;
     size_t org;
-    __device__ __forceinline__ unsigned char operator[](size_t g) const { return s[g - org]; }
+    __device__ __forceinline__ unsigned char operator[](size_t g) const { return s[g - org]; }      // absolute offset
+};
+struct StageLocal {                  // same image, 32-bit offsets relative to org (the parse loops live on these)
+    const unsigned char *s;
+    __device__ __forceinline__ unsigned char operator[](int o) const { return s[o]; }
 };
 
 // bit j of the result: a line starts at byte c0 + j (0 <= j < 60), i.e. byte c0 + j - 1 is '\n' or c0 + j == body; only
@@ -249,8 +260,8 @@ __global__ void __launch_bounds__(kThreads) k_ptx_count(const unsigned char *__r
     if (threadIdx.x == 0) counts[blockIdx.x] = total;
 }
 
-template <class Bytes>
-__device__ __forceinline__ void parse_line(const Bytes &b, size_t p, size_t end, int has_rgb, bool force_exact, float4 &out, unsigned char &status) {
+template <class Bytes, class Idx>
+__device__ __forceinline__ void parse_line(const Bytes &b, Idx p, Idx end, int has_rgb, bool force_exact, float4 &out, unsigned char &status) {
     while (end > p && (b[end - 1] == '\n' || is_blank(b[end - 1]))) --end;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     int st = kLineOk;
@@ -271,7 +282,7 @@ __device__ __forceinline__ void parse_line(const Bytes &b, size_t p, size_t end,
 __device__ __forceinline__ void parse_and_store(const StagedBytes &sb, const GlobalBytes &gb, size_t p, size_t e, size_t stage_end,
                                                 int has_rgb, bool force_exact, float4 *vals, unsigned char *status, unsigned long long row) {
     float4 v; unsigned char st;
-    if (e <= stage_end) parse_line(sb, p, e, has_rgb, force_exact, v, st);
+    if (e <= stage_end) parse_line(StageLocal{sb.s}, (int)(p - sb.org), (int)(e - sb.org), has_rgb, force_exact, v, st);
     else parse_line(gb, p, e, has_rgb, force_exact, v, st);
     vals[row] = v;
     status[row] = st;
