@@ -159,22 +159,20 @@ __device__ __forceinline__ int parse_float(const Bytes &b, Idx &p, Idx end, bool
     unsigned long long m = 0;
     int nd = 0, e10 = 0, any = 0;
     bool dropped = false;
-    while (p < end && is_digit(b[p])) {
-        const unsigned c = b[p] - '0';
-        any = 1;
-        if (nd < 19) { if (m != 0 || c != 0) { m = m * 10 + c; ++nd; } }
-        else { ++e10; dropped |= c != 0; }
-        ++p;
-    }
-    if (p < end && b[p] == '.') {
-        ++p;
-        while (p < end && is_digit(b[p])) {
-            const unsigned c = b[p] - '0';
+    // integer and fraction digits in ONE loop, so that lanes in different parts of their numbers run the same code:
+    // up to 19 significant digits go into m; digits beyond that only move the exponent (integer part) and must be 0
+    bool dot = false;
+    for (; p < end; ++p) {
+        const unsigned ch = b[p];
+        const unsigned c = ch - '0';
+        if (c <= 9u) {
             any = 1;
-            if (nd < 19) { m = m * 10 + c; --e10; if (m != 0) ++nd; }
-            else dropped |= c != 0;
-            ++p;
-        }
+            const bool room = nd < 19;
+            if (room && (m != 0 || c != 0)) { m = m * 10 + c; ++nd; }
+            e10 += room ? (dot ? -1 : 0) : (dot ? 0 : 1);
+            dropped |= !room && c != 0;
+        } else if (ch == '.' && !dot) dot = true;
+        else break;
     }
     if (!any) return kLineMalformed;                             // "nan", "inf", stray text
     if (p < end && (b[p] == 'e' || b[p] == 'E')) {
