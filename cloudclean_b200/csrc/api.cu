@@ -575,8 +575,8 @@ int ccg_don(ccg_ctx *ctx, const void *normals, size_t stride_bytes, double r1, d
     CCG_TRY(oo.open(ctx, 0, don4, n * 16));
     CCG_TRY(query_begin(ctx));
     // the reference passes float radii to pcl::search::KdTree (don(cloud, normals, float radius1, float radius2))
-    CCG_TRY(launch_tile_attrsum(ctx, radius_bound((double)(float)r1, 1), nd, stride_bytes, s1, c1));
-    CCG_TRY(launch_tile_attrsum(ctx, radius_bound((double)(float)r2, 1), nd, stride_bytes, s2, c2));
+    // both radii in one traversal (the walk is pruned by the larger one)
+    CCG_TRY(launch_tile_attrsum2(ctx, radius_bound((double)(float)r1, 1), radius_bound((double)(float)r2, 1), nd, stride_bytes, s1, c1, s2, c2));
     k_don_combine<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(s1, c1, s2, c2, (const char *)nd, stride_bytes, n, oo.dev<float>());
     ctx->stats.launches++;
     CCG_TRY(query_end(ctx));

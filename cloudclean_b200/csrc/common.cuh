@@ -189,6 +189,8 @@ struct PointArgs {
 int launch_point_query(ccg_ctx *ctx, const PointArgs &a);
 
 int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count);
+int launch_tile_attrsum2(ccg_ctx *ctx, float rb1, float rb2, const void *attr_dev, size_t stride, float *sum1, int32_t *count1,
+                         float *sum2, int32_t *count2);
 int launch_tile_principal_curv(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *pc5);
 int launch_tile_fpfh(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *spfh33, float *fpfh33);
 int launch_features(ccg_ctx *ctx, const float *eig3, size_t n, int formula_set, float *out);

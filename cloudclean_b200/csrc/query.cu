@@ -246,6 +246,34 @@ struct AttrSum {
     }
 };
 
+// two radii in one traversal (difference of normals): the walk is bounded by the larger one
+struct AttrSum2 {
+    float bound;                 // max(b1, b2): what the traversal prunes with
+    float b1, b2;
+    int c1, c2;
+    float s1[3], s2[3];
+    const char *attr; size_t stride;
+    __device__ __forceinline__ void init(float rb1, float rb2, bool active, const char *attr_, size_t stride_) {
+        b1 = active ? rb1 : -1.f; b2 = active ? rb2 : -1.f; bound = fmaxf(b1, b2);
+        c1 = c2 = 0; attr = attr_; stride = stride_;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) s1[i] = s2[i] = 0.f;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 4
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            const float d2 = d2_point(q, c);
+            if (d2 <= bound) {
+                const float *a = reinterpret_cast<const float *>(attr + (size_t)__float_as_int(c.w) * stride);
+                const float x = __ldg(a), y = __ldg(a + 1), z = __ldg(a + 2);
+                if (d2 <= b1) { ++c1; s1[0] = __fadd_rn(s1[0], x); s1[1] = __fadd_rn(s1[1], y); s1[2] = __fadd_rn(s1[2], z); }
+                if (d2 <= b2) { ++c2; s2[0] = __fadd_rn(s2[0], x); s2[1] = __fadd_rn(s2[1], y); s2[2] = __fadd_rn(s2[2], z); }
+            }
+        }
+    }
+};
+
 // streaming visitor for f4 (principal curvatures): first and second moments of (attr_j - ref) over everything inside
 // the radius, ref = the query's own attribute — the shift keeps the sums small where the attribute varies slowly
 struct AttrMoments {
@@ -1318,6 +1346,33 @@ int launch_tile_fpfh(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride
     k_tile_spfh<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, (const char *)attr_dev, stride, spfh33);
     k_tile_fpfh<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb, spfh33, fpfh33);
     ctx->stats.launches += 2;
+    CCG_CUDA(ctx, cudaGetLastError());
+    return CCG_OK;
+}
+
+__global__ void __launch_bounds__(128) k_tile_attrsum2(const __grid_constant__ TreeView T, float rb1, float rb2, const char *attr, size_t stride,
+                                                       float *sum1, int32_t *count1, float *sum2, int32_t *count2) {
+    __shared__ WarpScratch s_ws[4];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * 4 + warp;
+    if (tile >= T.count[0]) return;
+    const size_t pos = (size_t)tile * kLeaf + lane;
+    const float4 q = T.pts[pos];
+    const bool active = pos < (size_t)T.n;
+    AttrSum2 v;
+    v.init(rb1, rb2, active, attr, stride);
+    traverse_tile(T, tile, q, v, s_ws[warp]);
+    if (!active) return;
+    const size_t row = (size_t)__float_as_int(q.w);
+    sum1[3 * row] = v.s1[0]; sum1[3 * row + 1] = v.s1[1]; sum1[3 * row + 2] = v.s1[2]; count1[row] = v.c1;
+    sum2[3 * row] = v.s2[0]; sum2[3 * row + 1] = v.s2[1]; sum2[3 * row + 2] = v.s2[2]; count2[row] = v.c2;
+}
+
+int launch_tile_attrsum2(ccg_ctx *ctx, float rb1, float rb2, const void *attr_dev, size_t stride, float *sum1, int32_t *count1,
+                         float *sum2, int32_t *count2) {
+    if (ctx->n == 0) return CCG_OK;
+    k_tile_attrsum2<<<(ctx->nleaf + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), rb1, rb2, (const char *)attr_dev, stride, sum1, count1, sum2, count2);
+    ctx->stats.launches++;
     CCG_CUDA(ctx, cudaGetLastError());
     return CCG_OK;
 }
