@@ -25,9 +25,7 @@
 #include "common.cuh"
 #include <cub/block/block_reduce.cuh>
 #include <cub/block/block_scan.cuh>
-#include <cub/device/device_reduce.cuh>
 #include <cub/device/device_scan.cuh>
-#include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
 
