@@ -236,3 +236,18 @@ def test_ptx_flood_of_blank_lines(gpu_ctx, tmp_path):
     got = gpu_ctx.ptx_load(path, 1)
     _same(got, oracle.load_ptx(path, 1))
     assert got["lines"] == 2400
+
+
+def test_ptx_device_bytes_at_odd_addresses(gpu_ctx, tmp_path):
+    """the segment grid is laid on 16-byte aligned ADDRESSES: a device buffer that starts at any byte offset (a view into
+    a larger tensor) must parse to the same rows"""
+    import torch
+    path = tmp_path / "scan.ptx"
+    synth.write_ptx(path, 50, 41, seed=8, style="mixed")
+    raw = np.frombuffer(path.read_bytes(), np.uint8)
+    want = oracle.load_ptx(path, 1)
+    for off in (1, 2, 3, 5, 8, 11, 15, 16, 31):
+        buf = torch.full((off + raw.size + 64,), ord("\n"), dtype=torch.uint8, device="cuda")      # newlines around: must not leak in
+        buf[off:off + raw.size] = torch.from_numpy(raw.copy()).cuda()
+        got = gpu_ctx.ptx_parse(buf[off:off + raw.size], 1)
+        _same(got, want)
