@@ -15,3 +15,6 @@ echo "ncu launches rc=$?"
 $CMD > gpurun_out/plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:k_tile_sel -s 1 -c 1 -f -o gpurun_out/prof_sel $CMD > gpurun_out/ncu2.log 2>&1
 echo "ncu full rc=$?"
+# next rows: adapters program, PTX ingest timing (8.4 M lines), uncapped radius features at full size
+./adapters/test_adapters > gpurun_out/adapters.log 2>&1; echo "adapters rc=$?"
+python tools/ptx_bench.py 4096 2048 > gpurun_out/ptx_bench.log 2>&1; echo "ptx bench rc=$?"; tail -4 gpurun_out/ptx_bench.log
