@@ -251,3 +251,16 @@ def test_ptx_device_bytes_at_odd_addresses(gpu_ctx, tmp_path):
         buf[off:off + raw.size] = torch.from_numpy(raw.copy()).cuda()
         got = gpu_ctx.ptx_parse(buf[off:off + raw.size], 1)
         _same(got, want)
+
+
+def test_ptx_golden(gpu_ctx):
+    """the CUDA parser against the committed golden vectors (exact-rational float32 rounding, no libc)"""
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(here, "scan12x9_ptx.npz"))
+    for dec in (1, 2):
+        r = gpu_ctx.ptx_load(os.path.join(here, "scan12x9.ptx"), dec)
+        assert (r["file_width"], r["file_height"]) == tuple(g["size"])
+        assert r["sampled"] == int(g[f"sampled_dec{dec}"])
+        assert np.array_equal(r["points"].view(np.int32), g[f"points_dec{dec}"].view(np.int32))
+        assert np.array_equal(r["cloud_to_grid"], g[f"c2g_dec{dec}"])
+        assert np.array_equal(r["origin"], g["origin"]) and np.array_equal(r["matrix"], g["matrix"])

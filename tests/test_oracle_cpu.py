@@ -216,3 +216,18 @@ def test_load_ptx_restatement_against_a_line_by_line_reading(tmp_path):
         assert res["sampled"] == sampled
         assert np.array_equal(res["points"].view(np.int32), np.array(rows, np.float32).view(np.int32))
         assert np.array_equal(res["cloud_to_grid"], np.array(c2g, np.int32))
+
+
+def test_load_ptx_golden():
+    """the stdio restatement against tests/golden/scan12x9_ptx.npz (Python line reader + exact-rational float32 rounding,
+    tests/golden/make_golden_ptx.py)"""
+    import os
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(here, "scan12x9_ptx.npz"))
+    for dec in (1, 2):
+        r = oracle.load_ptx(os.path.join(here, "scan12x9.ptx"), dec)
+        assert (r["file_width"], r["file_height"]) == tuple(g["size"])
+        assert r["sampled"] == int(g[f"sampled_dec{dec}"])
+        assert np.array_equal(r["points"].view(np.int32), g[f"points_dec{dec}"].view(np.int32))
+        assert np.array_equal(r["cloud_to_grid"], g[f"c2g_dec{dec}"])
+        assert np.array_equal(r["origin"], g["origin"]) and np.array_equal(r["matrix"], g["matrix"])
