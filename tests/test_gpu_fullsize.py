@@ -147,3 +147,25 @@ def test_config2_sor_mask_at_full_size():
         interior = rd[:, 30] < (wall.astype(np.float64) ** 2) * 0.999
         assert interior.sum() > 500
         assert np.array_equal(h[sel.cpu().numpy()][interior], rmd[interior])
+
+
+def test_ptx_ingest_at_scan_size(tmp_path):
+    """PTX ingest (row f4) at the size of a real scan: 4096 x 2048 = 8.4 M lines (0.3 GB of text), every row bit-identical to
+    the oracle's stdio restatement of PointCloud::load_ptx, with and without decimation"""
+    w, h = 4096, 2048
+    n = w * h
+    rng = np.random.default_rng(7)
+    rows = np.zeros((n, 8), np.float32)
+    rows[:, :3] = rng.normal(size=(n, 3)).astype(np.float32) * np.array([15.0, 12.0, 3.0], np.float32)
+    rows[:, 4] = rng.random(n, dtype=np.float32)
+    rows[rng.random(n) < 0.1, 0] = np.nan                    # no-return lines ("0 0 0 0.5")
+    path = tmp_path / "scan.ptx"
+    assert oracle.write_ptx(path, rows, w, h) == n
+    with cc.Context(0) as ctx:
+        for dec in (1, 4):
+            got = ctx.ptx_load(path, dec)
+            want = oracle.load_ptx(path, dec)
+            assert got["sampled"] == want["sampled"] == (w // dec) * (h // dec)
+            assert got["points"].shape[0] == want["points"].shape[0] > 0.85 * want["sampled"]
+            assert np.array_equal(got["points"].view(np.int32), want["points"].view(np.int32))
+            assert np.array_equal(got["cloud_to_grid"], want["cloud_to_grid"])
