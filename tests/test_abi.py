@@ -62,3 +62,21 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".cpp", ".h", ".hpp")) and not f.startswith("test_"):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "ccoracle" not in text and "cco_" not in text, f
+
+
+def test_struct_layouts_match_the_header(tmp_path):
+    """ctypes mirrors of the header's structs have the C compiler's sizes and field offsets"""
+    import subprocess
+    fields = [f[0] for f in cc.PtxInfo._fields_]
+    prog = ['#include <stdio.h>', '#include <stddef.h>', '#include "ccgpu.h"', "int main(void) {",
+            '  printf("%zu\\n", sizeof(ccg_ptx_info));']
+    prog += [f'  printf("%zu\\n", offsetof(ccg_ptx_info, {f}));' for f in fields]
+    prog += ['  printf("%zu\\n", sizeof(ccg_stats));', "  return 0; }"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(prog))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert out[0] == ctypes.sizeof(cc.PtxInfo)
+    assert out[1:1 + len(fields)] == [getattr(cc.PtxInfo, f).offset for f in fields]
+    assert out[-1] == ctypes.sizeof(cc.Stats)
