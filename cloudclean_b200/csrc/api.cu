@@ -56,7 +56,7 @@ static int begin_call(ccg_ctx *ctx, bool need_cloud) {
     return CCG_OK;
 }
 static int query_begin(ccg_ctx *ctx) { CCG_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream)); return CCG_OK; }
-static int query_end(ccg_ctx *ctx) { CCG_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream)); return CCG_OK; }
+static int query_end(ccg_ctx *ctx) { CCG_TRY(join_side(ctx)); CCG_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream)); return CCG_OK; }
 static int finish_call(ccg_ctx *ctx) {
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
     CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -172,6 +172,7 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
     for (int c = 1; c < nch; ++c) bound[c] = hb[c] < n ? hb[c] : n;
     bound[nch] = n;
     a.tile_order = dv.Current();
+    a.async_side = 1;
     int launches = ctx->stats.launches;
     for (int c = 0; c < nch; ++c) {
         if (ctx->cancel && *ctx->cancel) return set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller");
@@ -182,6 +183,9 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
         launches += ctx->stats.launches;
         CCG_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[c], st));
         CCG_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[c], 0));
+        if (ctx->side_pending)                                       // this chunk's deferred queries (point kernel, side stream)
+            for (int i = 0; i < 2; ++i)
+                if (ctx->ev_side[i]) CCG_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_side[i], 0));
         const size_t r0 = bound[c], r1 = bound[c + 1];
         if (r1 > r0)
             for (int i = 0; i < nouts; ++i)
@@ -359,6 +363,16 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
     const char *sp = getenv("CCG_SPLIT_SPARSE");
     ctx->split_sparse = (sp && sp[0] == '0') ? 0 : 1;
+    const char *cv = getenv("CCG_CURVE");
+    ctx->curve_hilbert = (cv && cv[0] == 'm') ? 0 : 1;
+    const char *da = getenv("CCG_SEL_DRAIN_AT");
+    if (da) ctx->sel_drain_at = atoi(da);
+    const char *sg = getenv("CCG_SEL_STAGE");
+    ctx->sel_stage = (sg && sg[0] == 'l') ? 0 : 1;
+    const char *sc = getenv("CCG_SEL_CHUNKS");
+    if (sc) ctx->sel_chunks = atoi(sc);
+    const char *po = getenv("CCG_POINT_OVERLAP");
+    ctx->point_overlap = (po && po[0] == '0') ? 0 : 1;
     const char *kt = getenv("CCG_KNN_TOPK");
     ctx->knn_use_topk = (kt && kt[0] == '1') ? 1 : 0;
     const char *pc = getenv("CCG_PIPELINE_CHUNKS");
@@ -373,11 +387,14 @@ void ccg_destroy(ccg_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    ctx->raw.release(); ctx->orig.release(); ctx->sorted.release();
+    ctx->raw.release(); ctx->orig.release(); ctx->sorted.release(); ctx->rel.release();
     for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
     ctx->vox_out.release();
     ctx->ptx_bytes.release(); ctx->ptx_starts.release(); ctx->ptx_points.release(); ctx->ptx_c2g.release();
-    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release();
+    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release(); ctx->defer_b.release();
+    for (int i = 0; i < 2; ++i) if (ctx->ev_side[i]) cudaEventDestroy(ctx->ev_side[i]);
+    if (ctx->ev_tile) cudaEventDestroy(ctx->ev_tile);
+    if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
     for (int i = 0; i < 4; ++i) { ctx->out[i].release(); ctx->tmp[i].release(); }
     for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     for (int i = 0; i < 17; ++i) if (ctx->ev_chunk[i]) cudaEventDestroy(ctx->ev_chunk[i]);

@@ -90,20 +90,47 @@ __device__ __forceinline__ unsigned long long spread21(unsigned v) {
     return x;
 }
 
-// Morton key of every point (kMortonBits per axis, cubic cells over the bounding box) + identity values.
+// 3-D Hilbert index from the quantised coordinates (Skilling's transpose algorithm, b bits per axis), interleaved into
+// one key.  Unlike the Morton curve the Hilbert curve has no jumps: consecutive points along it are always spatial
+// neighbours, so a run of 32 consecutive points (a leaf) is a compact blob instead of, every so often, two pieces of
+// surface a Z-jump apart.  Measured on the bench scans (tools/sim_tiles.cpp): candidate leaves scanned per tile 22 -> 12.
+__device__ __forceinline__ unsigned long long hilbert_key(unsigned x, unsigned y, unsigned z) {
+    unsigned X0 = x, X1 = y, X2 = z;
+    constexpr unsigned M = 1u << (kMortonBits - 1);
+#pragma unroll
+    for (unsigned Q = M; Q > 1; Q >>= 1) {
+        const unsigned P = Q - 1;
+        if (X0 & Q) X0 ^= P;                                        // axis 0: invert low bits of X0
+        if (X1 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X1) & P; X0 ^= t; X1 ^= t; }
+        if (X2 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X2) & P; X0 ^= t; X2 ^= t; }
+    }
+    X1 ^= X0; X2 ^= X1;
+    unsigned t = 0;
+#pragma unroll
+    for (unsigned Q = M; Q > 1; Q >>= 1) if (X2 & Q) t ^= Q - 1;
+    X0 ^= t; X1 ^= t; X2 ^= t;
+    return spread21(X2) | (spread21(X1) << 1) | (spread21(X0) << 2);
+}
+
+// Space-filling-curve key of every point (kMortonBits per axis, cubic cells over the bounding box) + identity values.
 // 16 bits per axis = 48-bit keys = 6 radix passes instead of 8 (the sort is 60 % of the build): cells of extent/65536
 // (1.5 mm on a 100 m scan) are below the point spacing almost everywhere, and points sharing a cell simply keep their
 // original (scan) order — the order is only a permutation, search results do not depend on it.
-__global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig, int n, float3 lo, float inv_cell,
+// The bounding box is read from the ingest scratch ON THE DEVICE (no host round trip in the middle of the build).
+template <bool HILBERT>
+__global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig, int n, const IngestScratch *__restrict__ sc,
                                                 unsigned long long *__restrict__ keys, unsigned *__restrict__ vals) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const float lx = ord2f(sc->lo[0]), ly = ord2f(sc->lo[1]), lz = ord2f(sc->lo[2]);
+    const float ext = fmaxf(fmaxf(ord2f(sc->hi[0]) - lx, ord2f(sc->hi[1]) - ly), ord2f(sc->hi[2]) - lz);
+    const float inv_cell = ext > 0.f ? __fdiv_rn((float)(1u << kMortonBits), __fmul_rn(ext, 1.0001f)) : 0.f;
     float4 p = orig[i];
     constexpr float qmax = (float)((1u << kMortonBits) - 1u);
-    unsigned qx = (unsigned)fminf(fmaxf((p.x - lo.x) * inv_cell, 0.f), qmax);
-    unsigned qy = (unsigned)fminf(fmaxf((p.y - lo.y) * inv_cell, 0.f), qmax);
-    unsigned qz = (unsigned)fminf(fmaxf((p.z - lo.z) * inv_cell, 0.f), qmax);
-    keys[i] = spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
+    unsigned qx = (unsigned)fminf(fmaxf((p.x - lx) * inv_cell, 0.f), qmax);
+    unsigned qy = (unsigned)fminf(fmaxf((p.y - ly) * inv_cell, 0.f), qmax);
+    unsigned qz = (unsigned)fminf(fmaxf((p.z - lz) * inv_cell, 0.f), qmax);
+    keys[i] = HILBERT ? hilbert_key(qx, qy, qz) : (spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2));
     vals[i] = (unsigned)i;
 }
 
@@ -150,10 +177,15 @@ __global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ o
     if (valid) dense[i] = (iso > kIsoFactor * kIsoFactor * med) ? 0 : 1;
 }
 
-// One warp per leaf: gather the 32 points of the leaf in Morton order, tag them with their original index,
-// and reduce the leaf's bounding box.  Pad slots of the last leaf are +inf points with index INT_MAX.
+// One warp per leaf: gather the 32 points of the leaf in curve order, tag them with their original index, reduce the
+// leaf's bounding box, and write the leaf's PREFILTER BLOCK (kRelStride float4 = 528 B, see query.cu):
+//   [0]      = (cx, cy, cz, 0)                    box centre c = 0.5 * (lo + hi)
+//   [1 + 2p] = (X(2p), X(2p+1), Y(2p), Y(2p+1))   P = p - c of candidates 2p and 2p+1, pair-interleaved so that one
+//   [2 + 2p] = (Z(2p), Z(2p+1), W(2p), W(2p+1))   packed FFMA2 scores two candidates; W = -|P|^2
+// A candidate leaf is then staged into shared memory by a plain copy (one cp.async.bulk), with no per-tile arithmetic.
+// Pad slots of the last leaf are +inf points with index INT_MAX (their block entries are inf / -inf: never a neighbour).
 __global__ void __launch_bounds__(256) k_reorder_leaves(const float4 *__restrict__ orig, const unsigned *__restrict__ order,
-                                                        int n, int nleaf, float4 *__restrict__ sorted,
+                                                        int n, int nleaf, float4 *__restrict__ sorted, float4 *__restrict__ rel,
                                                         float4 *__restrict__ lo0, float4 *__restrict__ hi0) {
     int leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
@@ -178,6 +210,15 @@ __global__ void __launch_bounds__(256) k_reorder_leaves(const float4 *__restrict
         lo0[leaf] = make_float4(lx, ly, lz, 0.f);
         hi0[leaf] = make_float4(hx, hy, hz, 0.f);
     }
+    const float cx = __fmul_rn(0.5f, __fadd_rn(lx, hx)), cy = __fmul_rn(0.5f, __fadd_rn(ly, hy)), cz = __fmul_rn(0.5f, __fadd_rn(lz, hz));
+    const float X = p.x - cx, Y = p.y - cy, Z = p.z - cz;
+    const float W = -fmaf(X, X, fmaf(Y, Y, Z * Z));
+    // even lane 2p writes [1 + 2p] = (X, X', Y, Y'), odd lane 2p+1 writes [2 + 2p] = (Z', Z, W', W) with ' = the partner's value
+    const float oX = __shfl_xor_sync(kFull, X, 1), oY = __shfl_xor_sync(kFull, Y, 1), oZ = __shfl_xor_sync(kFull, Z, 1),
+                oW = __shfl_xor_sync(kFull, W, 1);
+    float4 *blk = rel + (size_t)leaf * kRelStride;
+    blk[1 + lane] = (lane & 1) ? make_float4(oZ, Z, oW, W) : make_float4(X, oX, Y, oY);
+    if (lane == 0) blk[0] = make_float4(cx, cy, cz, 0.f);
 }
 
 // One warp per parent: lane c reduces child c's box.
@@ -247,6 +288,7 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
     CCG_CUDA(ctx, ctx->boxes_hi.reserve(off * sizeof(float4)));
     CCG_CUDA(ctx, ctx->orig.reserve(n * sizeof(float4)));
     CCG_CUDA(ctx, ctx->sorted.reserve(npad * sizeof(float4)));
+    CCG_CUDA(ctx, ctx->rel.reserve((size_t)nleaf * kRelStride * sizeof(float4)));
     for (int b = 0; b < 2; ++b) {
         CCG_CUDA(ctx, ctx->keys[b].reserve(n * sizeof(unsigned long long)));
         CCG_CUDA(ctx, ctx->vals[b].reserve(n * sizeof(unsigned)));
@@ -282,23 +324,15 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
         else k_ingest<false><<<blocks, 256, 0, st>>>(src_dev, stride, (int)n, ctx->orig.as<float4>(), ctx->scratch.as<IngestScratch>());
         ctx->stats.launches_build++;
     }
-    IngestScratch res;
-    CCG_CUDA(ctx, cudaMemcpyAsync(&res, ctx->scratch.p, sizeof(res), cudaMemcpyDeviceToHost, st));
-    CCG_CUDA(ctx, cudaStreamSynchronize(st));
-    if (res.nonfinite) return set_error(ctx, CCG_ERR_NONFINITE, "cloud holds non-finite coordinates");
-    float ext = 0.f;
-    for (int d = 0; d < 3; ++d) {
-        ctx->bb_lo[d] = ord2f(res.lo[d]);
-        ctx->bb_hi[d] = ord2f(res.hi[d]);
-        ext = fmaxf(ext, ctx->bb_hi[d] - ctx->bb_lo[d]);
-    }
-    float inv_cell = ext > 0.f ? (float)(1u << kMortonBits) / (ext * 1.0001f) : 0.f;
-
     // ---- Morton keys + radix sort ---------------------------------------------------------------------
     {
         int blocks = (int)((n + 255) / 256);
-        k_morton<<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, make_float3(ctx->bb_lo[0], ctx->bb_lo[1], ctx->bb_lo[2]),
-                                         inv_cell, ctx->keys[0].as<unsigned long long>(), ctx->vals[0].as<unsigned>());
+        if (ctx->curve_hilbert)
+            k_morton<true><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(),
+                                                   ctx->keys[0].as<unsigned long long>(), ctx->vals[0].as<unsigned>());
+        else
+            k_morton<false><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(),
+                                                    ctx->keys[0].as<unsigned long long>(), ctx->vals[0].as<unsigned>());
         ctx->stats.launches_build++;
     }
     {
@@ -331,7 +365,7 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
         float4 *lo = ctx->boxes_lo.as<float4>(), *hi = ctx->boxes_hi.as<float4>();
         int blocks = (nleaf + 7) / 8;
         k_reorder_leaves<<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), ctx->vals[ctx->order_sel].as<unsigned>(), (int)n, nleaf,
-                                                 ctx->sorted.as<float4>(), lo + ctx->level_off[0], hi + ctx->level_off[0]);
+                                                 ctx->sorted.as<float4>(), ctx->rel.as<float4>(), lo + ctx->level_off[0], hi + ctx->level_off[0]);
         ctx->stats.launches_build++;
         for (int l = 1; l < nlevels; ++l) {
             int np = counts[l];
@@ -340,9 +374,15 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
             ctx->stats.launches_build++;
         }
     }
+    // the bounding box and the finiteness flag come back with the ONE synchronisation at the end of the build
+    CCG_CUDA(ctx, ctx->hpin[1].reserve(256));
+    IngestScratch *res = ctx->hpin[1].as<IngestScratch>();
+    CCG_CUDA(ctx, cudaMemcpyAsync(res, ctx->scratch.p, sizeof(IngestScratch), cudaMemcpyDeviceToHost, st));
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
     CCG_CUDA(ctx, cudaStreamSynchronize(st));
     CCG_CUDA(ctx, cudaGetLastError());
+    if (res->nonfinite) return set_error(ctx, CCG_ERR_NONFINITE, "cloud holds non-finite coordinates");
+    for (int d = 0; d < 3; ++d) { ctx->bb_lo[d] = ord2f(res->lo[d]); ctx->bb_hi[d] = ord2f(res->hi[d]); }
     cudaEventElapsedTime(&ctx->stats.ms_upload, ctx->ev[0], ctx->ev[1]);
     cudaEventElapsedTime(&ctx->stats.ms_build, ctx->ev[1], ctx->ev[2]);
     ctx->n = n; ctx->npad = npad; ctx->nleaf = nleaf; ctx->nlevels = nlevels;

@@ -11,6 +11,7 @@ namespace ccg {
 
 constexpr int kLeaf = 32;        // points per leaf of the Morton order == one warp-wide float4 load (512 B)
 constexpr int kFan = 32;         // children per inner node == one lane per child
+constexpr int kRelStride = 33;   // float4 per leaf of the prefilter block array (centre + 16 pair-interleaved pairs, build.cu)
 constexpr int kMaxLevels = 8;    // 32^8 leaves is far beyond any cloud
 constexpr unsigned kFull = 0xffffffffu;
 
@@ -18,6 +19,7 @@ constexpr unsigned kFull = 0xffffffffu;
 struct TreeView {
     const float4 *pts;               // sorted points, npad = nleaf*32; w = original index (int bits); pads = +inf
     const float4 *orig;              // original-order points (w unused), for the PCA gather
+    const float4 *rel;               // per leaf kRelStride float4: prefilter block (leaf-centre-relative, pair-interleaved)
     const float4 *lo[kMaxLevels];    // per level: box min (w unused)
     const float4 *hi[kMaxLevels];    // per level: box max
     int count[kMaxLevels];           // nodes per level; level 0 = leaves
@@ -79,7 +81,8 @@ struct ccg_ctx {
 
     ccg::DevBuf raw;         // staged AoS input (host clouds only)
     ccg::DevBuf orig;        // float4[n]   original order
-    ccg::DevBuf sorted;      // float4[npad] Morton order, w = original index
+    ccg::DevBuf sorted;      // float4[npad] curve order, w = original index
+    ccg::DevBuf rel;         // float4[nleaf * kRelStride] prefilter blocks
     ccg::DevBuf keys[2];     // uint64[n] Morton keys (double buffer)
     ccg::DevBuf vals[2];     // uint32[n] original index (double buffer); vals[order_sel] is the final order
     int order_sel = 0;
@@ -92,7 +95,10 @@ struct ccg_ctx {
     int64_t vox_n = 0; int vox_nf = 0;
     ccg::DevBuf ptx_bytes, ptx_starts, ptx_points, ptx_c2g;   // last ccg_ptx_parse: file bytes, line starts, 32-byte rows, cloud_to_grid_map
     int64_t ptx_n = 0;
-    ccg::DevBuf defer;       // [count | query list | output rows] of queries deferred to the exact point kernel
+    ccg::DevBuf defer, defer_b;   // [count | query list | output rows] of queries deferred to the exact point kernel (double buffer)
+    int defer_sel = 0, side_pending = 0, last_side = 0;
+    cudaStream_t side_stream = nullptr;  // the point kernel of launch i runs here, next to tile launch i+1
+    cudaEvent_t ev_side[2] = {}, ev_tile = nullptr;
     ccg::HostBuf hpin[2];    // pinned bounce buffers
     float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};
 
@@ -102,6 +108,11 @@ struct ccg_ctx {
     int pipeline_min_points = 1 << 18;
     int shard_world = 0, shard_rank = 0, shard_chunk = 0;   // set by ccg_*_shard around pca_common
     int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
+    int curve_hilbert = 1;   // leaf order along the Hilbert curve (CCG_CURVE=morton: Z-order, for A/B runs)
+    int sel_drain_at = 8;    // k_tile_sel: pending survivors per lane that trigger a drain (CCG_SEL_DRAIN_AT)
+    int sel_stage = 1;       // k_tile_sel leaf staging: 1 = cp.async.bulk + mbarrier ring, 0 = LDG/STS (CCG_SEL_STAGE=ldg)
+    int sel_chunks = 4;      // sub-launches of a long k_tile_sel launch (CCG_SEL_CHUNKS)
+    int point_overlap = 1;   // deferred exact queries on a side stream (CCG_POINT_OVERLAP=0: same stream)
     int split_sparse = 1;    // move isolated points to the end of the order (CCG_SPLIT_SPARSE=0 disables)
     char err[512] = "";
 
@@ -109,6 +120,7 @@ struct ccg_ctx {
         ccg::TreeView t;
         t.pts = sorted.as<float4>();
         t.orig = orig.as<float4>();
+        t.rel = rel.as<float4>();
         for (int l = 0; l < ccg::kMaxLevels; ++l) {
             t.lo[l] = boxes_lo.as<float4>() + level_off[l];
             t.hi[l] = boxes_hi.as<float4>() + level_off[l];
@@ -161,8 +173,10 @@ struct QueryArgs {
     // interleaved shard (multi-GPU load balance): this call answers the tiles t with (t / shard_chunk) % shard_world ==
     // shard_rank and ignores begin/end; shard_world <= 1 = off
     int shard_world, shard_rank, shard_chunk;
+    int async_side;         // 1: the caller joins the side stream itself (join_side) — output pipelining
 };
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a);
+int join_side(ccg_ctx *ctx);
 
 struct StreamArgs {
     int mode;               // 0: count (early-out at count_cap when > 0), 1: moments -> PCA

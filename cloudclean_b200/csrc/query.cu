@@ -675,6 +675,7 @@ struct TileParams {
     unsigned long long *stat_scanned;
     int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
     int *slow_count; int32_t *slow_tiles;                          // k_tile_sel: tiles handed to k_tile_sel_stack
+    int drain_at;                 // k_tile_sel: pending survivors per lane that trigger a pooled drain
     const int32_t *tile_order;    // k_tile_sel: non-NULL = tile_begin/tile_end index this list of tiles (output pipelining)
     int shard_world, shard_rank, shard_chunk;   // k_tile_sel: > 1 = slots enumerate the interleaved chunks of one rank
 };
@@ -756,7 +757,7 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 // with one lane per child box then lists every leaf whose box is within the warp's largest bound of the tile
 // box (ballot + popc compaction into shared memory).  Compared with the nearest-first stack walk this costs a
 // few hundred instructions per tile instead of ~100 per visited child, and pass 2 re-uses the list.
-constexpr int kListCap = 384;     // leaves listed per tile (overflow -> stack walk, exact as well)
+constexpr int kListCap = 256;     // leaves listed per tile before the per-query refinement (overflow: sub-box retry, then the point kernel)
 constexpr int kQueueCap = 128;     // inner nodes per level
 struct WarpScratch2 {
     WarpScratch ws;
@@ -832,188 +833,356 @@ __device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, boo
     __syncwarp();
 }
 
-// mask of the staged candidates that may lie within `bound` of the lane's query (never misses one; see ValLog)
-__device__ __forceinline__ unsigned prefilter(const float4 &qr, const float4 *rel, float bound) {
-    unsigned m = 0;
-    const float thr = __fadd_ru(__fsub_ru(bound, qr.w), __fmul_ru(1.5258789e-5f, __fadd_ru(qr.w, bound)));
-#pragma unroll
-    for (int j = 0; j < kLeaf; ++j) {
-        const float4 c = rel[j];
-        const float a = fmaf(qr.x, c.x, fmaf(qr.y, c.y, fmaf(qr.z, c.z, c.w)));
-        m |= (a <= thr) ? (1u << j) : 0u;
-    }
-    return m;
+// ---------------------------------------------------------------------------------------------------
+// k_tile_sel, round 2: queue-based two-pass selection
+// ---------------------------------------------------------------------------------------------------
+// What r01's ncu profile said (profiles/r01_sel_v13_ncu_lines.txt) and what tools/sim_tiles.cpp adds to it: per tile the
+// kernel prefiltered ~28 leaves and then DRAINED each leaf's survivors on the spot — ~70 instructions per round, with
+// ~65 rounds per tile for the listed leaves although they hold only ~8 survivors per query (a leaf's survivors sit in the
+// 2-3 lanes next to it: 10 of 32 lanes active), plus ~78 rounds for the three home leaves.  This version
+//   * scores the home leaves directly (every lane wants nearly every candidate there: no mask, no drain);
+//   * keeps, of each listed leaf, only the per-lane 32-bit SURVIVOR MASK of a 4-instruction-per-candidate prefilter
+//     (packed FFMA2 on pair-interleaved, leaf-centre-relative blocks that build.cu precomputes, sign bits collected by a
+//     funnel shift) in a per-lane queue in shared memory, and scores the queued survivors in pooled rounds — lanes
+//     balance across leaves, so the expensive ordered insert runs ~20 times per tile instead of ~65;
+//   * refines the candidate list per query ONCE (one lane per listed leaf against the 32 queries) instead of testing
+//     a box per leaf and lane inside the loop, which also lets the staging copy only wanted leaves;
+//   * stages a leaf's 528-byte block with ONE cp.async.bulk into a 2-stage mbarrier ring (the north star's "TMA bulk
+//     copy where the cell run is contiguous"; CCG_SEL_STAGE=ldg selects an LDG/STS ring for the A/B profile);
+//   * re-uses the queue as the log of pass 2 (drains clear the bits that fell outside the bound).
+constexpr int kSelStages = 2;
+constexpr int kQCap = 20;              // queue entries per lane: listed leaves use <= kQCap - 3, pass 2 adds the 3 home leaves
+constexpr int kSlotHome = 253;         // qslot codes 253 / 254 / 255 = own leaf / previous / next
+constexpr int kListMax = 252;          // listed leaves a tile may keep after the per-query refinement (u8 slots)
+
+struct alignas(16) SelScratch {
+    WarpScratch2 w;                        // w.ws.leaf: the 32 queries, or a home neighbour's exact points; w.list; w.sub
+    float4 blk[kSelStages][kRelStride];    // staged prefilter blocks
+    union {
+        struct { unsigned qmask[kQCap * 32]; unsigned char qslot[kQCap * 32]; } q;   // entry e of lane l at [e * 32 + l]
+        int queue[2][kQueueCap];           // breadth-first queues of collect_leaves (dead before the first queue entry)
+    };
+    float sbound[32];
+    unsigned long long bar[kSelStages];
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!ok);
 }
 
-// Pass-1 visitor of k_tile_sel: the value list of ValK plus (LOG) a per-lane LOG in shared memory of every
-// candidate of a LISTED leaf that was inside the lane's bound when it was scored.  The final neighbour set
-// {d2 <= T} is a subset of the home leaves' points and the log (T <= bound at all times), so pass 2 never rescans
-// the list: it re-scores the three home leaves against T and walks the log.  A log entry is 16 bits,
-// (list index << 5 | position in leaf); dropping stale entries (compact) re-scores them from the point array.
-template <int K> struct LogCap { static constexpr int value = K <= 32 ? 96 : 128; };
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
 
-template <int K, bool LOG>
-struct ValLog {
+// Prefilter of one staged block against the lane's query: bit (31 - j) of the result is set when candidate j MAY lie within
+// `bound` of q.  With C the leaf's box centre, P = p - C (precomputed, W = -|P|^2) and Q = q - C:
+//     d2 = |P|^2 - 2 P.Q + |Q|^2,   s_j = thr + W_j + 2 Q.P_j,   thr = bound - |Q|^2 + margin,   pass <=> s_j >= 0.
+// Rounding: P, Q carry 2^-24 relative error per coordinate, W and |Q|^2 three fused roundings each, s_j one add and three
+// fma; together below 2^-20 (|P| + |Q|)^2.  A true neighbour (contract d2 <= bound) has |P| <= |Q| + sqrt(bound)(1 + 2^-22),
+// so (|P| + |Q|)^2 <= 8 |Q|^2 + 2 bound + ..., i.e. an error below 2^-17 |Q|^2 + 2^-19 bound.  margin = 2^-15 (|Q|^2 + bound),
+// rounded up, never rejects one.  Survivors are always re-scored with the contract arithmetic before they count.
+// Two candidates per instruction: packed fma.rn.f32x2 (FFMA2, sm_100) on the pair-interleaved block layout; the sign
+// bits are shifted into the mask with one funnel shift each (reject bits; the caller gets the complement).
+__device__ __forceinline__ unsigned prefilter_blk(const float4 *blk, const float4 &q, float bound) {
+    const float4 c = blk[0];
+    const float qx = q.x - c.x, qy = q.y - c.y, qz = q.z - c.z;
+    const float qq = fmaf(qx, qx, fmaf(qy, qy, qz * qz));
+    const float thr = __fadd_ru(__fsub_ru(bound, qq), __fmul_ru(3.0517578125e-5f, __fadd_ru(qq, bound)));
+    const f32x2 AX = pack2(2.f * qx, 2.f * qx), AY = pack2(2.f * qy, 2.f * qy), AZ = pack2(2.f * qz, 2.f * qz), TH = pack2(thr, thr);
+    unsigned m = 0;
+#pragma unroll
+    for (int p = 0; p < kLeaf / 2; ++p) {
+        const float4 a = blk[1 + 2 * p], b = blk[2 + 2 * p];      // (X0 X1 Y0 Y1), (Z0 Z1 W0 W1)
+        f32x2 s = add2(TH, pack2(b.z, b.w));
+        s = fma2(AZ, pack2(b.x, b.y), s);
+        s = fma2(AY, pack2(a.z, a.w), s);
+        s = fma2(AX, pack2(a.x, a.y), s);
+        m = __funnelshift_l((unsigned)s, m, 1);
+        m = __funnelshift_l((unsigned)(s >> 32), m, 1);
+    }
+    return bound >= 0.f ? ~m : 0u;
+}
+
+// sorted list of the K smallest d2 VALUES seen (front slots pinned to -1 when k < K); see the r01 notes at ValK above
+template <int K>
+struct ValList {
     float key[K];
-    float bound, rb;
-    int cnt;                  // log entries of this lane
-    int slot;                 // list index of the leaf being scored (warp-uniform); < 0: home leaf, not logged
-    unsigned short *log;      // this lane's column: entry e at log[e * 32]
-
-    __device__ __forceinline__ void init(int k, float rb_, bool active, unsigned short *log_) {
+    float bound, rb;          // bound = min(rb, key[K-1]); -1 for lanes that take no part (pads, isolated points)
+    __device__ __forceinline__ void init(int k, float rb_, bool active) {
 #pragma unroll
         for (int i = 0; i < K; ++i) key[i] = (i < K - k) ? -1.f : INFINITY;
         rb = rb_;
         bound = active ? rb_ : -1.f;
-        cnt = 0; slot = -1; log = log_;
     }
-    __device__ __forceinline__ void insert(float c) {
+    __device__ __forceinline__ void insert(float c) {      // a no-op for c >= key[K-1]
 #pragma unroll
         for (int i = K - 1; i > 0; --i) key[i] = fmaxf(key[i - 1], fminf(key[i], c));
         key[0] = fminf(key[0], c);
     }
-    // Prefilter (all 32 candidates, every lane): d2 ~ |P|^2 - 2 P.Q + |Q|^2 with P, Q relative to the tile centre,
-    // |P|^2 staged with the candidate -> 3 FFMA + compare per candidate instead of the contract's 8 unfused
-    // operations.  Its absolute error is below 2^-19 (|P| + |Q|)^2 (roundings of P, Q, |P|^2 and of the three fma),
-    // and a true neighbour has |P| <= |Q| + sqrt(bound), so with (a+b)^2 <= 2a^2 + 2b^2 the test
-    //     fma-chain <= bound - |Q|^2 + 2^-16 (|Q|^2 + bound)
-    // never rejects one.  Survivors are re-scored with the exact contract arithmetic in the drain loop.
-    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 &qr, const float4 *exact, const float4 *rel) {
-        unsigned m = prefilter(qr, rel, bound);
-        while (__any_sync(kFull, m != 0)) {
-            if (m != 0) {
-                const int j = __ffs(m) - 1;
-                m &= m - 1;
-                const float d2 = d2_point(q, exact[j]);
-                if (d2 <= bound) {                       // inclusive: candidates tied at the k-th value must be logged
-                    if (LOG && slot >= 0) {
-                        log[cnt * 32] = (unsigned short)(slot << 5 | j);
-                        ++cnt;                           // the caller keeps 32 free entries before every leaf
-                    }
-                    if (d2 < key[K - 1]) {
-                        insert(d2);
-                        bound = fminf(rb, key[K - 1]);
-                    }
-                }
-            }
+    __device__ __forceinline__ void tighten() { bound = bound < 0.f ? -1.f : fminf(rb, key[K - 1]); }
+    // every staged point scored exactly (home leaves: nearly every lane wants nearly every candidate)
+    __device__ __forceinline__ void score_direct(const float4 &q, const float4 *pts) {
+#pragma unroll 2
+        for (int j = 0; j < kLeaf; ++j) {
+            const float d = d2_point(q, pts[j]);
+            const float c = d <= rb ? d : INFINITY;          // NaN (pad lanes) and out-of-radius candidates: no-op insert
+            if (__any_sync(kFull, c < key[K - 1])) insert(c);
         }
+        tighten();
     }
 };
 
-template <int CAP>
-struct WarpScratch3 {
-    WarpScratch2 w;
-    float4 rel[kLeaf];    // staged leaf relative to the tile centre: (P, |P|^2)
-    union {               // the breadth-first queues are only live inside collect_leaves, which runs before the first log entry
-        unsigned short log[CAP * 32];
-        int queue[2][kQueueCap];
-    };
-};
-
-// re-score this lane's log entries and keep those still within `limit` (warp-uniform trip count)
-template <int K, bool LOG, int CAP>
-__device__ __forceinline__ void compact_log(const TreeView &T, const float4 &q, ValLog<K, LOG> &v, const WarpScratch3<CAP> &S,
-                                            float limit) {
-    const int maxc = __reduce_max_sync(kFull, v.cnt);
-    int wpos = 0;
-    for (int e = 0; e < maxc; ++e) {
-        if (e < v.cnt) {
-            const unsigned id = v.log[e * 32];
-            const float4 c = T.pts[(size_t)S.w.list[id >> 5] * kLeaf + (id & 31u)];
-            if (d2_point(q, c) <= limit) { v.log[wpos * 32] = (unsigned short)id; ++wpos; }
-        }
-    }
-    v.cnt = wpos;
+__device__ __forceinline__ int sel_leaf_of(const SelScratch &S, int tile, unsigned slot) {
+    return slot < (unsigned)kSlotHome ? S.w.list[slot] : tile + (slot == (unsigned)kSlotHome ? 0 : (slot == (unsigned)kSlotHome + 1 ? -1 : 1));
 }
 
-// Pass 1 over the tile's candidate leaves: entries 0..2 are the own leaf and its Morton neighbours (always scanned:
-// they produce the bound the list is collected with), the rest is the list.  One scan site keeps the kernel
-// inside the instruction cache (ncu r01 v4: one inlined scan per case stalled on no_instruction).
-// Returns leaves scanned, or < 0 when the tile must go to the point kernel.
-template <int K, bool LOG, int CAP>
-__device__ __forceinline__ int scan_pass1(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, const float4 &q,
-                                          const float4 &qr, float cx, float cy, float cz,
-                                          ValLog<K, LOG> &v, WarpScratch3<CAP> &S, int &nlist, bool &lone) {
-    const int lane = threadIdx.x & 31;
-    lone = false;
-    int scanned = 0;
-    int total = 3;
-    // entry i+1 (its points and box) is fetched while entry i is scored: the walk is a chain of dependent L2 reads otherwise
-    int leaf = tile, nleaf = -1;
-    float4 p = q, blo = tlo, bhi = thi, np = q, nlo = tlo, nhi = thi;
-    for (int i = 0; i < total; ++i) {
-        if (i + 1 < total) {
-            if (i + 1 < 3) {
-                nleaf = tile + (i == 0 ? -1 : 1);
-                if (nleaf < 0 || nleaf >= T.count[0]) nleaf = -1;
-            } else {
-                nleaf = S.w.list[i - 2];
-            }
-            if (nleaf >= 0) {
-                np = T.pts[(size_t)nleaf * kLeaf + lane];
-                nlo = T.lo[0][nleaf]; nhi = T.hi[0][nleaf];
+// ---- staging ring: block of `leaf` -> S.blk[seq & 1] --------------------------------------------------------
+// TMA flavour: lane 0 arms the stage's mbarrier with the byte count and issues one 528-byte cp.async.bulk; the warp
+// waits on the barrier's phase parity when it gets there.  LDG flavour: every lane fetches its float4 of the block into a
+// register when the copy is "issued" and stores it to shared memory when it is "awaited".
+template <bool TMA>
+struct Stager {
+    float4 r0, r1;            // LDG flavour: lane's float4 (index lane + 1) and, lane 0, the header
+    __device__ __forceinline__ void issue(const TreeView &T, SelScratch &S, int leaf, unsigned seq, int lane) {
+        const float4 *src = T.rel + (size_t)leaf * kRelStride;
+        if (TMA) {
+            if (lane == 0) {
+                unsigned long long *bar = &S.bar[seq & (kSelStages - 1)];
+                mbar_expect_tx(bar, kRelStride * 16);
+                bulk_g2s(S.blk[seq & (kSelStages - 1)], src, kRelStride * 16, bar);
             }
         } else {
-            nleaf = -1;
+            r1 = src[1 + lane];
+            if (lane == 0) r0 = src[0];
         }
-        if (leaf >= 0) {
-            bool want = true;
-            if (i >= 3) want = d2_point_box(q, blo, bhi) <= v.bound;
-            if (__any_sync(kFull, want)) {
-                if (LOG && i >= 3) {
-                    if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) {
-                        compact_log<K, LOG, CAP>(T, q, v, S, v.bound);
-                        if (__reduce_max_sync(kFull, v.cnt) > CAP - kLeaf) return -3;   // that many ties: exact kernel decides
-                    }
-                    v.slot = i - 3;
-                }
-                const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
-                __syncwarp();
-                S.w.ws.leaf[lane] = p;
-                S.rel[lane] = make_float4(x, y, z, fmaf(x, x, fmaf(y, y, z * z)));
-                __syncwarp();
-                v.scan_leaf(q, qr, S.w.ws.leaf, S.rel);
-                ++scanned;
-            }
-        }
-        if (i == 2) {
-            // A lane whose bound is far above the warp's median after the home leaves is an isolated point inside an
-            // otherwise dense tile: its search ball would make the whole tile list hundreds of leaves.  It leaves the
-            // tile (bound -1) and is finished by the point kernel.
-            {
-                float b = v.bound >= 0.f ? v.bound : INFINITY;
-#pragma unroll
-                for (int kk = 2; kk <= 32; kk <<= 1) {
-#pragma unroll
-                    for (int j = kk >> 1; j > 0; j >>= 1) {
-                        const float o = __shfl_xor_sync(kFull, b, j);
-                        const bool up = ((lane & kk) == 0) == ((lane & j) == 0);
-                        b = up ? fminf(b, o) : fmaxf(b, o);
-                    }
-                }
-                const int nact = __popc(__ballot_sync(kFull, v.bound >= 0.f));
-                const float med = __shfl_sync(kFull, b, nact >> 1);
-                lone = v.bound >= 0.f && v.bound > 16.f * med;
-                if (lone) v.bound = -1.f;
-            }
-            const float rmax = warp_max(v.bound);
-            if (!(rmax < INFINITY)) return -4;
-            nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w, S.queue);
-            if (nlist < 0) {                    // wide or split tile: describe it by 8 sub-boxes and try again
-                make_sub_boxes(q, v.bound, v.bound >= 0.f, S.w);
-                nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w, S.queue);
-                if (nlist < 0) return -5;
-            }
-            total = 3 + nlist;
-            if (nlist > 0) {
-                nleaf = S.w.list[0];
-                np = T.pts[(size_t)nleaf * kLeaf + lane];
-                nlo = T.lo[0][nleaf]; nhi = T.hi[0][nleaf];
-            }
-        }
-        leaf = nleaf; p = np; blo = nlo; bhi = nhi;
     }
-    return scanned;
+    __device__ __forceinline__ const float4 *await(SelScratch &S, unsigned seq, int lane) {
+        float4 *dst = S.blk[seq & (kSelStages - 1)];
+        if (TMA) {
+            mbar_wait(&S.bar[seq & (kSelStages - 1)], (seq / kSelStages) & 1u);
+        } else {
+            dst[1 + lane] = r1;
+            if (lane == 0) dst[0] = r0;
+            __syncwarp();
+        }
+        return dst;
+    }
+};
+
+// keep the listed leaves that at least one query of the tile wants (point-box distance within that query's bound): one
+// lane per listed leaf against the 32 staged queries.  Needs S.w.ws.leaf = queries, S.sbound = bounds.
+__device__ __forceinline__ int refine_list(const TreeView &T, SelScratch &S, int nlist, int lane) {
+    int out = 0;
+    for (int base = 0; base < nlist; base += 32) {
+        const int i = base + lane;
+        int leaf = -1;
+        bool want = false;
+        if (i < nlist) {
+            leaf = S.w.list[i];
+            const float4 lo = T.lo[0][leaf], hi = T.hi[0][leaf];
+#pragma unroll 4
+            for (int j = 0; j < kLeaf; ++j) want |= d2_point_box(S.w.ws.leaf[j], lo, hi) <= S.sbound[j];
+        }
+        const unsigned m = __ballot_sync(kFull, want);
+        __syncwarp();
+        if (want) S.w.list[out + __popc(m & ((1u << lane) - 1u))] = leaf;
+        out += __popc(m);
+        __syncwarp();
+    }
+    return out;
+}
+
+// generator over the set bits of this lane's queue entries [ge, cnt): one candidate per call, its point fetched from the
+// sorted array (L1/L2) — the caller issues the fetch of candidate r+1 before it scores candidate r
+struct QueueWalk {
+    int ge, cnt;
+    unsigned gcur;
+    __device__ __forceinline__ void start(const SelScratch &S, int first, int cnt_, int lane) {
+        ge = first; cnt = cnt_;
+        gcur = ge < cnt ? S.q.qmask[ge * 32 + lane] : 0u;
+    }
+    __device__ __forceinline__ void next(const TreeView &T, const SelScratch &S, int tile, int lane, float4 &c, int &e, unsigned &bit) {
+        while (gcur == 0u && ge < cnt) {           // masks are non-zero until a drain cleared them: rarely more than one step
+            ++ge;
+            gcur = ge < cnt ? S.q.qmask[ge * 32 + lane] : 0u;
+        }
+        e = -1;
+        if (gcur) {
+            const int j = __clz(gcur);
+            bit = 0x80000000u >> j;
+            gcur ^= bit;
+            e = ge;
+            c = T.pts[(size_t)sel_leaf_of(S, tile, S.q.qslot[ge * 32 + lane]) * kLeaf + j];
+        }
+    }
+};
+
+// score the queued survivors of entries [first, cnt): `rounds` = the largest number of pending bits any lane holds.
+// Bits whose candidate is outside the lane's bound are cleared, so that pass 2 does not meet them again.
+template <int K>
+__device__ __forceinline__ void drain_queue(const TreeView &T, SelScratch &S, int tile, int lane, const float4 &q, ValList<K> &v,
+                                            int first, int cnt, int rounds) {
+    QueueWalk w;
+    w.start(S, first, cnt, lane);
+    float4 fc = q; int fe; unsigned fbit = 0;
+    w.next(T, S, tile, lane, fc, fe, fbit);
+    for (int r = 0; r < rounds; ++r) {
+        const float4 c = fc; const int e = fe; const unsigned bit = fbit;
+        w.next(T, S, tile, lane, fc, fe, fbit);
+        if (e >= 0) {
+            const float d = d2_point(q, c);
+            if (d <= v.bound) {
+                if (d < v.key[K - 1]) { v.insert(d); v.bound = fminf(v.rb, v.key[K - 1]); }
+            } else {
+                S.q.qmask[e * 32 + lane] &= ~bit;
+            }
+        }
+    }
+}
+
+// drop the entries a drain emptied; returns the lane's new entry count
+__device__ __forceinline__ int squeeze_queue(SelScratch &S, int cnt, int lane) {
+    const int maxc = __reduce_max_sync(kFull, cnt);
+    int w = 0;
+    for (int e = 0; e < maxc; ++e) {
+        if (e < cnt) {
+            const unsigned m = S.q.qmask[e * 32 + lane];
+            if (m) {
+                if (w != e) { S.q.qmask[w * 32 + lane] = m; S.q.qslot[w * 32 + lane] = S.q.qslot[e * 32 + lane]; }
+                ++w;
+            }
+        }
+    }
+    return w;
+}
+
+// Pass 1 for one tile.  Returns leaves prefiltered (>= 0), or < 0 when the whole tile goes to the exact point kernel
+// (-3 queue overflow = that many ties, -4 unbounded search, -5 candidate list too long).
+// On return: v = value lists and bounds, cnt = queue entries of this lane, lone = lane handed to the point kernel.
+template <int K, bool TMA>
+__device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P, int tile, const float4 &tlo, const float4 &thi,
+                                         const float4 &q, ValList<K> &v, SelScratch &S, Stager<TMA> &stg, unsigned &seq, int &cnt,
+                                         int &nlist, bool &lone, unsigned long long *st5) {
+    const int lane = threadIdx.x & 31;
+    lone = false; cnt = 0; nlist = 0;
+    // ---- home leaves, scored directly: own leaf (the staged queries), then the two curve neighbours -----------------
+    S.w.ws.leaf[lane] = q;
+    __syncwarp();
+    v.score_direct(q, S.w.ws.leaf);
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+        const int leaf = tile + (h == 0 ? -1 : 1);
+        if (leaf < 0 || leaf >= T.count[0]) continue;
+        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
+        __syncwarp();
+        S.w.ws.leaf[lane] = p;
+        __syncwarp();
+        v.score_direct(q, S.w.ws.leaf);
+    }
+    // ---- isolated lanes -> point kernel (a lane whose bound is far above the warp's median would make the tile's
+    //      candidate list hundreds of leaves long) --------------------------------------------------------------
+    {
+        float b = v.bound >= 0.f ? v.bound : INFINITY;
+#pragma unroll
+        for (int kk = 2; kk <= 32; kk <<= 1) {
+#pragma unroll
+            for (int j = kk >> 1; j > 0; j >>= 1) {
+                const float o = __shfl_xor_sync(kFull, b, j);
+                const bool up = ((lane & kk) == 0) == ((lane & j) == 0);
+                b = up ? fminf(b, o) : fmaxf(b, o);
+            }
+        }
+        const int nact = __popc(__ballot_sync(kFull, v.bound >= 0.f));
+        const float med = __shfl_sync(kFull, b, nact >> 1);
+        lone = v.bound >= 0.f && v.bound > 16.f * med;
+        if (lone) v.bound = -1.f;
+    }
+    const float rmax = warp_max(v.bound);
+    if (!(rmax < INFINITY)) return -4;
+    __syncwarp();
+    S.w.ws.leaf[lane] = q;                 // the refinement reads the queries and their bounds from shared memory
+    S.sbound[lane] = v.bound;
+    nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w, S.queue);
+    if (nlist < 0) {                       // wide or split tile: describe it by 8 sub-boxes and try again
+        make_sub_boxes(q, v.bound, v.bound >= 0.f, S.w);
+        nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w, S.queue);
+        if (nlist < 0) return -5;
+    }
+    __syncwarp();
+    const int listed = nlist;
+    nlist = refine_list(T, S, nlist, lane);
+    if (st5 && lane == 0) { atomicAdd(st5 + 2, (unsigned long long)listed); atomicAdd(st5 + 5, (unsigned long long)nlist); }
+    if (nlist > kListMax) return -5;
+    // ---- listed leaves: stage, prefilter, queue the survivor masks; pooled drains ----------------------------------
+    int first = 0, pend = 0;
+    const int drain_at = P.drain_at;
+    if (nlist > 0) stg.issue(T, S, S.w.list[0], seq, lane);
+    for (int i = 0; i < nlist; ++i) {
+        if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
+            // a full queue: score what is pending, drop the entries that emptied, give up only if it is still full
+            const int rounds = __reduce_max_sync(kFull, pend);
+            drain_queue<K>(T, S, tile, lane, q, v, first, cnt, rounds);
+            cnt = squeeze_queue(S, cnt, lane);
+            first = cnt; pend = 0;
+            if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
+            if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
+                stg.await(S, seq, lane);                 // no copy may be in flight when the block retires
+                ++seq;
+                return -3;
+            }
+        }
+        const float4 *blk = stg.await(S, seq, lane);
+        if (i + 1 < nlist) {
+            __syncwarp();                                // every lane is done with the stage the next copy overwrites
+            stg.issue(T, S, S.w.list[i + 1], seq + 1, lane);
+        }
+        ++seq;
+        const unsigned pm = prefilter_blk(blk, q, v.bound);
+        if (pm) {
+            S.q.qmask[cnt * 32 + lane] = pm;
+            S.q.qslot[cnt * 32 + lane] = (unsigned char)i;
+            ++cnt;
+            pend += __popc(pm);
+        }
+        const int rounds = __reduce_max_sync(kFull, pend);
+        if (rounds >= drain_at || (i + 1 == nlist && rounds > 0)) {
+            drain_queue<K>(T, S, tile, lane, q, v, first, cnt, rounds);
+            first = cnt; pend = 0;
+            if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
+        }
+    }
+    return nlist;
 }
 
 template <int K>
@@ -1025,11 +1194,9 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
     mean_d[row] = (float)(s / (double)mean_k);
 }
 
-template <int K, int MODE>
+template <int K, int MODE, bool TMA>
 __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
-    constexpr int CAP = MODE != MODE_SOR ? LogCap<K>::value : 1;
-    constexpr bool LOG = MODE != MODE_SOR;
-    __shared__ WarpScratch3<CAP> s_ws[2];
+    __shared__ SelScratch s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = P.tile_begin + blockIdx.x * 2 + warp;
     if (slot >= P.tile_end) return;
@@ -1041,7 +1208,15 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
         tile = (c * P.shard_world + P.shard_rank) * P.shard_chunk + (slot - c * P.shard_chunk);
         if (tile >= T.count[0]) return;
     }
-    WarpScratch3<CAP> &S = s_ws[warp];
+    SelScratch &S = s_ws[warp];
+    if (TMA) {
+        if (lane == 0) {
+#pragma unroll
+            for (int s = 0; s < kSelStages; ++s) mbar_init(&S.bar[s], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
     const size_t pos = (size_t)tile * kLeaf + lane;
     const float4 q = T.pts[pos];
     const bool active = pos < (size_t)T.n;
@@ -1050,17 +1225,13 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
     const int k = P.k;
     const float4 tlo = T.lo[0][tile], thi = T.hi[0][tile];
 
-    const float cx = 0.5f * (tlo.x + thi.x), cy = 0.5f * (tlo.y + thi.y), cz = 0.5f * (tlo.z + thi.z);
-    float4 qr;                                  // (-2Q, |Q|^2), Q = q - centre
-    {
-        const float x = q.x - cx, y = q.y - cy, z = q.z - cz;
-        qr = make_float4(-2.f * x, -2.f * y, -2.f * z, fmaf(x, x, fmaf(y, y, z * z)));
-    }
-    ValLog<K, LOG> v;
-    v.init(k, P.rb, active, S.log + lane);
-    int nlist = 0;
+    ValList<K> v;
+    v.init(k, P.rb, active);
+    Stager<TMA> stg;
+    unsigned seq = 0;
+    int cnt = 0, nlist = 0;
     bool lone = false;
-    const int scanned = scan_pass1<K, LOG, CAP>(T, tile, tlo, thi, q, qr, cx, cy, cz, v, S, nlist, lone);
+    const int scanned = sel_pass1<K, TMA>(T, P, tile, tlo, thi, q, v, S, stg, seq, cnt, nlist, lone, P.stat_scanned);
     if (scanned >= 0) {                             // isolated lanes of a dense tile -> point kernel
         const unsigned lm = __ballot_sync(kFull, lone);
         if (lm) {
@@ -1068,9 +1239,9 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
             if (lane == 0) base = atomicAdd(P.defer_count, __popc(lm));
             base = __shfl_sync(kFull, base, 0);
             if (lone) {
-                const int slot = base + __popc(lm & ((1u << lane) - 1u));
-                P.defer_list[slot] = qidx;
-                P.defer_row[slot] = (long long)row;
+                const int ds = base + __popc(lm & ((1u << lane) - 1u));
+                P.defer_list[ds] = qidx;
+                P.defer_row[ds] = (long long)row;
             }
         }
     }
@@ -1083,21 +1254,18 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
         }
         base = __shfl_sync(kFull, base, 0);
         if (active) {
-            const int slot = base + __popc(am & ((1u << lane) - 1u));
-            P.defer_list[slot] = qidx;
-            P.defer_row[slot] = (long long)row;
+            const int ds = base + __popc(am & ((1u << lane) - 1u));
+            P.defer_list[ds] = qidx;
+            P.defer_row[ds] = (long long)row;
         }
         return;
     }
-    if (P.stat_scanned && lane == 0) {
-        atomicAdd(P.stat_scanned, (unsigned long long)scanned);
-        atomicAdd(P.stat_scanned + 2, (unsigned long long)nlist);
-    }
+    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
     if (MODE == MODE_SOR) {
         if (active && !lone) sor_finish<K>(v.key, k, P.mean_k, P.mean_d, row);
         return;
     }
-    // pass 2: the neighbour set {d2 <= t} lies in the home leaves and the log
+    // ---- pass 2: the neighbour set {d2 <= t} lies in the home leaves and the queue ---------------------------------
     float t = (active && !lone) ? fminf(fminf(P.rb, v.key[K - 1]), FLT_MAX) : -1.f;   // finite: +inf pads never qualify
     // MODE_KNN (ordered lists): the value list is already the sorted d2 row; a neighbour's slot is the number of list
     // values below its d2, which is unique as long as no two list values are equal.  Equal values need the
@@ -1109,25 +1277,44 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
             if (i > K - k) dup = dup || (v.key[i] == v.key[i - 1] && v.key[i] != INFINITY);
         if (dup) t = -1.f;
     }
+    // the three home leaves join the queue with their prefilter masks against t (3 entries are reserved for them)
+    int tot = 0;
+    {
+        const int maxc = __reduce_max_sync(kFull, cnt);
+        for (int e = 0; e < maxc; ++e)
+            if (e < cnt) tot += __popc(S.q.qmask[e * 32 + lane]);
+    }
+#pragma unroll 1
+    for (int h = 0; h < 3; ++h) {
+        const int leaf = tile + (h == 0 ? 0 : (h == 1 ? -1 : 1));
+        if (leaf < 0 || leaf >= T.count[0]) continue;
+        __syncwarp();
+        stg.issue(T, S, leaf, seq, lane);
+        const float4 *blk = stg.await(S, seq, lane);
+        ++seq;
+        const unsigned pm = prefilter_blk(blk, q, t);
+        if (pm) {
+            S.q.qmask[cnt * 32 + lane] = pm;
+            S.q.qslot[cnt * 32 + lane] = (unsigned char)(kSlotHome + h);
+            ++cnt;
+            tot += __popc(pm);
+        }
+    }
     int count = 0;
     float m[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) m[i] = 0.f;
-    for (int i = 0; i < 3; ++i) {
-        const int leaf = tile + (i == 0 ? 0 : (i == 1 ? -1 : 1));
-        if (leaf < 0 || leaf >= T.count[0]) continue;
-        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
-        const float x = p.x - cx, y = p.y - cy, z = p.z - cz;
-        __syncwarp();
-        S.w.ws.leaf[lane] = p;
-        S.rel[lane] = make_float4(x, y, z, fmaf(x, x, fmaf(y, y, z * z)));
-        __syncwarp();
-        unsigned msk = prefilter(qr, S.rel, t);
-        while (__any_sync(kFull, msk != 0)) {
-            if (msk != 0) {
-                const int j = __ffs(msk) - 1;
-                msk &= msk - 1;
-                const float4 c = S.w.ws.leaf[j];
+    {
+        const int rounds = __reduce_max_sync(kFull, tot);
+        if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)rounds);
+        QueueWalk w;
+        w.start(S, 0, cnt, lane);
+        float4 fc = q; int fe; unsigned fbit = 0;
+        w.next(T, S, tile, lane, fc, fe, fbit);
+        for (int r = 0; r < rounds; ++r) {
+            const float4 c = fc; const int e = fe;
+            w.next(T, S, tile, lane, fc, fe, fbit);
+            if (e >= 0) {
                 const float dd = d2_point(q, c);
                 if (dd <= t) {
                     ++count;
@@ -1137,41 +1324,19 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
                         for (int i2 = 0; i2 < K; ++i2) below += v.key[i2] < dd ? 1 : 0;
                         if (P.idx) P.idx[row * k + (below - (K - k))] = __float_as_int(c.w);
                     } else {
-                        const float dx = c.x - q.x, dy = c.y - q.y, dz = c.z - q.z;
-                        m[0] += dx; m[1] += dy; m[2] += dz;
-                        m[3] += dx * dx; m[4] += dx * dy; m[5] += dx * dz; m[6] += dy * dy; m[7] += dy * dz; m[8] += dz * dz;
+                        const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
+                        m[0] += x; m[1] += y; m[2] += z;
+                        m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
                     }
-                }
-            }
-        }
-    }
-    const int maxc = __reduce_max_sync(kFull, v.cnt);
-    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)maxc);
-    for (int e = 0; e < maxc; ++e) {
-        if (e < v.cnt) {
-            const unsigned id = v.log[e * 32];
-            const float4 c = T.pts[(size_t)S.w.list[id >> 5] * kLeaf + (id & 31u)];
-            const float dd = d2_point(q, c);
-            if (dd <= t) {
-                ++count;
-                if (MODE == MODE_KNN) {
-                    int below = 0;
-#pragma unroll
-                    for (int i2 = 0; i2 < K; ++i2) below += v.key[i2] < dd ? 1 : 0;
-                    if (P.idx) P.idx[row * k + (below - (K - k))] = __float_as_int(c.w);
-                } else {
-                    const float x = c.x - q.x, y = c.y - q.y, z = c.z - q.z;
-                    m[0] += x; m[1] += y; m[2] += z;
-                    m[3] += x * x; m[4] += x * y; m[5] += x * z; m[6] += y * y; m[7] += y * z; m[8] += z * z;
                 }
             }
         }
     }
     if (!active || lone) return;
     if (count > k || dup) {                                // ties at the k-th distance overflow the list: exact kernel decides
-        const int slot = atomicAdd(P.defer_count, 1);
-        P.defer_list[slot] = qidx;
-        P.defer_row[slot] = (long long)row;
+        const int ds = atomicAdd(P.defer_count, 1);
+        P.defer_list[ds] = qidx;
+        P.defer_row[ds] = (long long)row;
         return;
     }
     if (MODE == MODE_KNN) {
@@ -1393,12 +1558,17 @@ static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cuda
     k_tile_topk<K><<<blocks, 128, 0, st>>>(T, P);
 }
 
-template <int K>
-static void launch_sel(const TreeView &T, const TileParams &P, int blocks, int sms, cudaStream_t st) {
+template <int K, bool TMA>
+static void launch_sel2(const TreeView &T, const TileParams &P, cudaStream_t st) {
     const int ntiles = P.tile_end - P.tile_begin;
-    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else k_tile_sel<K, MODE_SOR><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else k_tile_sel<K, MODE_SOR, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+}
+template <int K>
+static void launch_sel(const TreeView &T, const TileParams &P, int tma, cudaStream_t st) {
+    if (tma) launch_sel2<K, true>(T, P, st);
+    else launch_sel2<K, false>(T, P, st);
 }
 
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
@@ -1418,6 +1588,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.tile_order = a.tile_order;
+    P.drain_at = ctx->sel_drain_at > 0 ? ctx->sel_drain_at : 1 << 30;
     P.shard_world = a.shard_world; P.shard_rank = a.shard_rank; P.shard_chunk = a.shard_chunk;
     if (a.shard_world > 1) {
         if (a.mode == MODE_KNN && ctx->knn_use_topk) return set_error(ctx, CCG_ERR_INVALID, "interleaved shards need the selection kernel");
@@ -1448,33 +1619,67 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
         else if (k <= 48) launch_topk<48>(T, P, blocks, st);
         else launch_topk<64>(T, P, blocks, st);
     } else {
-        // two-pass selection; queries whose k-th distance is tied beyond the list go to the exact point kernel
-        const size_t rows = (size_t)ntiles * kLeaf;
+        const bool overlap = ctx->point_overlap && !ctx->collect_stats;
+        // two-pass selection; queries whose k-th distance is tied beyond the list go to the exact point kernel.
+        // The point kernel is latency-bound (r01: 7.6 % of GPU time for 0.3 % of the queries, serialised behind every tile
+        // launch), so it runs on a side stream next to the NEXT tile launch; the defer list is double-buffered for that and
+        // join_side() (every entry point calls it before it touches the outputs) brings the streams together again.
+        // A long launch is cut into sel_chunks sub-launches so that chunk c's point kernel overlaps chunk c+1's tiles.
+        const int tb0 = P.tile_begin, te0 = P.tile_end;
+        int nsub = (overlap && !a.async_side && ntiles >= 65536) ? ctx->sel_chunks : 1;
+        if (nsub < 1) nsub = 1;
+        const int per = ((ntiles + nsub - 1) / nsub + 1) & ~1;        // even: two tiles per block
+        for (int tb = tb0; tb < te0; tb += per) {
+        P.tile_begin = tb; P.tile_end = tb + per < te0 ? tb + per : te0;
+        const size_t rows = (size_t)(P.tile_end - P.tile_begin) * kLeaf;
         const size_t off_list = 256, off_rows = off_list + ((rows * 4 + 255) & ~(size_t)255);
-        const size_t off_slow = off_rows + ((rows * 8 + 255) & ~(size_t)255);
-        CCG_CUDA(ctx, ctx->defer.reserve(off_slow + (size_t)ntiles * 4));
-        CCG_CUDA(ctx, cudaMemsetAsync(ctx->defer.p, 0, 8, st));
-        P.defer_count = ctx->defer.as<int>();
-        P.slow_count = ctx->defer.as<int>() + 1;
-        P.defer_list = (int32_t *)((char *)ctx->defer.p + off_list);
-        P.defer_row = (long long *)((char *)ctx->defer.p + off_rows);
-        P.slow_tiles = (int32_t *)((char *)ctx->defer.p + off_slow);
-        if (k <= 8) launch_sel<8>(T, P, blocks, ctx->sm_count, st);
-        else if (k <= 16) launch_sel<16>(T, P, blocks, ctx->sm_count, st);
-        else if (k <= 20) launch_sel<20>(T, P, blocks, ctx->sm_count, st);
-        else if (k <= 24) launch_sel<24>(T, P, blocks, ctx->sm_count, st);
-        else if (k <= 32) launch_sel<32>(T, P, blocks, ctx->sm_count, st);
-        else if (k <= 48) launch_sel<48>(T, P, blocks, ctx->sm_count, st);
-        else launch_sel<64>(T, P, blocks, ctx->sm_count, st);
+        const size_t off_end = off_rows + ((rows * 8 + 255) & ~(size_t)255);
+        const int sel = overlap ? (ctx->defer_sel ^= 1) : 0;
+        DevBuf &db = sel ? ctx->defer_b : ctx->defer;
+        if (overlap) {
+            for (int i = 0; i < 2; ++i)
+                if (!ctx->ev_side[i]) CCG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_side[i], cudaEventDisableTiming));
+            if (!ctx->ev_tile) CCG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_tile, cudaEventDisableTiming));
+            if (!ctx->side_stream) CCG_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
+            CCG_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_side[sel], 0));      // the launch before last still reads this buffer
+        }
+        CCG_CUDA(ctx, db.reserve(off_end));
+        CCG_CUDA(ctx, cudaMemsetAsync(db.p, 0, 8, st));
+        P.defer_count = db.as<int>();
+        P.slow_count = db.as<int>() + 1;
+        P.defer_list = (int32_t *)((char *)db.p + off_list);
+        P.defer_row = (long long *)((char *)db.p + off_rows);
+        P.slow_tiles = nullptr;
+        if (k <= 8) launch_sel<8>(T, P, ctx->sel_stage, st);
+        else if (k <= 16) launch_sel<16>(T, P, ctx->sel_stage, st);
+        else if (k <= 20) launch_sel<20>(T, P, ctx->sel_stage, st);
+        else if (k <= 24) launch_sel<24>(T, P, ctx->sel_stage, st);
+        else if (k <= 32) launch_sel<32>(T, P, ctx->sel_stage, st);
+        else if (k <= 48) launch_sel<48>(T, P, ctx->sel_stage, st);
+        else launch_sel<64>(T, P, ctx->sel_stage, st);
         {
             PointParams Q{};
             Q.queries = P.defer_list; Q.nq = 0; Q.nq_dev = P.defer_count; Q.rows = P.defer_row;
             Q.mode = a.mode; Q.k = k; Q.rb = a.rb; Q.list_rows = 0;
             Q.idx = a.idx; Q.d2 = a.d2;
             Q.count = a.count; Q.pca = P.pca; Q.mean_k = a.mean_k; Q.mean_d = a.mean_d;
-            k_point_query<<<ctx->sm_count * 8, 128, 0, st>>>(T, Q);
-            ctx->stats.launches++;
+            cudaStream_t ps = st;
+            if (overlap) {
+                CCG_CUDA(ctx, cudaEventRecord(ctx->ev_tile, st));
+                CCG_CUDA(ctx, cudaStreamWaitEvent(ctx->side_stream, ctx->ev_tile, 0));
+                ps = ctx->side_stream;
+            }
+            k_point_query<<<ctx->sm_count * 8, 128, 0, ps>>>(T, Q);
+            if (overlap) {
+                CCG_CUDA(ctx, cudaEventRecord(ctx->ev_side[sel], ps));
+                ctx->side_pending = 1;
+                ctx->last_side = sel;
+            }
+            ctx->stats.launches += 2;
         }
+        }   // sub-launches
+        ctx->stats.launches--;
+        if (overlap && !a.async_side) CCG_TRY(join_side(ctx));
     }
     ctx->stats.launches++;
     CCG_CUDA(ctx, cudaGetLastError());
@@ -1490,6 +1695,15 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
             fprintf(stderr, "[ccg] tiles=%d leaves scanned=%llu (pass2 %llu) listed=%llu slow tiles=%llu (slots %llu, ties %llu, unbounded %llu, wide %llu) deferred=%d\n", ntiles,
                     s4[0], s4[1], s4[2], s4[3], s4[6], s4[7], s4[8], s4[9], nd);
     }
+    return CCG_OK;
+}
+
+// the main stream waits for the point kernels still running on the side stream
+int join_side(ccg_ctx *ctx) {
+    if (!ctx->side_pending) return CCG_OK;
+    for (int i = 0; i < 2; ++i)
+        if (ctx->ev_side[i]) CCG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_side[i], 0));
+    ctx->side_pending = 0;
     return CCG_OK;
 }
 

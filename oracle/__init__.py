@@ -53,6 +53,7 @@ def lib():
         L.cco_eig3_f64_export.argtypes = [vp, vp, vp]
         L.cco_eig3_f32_export.argtypes = [vp, vp]
         L.cco_max_threads.restype = i32
+        L.cco_knn_pca_features.argtypes = [vp, i32, i32, i32, i32, i32, vp, vp, vp, i32]
         _lib = L
     return _lib
 
@@ -125,6 +126,17 @@ class Tree:
         out = np.empty(self.n, np.uint8)
         lib().cco_radius_outliers(self.h, float(r), min_neighbours, 1 if prefilter else 0, _p(out), threads)
         return out
+
+
+def knn_pca_features(tree, k, cov_norm=1, formula_set=0, threads=0, normals=True):
+    """The bench metric's CPU baseline: per point kNN(k) -> fp32 PCA -> 7 features, fused (the reference's getPCA loop shape,
+    cv.h:96-113 + markov.cpp:449-475), OpenMP over queries (threads=1: serial like the reference).  -> eig3, normal4, feat7"""
+    n = tree.n
+    eig = np.empty((n, 3), np.float32)
+    nrm = np.empty((n, 4), np.float32) if normals else None
+    feat = np.empty((n, 7), np.float32)
+    lib().cco_knn_pca_features(tree.h, k, cov_norm, formula_set, 0, n, _p(eig), _p(nrm) if normals else None, _p(feat), threads)
+    return eig, nrm, feat
 
 
 def knn_brute(points, k, q_begin=0, q_end=None):

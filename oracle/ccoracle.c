@@ -63,12 +63,14 @@ typedef struct {
     float bb_lo[3], bb_hi[3];
 } cco_tree;
 
+/* nodes are pre-allocated (median splits down to <= CCO_LEAF points leave >= 8 points per leaf: fewer than n/4 + 2
+ * nodes), so that sub-trees can be built by concurrent OpenMP tasks; only the numbering of the nodes depends on the
+ * schedule, the tree and every search result do not */
 static int cco_new_node(cco_tree *t) {
-    if (t->n_nodes == t->cap_nodes) {
-        t->cap_nodes = t->cap_nodes ? t->cap_nodes * 2 : 1024;
-        t->nodes = (cco_node *)realloc(t->nodes, sizeof(cco_node) * (size_t)t->cap_nodes);
-    }
-    return t->n_nodes++;
+    int id;
+    #pragma omp atomic capture
+    id = t->n_nodes++;
+    return id;
 }
 
 /* quickselect on perm[b..e) by coordinate dim, ties by index so the build is deterministic */
@@ -112,8 +114,16 @@ static int cco_build_rec(cco_tree *t, int b, int e) {
     float lo_max = -FLT_MAX, hi_min = FLT_MAX;
     for (int i = b; i < m; i++) { float v = t->xyz[3 * (size_t)t->perm[i] + dim]; if (v > lo_max) lo_max = v; }
     for (int i = m; i < e; i++) { float v = t->xyz[3 * (size_t)t->perm[i] + dim]; if (v < hi_min) hi_min = v; }
-    int l = cco_build_rec(t, b, m);
-    int r = cco_build_rec(t, m, e);
+    int l, r;
+    if (e - b > 32768) {
+        #pragma omp task shared(l) firstprivate(t, b, m)
+        l = cco_build_rec(t, b, m);
+        r = cco_build_rec(t, m, e);
+        #pragma omp taskwait
+    } else {
+        l = cco_build_rec(t, b, m);
+        r = cco_build_rec(t, m, e);
+    }
     cco_node *nd = &t->nodes[id];
     nd->left = l; nd->right = r; nd->dim = dim; nd->lo_max = lo_max; nd->hi_min = hi_min;
     nd->begin = b; nd->end = e;
@@ -136,7 +146,13 @@ void *cco_tree_build(const void *xyz, int n, int stride_bytes) {
         }
         t->perm[i] = i;
     }
-    if (n > 0) cco_build_rec(t, 0, n);
+    t->cap_nodes = n / 4 + 64;
+    t->nodes = (cco_node *)malloc(sizeof(cco_node) * (size_t)t->cap_nodes);
+    if (n > 0) {
+        #pragma omp parallel
+        #pragma omp single
+        cco_build_rec(t, 0, n);
+    }
     return t;
 }
 void cco_tree_free(void *tv) {
@@ -767,6 +783,60 @@ int cco_grid_normals(const void *xyz, int n, int stride_bytes, const int32_t *cl
     }
     free(g2c); free(missing);
     return still;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* CPU baseline of the bench metric: the reference's per-point loop shape (cv.h:96-113: search,  */
+/* then pcl::PCA of the neighbourhood, then the feature formulas of markov.cpp:449-475), fused:  */
+/* kNN(k) -> fp32 centroid/covariance -> eigenvalues (fp32 QL) + normal (eigenvector of the      */
+/* smallest eigenvalue via the fp64 Jacobi, as SelfAdjointEigenSolver returns vectors too) ->    */
+/* 7 features.  No neighbour table is materialised.  OpenMP over queries (nthreads <= 0: all;    */
+/* 1 = what the reference does: its loop is serial).  Outputs may be NULL.                       */
+/* ------------------------------------------------------------------------------------------ */
+void cco_knn_pca_features(const void *tv, int k, int cov_norm, int formula_set, int q_begin, int q_end, float *eig3, float *normal4,
+                          float *feat7, int nthreads) {
+    const cco_tree *t = (const cco_tree *)tv;
+    int nt = cco_nt(nthreads);
+    #pragma omp parallel num_threads(nt)
+    {
+        float *d2 = (float *)malloc(sizeof(float) * (size_t)(k + 1));
+        int *ix = (int *)malloc(sizeof(int) * (size_t)(k + 1));
+        #pragma omp for schedule(dynamic, 1024)
+        for (int qi = q_begin; qi < q_end; qi++) {
+            cco_rs rs; rs.k = k; rs.cnt = 0; rs.d2 = d2; rs.idx = ix; rs.use_radius = 0; rs.total_in_radius = 0;
+            rs.bound = 0; rs.bound_d = 0;
+            const float *q = &t->xyz[3 * (size_t)qi];
+            float off[3]; cco_root_off(t, q, off);
+            if (t->n > 0 && k > 0) cco_search(t, 0, q, off, &rs, 0);
+            const int n = rs.cnt;
+            float w[3] = {0.f, 0.f, 1.f}, nrm[4] = {NAN, NAN, NAN, NAN};
+            if (n >= 3) {
+                float mx = 0.f, my = 0.f, mz = 0.f;
+                for (int j = 0; j < n; j++) { const float *p = &t->xyz[3 * (size_t)ix[j]]; mx += p[0]; my += p[1]; mz += p[2]; }
+                mx /= (float)n; my /= (float)n; mz /= (float)n;
+                float s[6] = {0, 0, 0, 0, 0, 0};
+                for (int j = 0; j < n; j++) {
+                    const float *p = &t->xyz[3 * (size_t)ix[j]];
+                    float x = p[0] - mx, y = p[1] - my, z = p[2] - mz;
+                    s[0] += x * x; s[1] += x * y; s[2] += x * z; s[3] += y * y; s[4] += y * z; s[5] += z * z;
+                }
+                float sc = cov_norm == 1 ? 1.f / (float)(n - 1) : cov_norm == 2 ? 1.f / (float)n : 1.f;
+                for (int c = 0; c < 6; c++) s[c] *= sc;
+                cco_eig3_f32_ql(s, w);
+                if (normal4) {
+                    double S[6], wd[3], v[9];
+                    for (int c = 0; c < 6; c++) S[c] = s[c];
+                    cco_eig3_f64(S, wd, v);
+                    double tr = wd[0] + wd[1] + wd[2];
+                    nrm[0] = (float)v[6]; nrm[1] = (float)v[7]; nrm[2] = (float)v[8]; nrm[3] = tr > 0 ? (float)fabs(wd[2] / tr) : 0.f;
+                }
+            }
+            if (eig3) { eig3[3 * (size_t)qi] = w[0]; eig3[3 * (size_t)qi + 1] = w[1]; eig3[3 * (size_t)qi + 2] = w[2]; }
+            if (normal4) for (int c = 0; c < 4; c++) normal4[4 * (size_t)qi + c] = nrm[c];
+            if (feat7) cco_features(w, 1, formula_set, &feat7[7 * (size_t)qi]);
+        }
+        free(d2); free(ix);
+    }
 }
 
 int cco_max_threads(void) {
