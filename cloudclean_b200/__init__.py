@@ -143,6 +143,18 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
+def _rowptr(a):
+    """first byte of a [n, S] float32 array whose rows may be strided (a column-sliced view of a wider struct array): the C ABI
+    takes the row stride separately, only the elements of a row must be adjacent"""
+    if a is None:
+        return None
+    if _is_torch(a):
+        assert a.dim() == 1 or a.stride(-1) == 1
+        return C.c_void_p(a.data_ptr())
+    assert a.ndim == 1 or a.strides[-1] == a.itemsize
+    return a.ctypes.data_as(C.c_void_p)
+
+
 class Context:
     """One GPU, one cloud.  Thin wrapper over ccg_ctx; every method is one C-ABI call."""
 
@@ -187,6 +199,10 @@ class Context:
         """allocate an output next to the inputs: torch CUDA tensor if the cloud came from one, else numpy"""
         if like_device:
             import torch
+            if getattr(self, "_own_stream", True):
+                # the ctx stream is not ordered after torch's: a block the caching allocator hands out may still be read or
+                # written by work queued on torch's current stream
+                torch.cuda.current_stream(self.device).synchronize()
             tdt = {np.float32: torch.float32, np.int32: torch.int32, np.uint8: torch.uint8, np.float64: torch.float64}[dtype]
             return torch.empty(shape, dtype=tdt, device=f"cuda:{self.device}")
         return np.empty(shape, dtype)
@@ -293,7 +309,7 @@ class Context:
         out = self._out(dev, (self.n,), np.float32)
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
         self._settle(normals)
-        self._check(self.L.ccg_normal_stdev(self.h, float(r), max_nn, _ptr(normals), stride, _ptr(out)))
+        self._check(self.L.ccg_normal_stdev(self.h, float(r), max_nn, _rowptr(normals), stride, _ptr(out)))
         return out
 
     def stdev_dist(self, r, max_nn, use_depth=False, centre=None, device_out=None):
@@ -323,7 +339,7 @@ class Context:
         out = self._out(dev, (self.n, 4), np.float32)
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
         self._settle(normals)
-        self._check(self.L.ccg_don(self.h, _ptr(normals), stride, float(r1), float(r2), _ptr(out)))
+        self._check(self.L.ccg_don(self.h, _rowptr(normals), stride, float(r1), float(r2), _ptr(out)))
         return out
 
     def principal_curvatures(self, normals, r, device_out=None):
@@ -333,7 +349,7 @@ class Context:
         out = self._out(dev, (self.n, 5), np.float32)
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
         self._settle(normals)
-        self._check(self.L.ccg_principal_curvatures(self.h, float(r), _ptr(normals), stride, _ptr(out)))
+        self._check(self.L.ccg_principal_curvatures(self.h, float(r), _rowptr(normals), stride, _ptr(out)))
         return out
 
     def fpfh(self, normals, r, want_spfh=False, device_out=None):
@@ -344,7 +360,7 @@ class Context:
         sp = self._out(dev, (self.n, 33), np.float32) if want_spfh else None
         stride = normals.stride(0) * 4 if _is_torch(normals) else normals.strides[0]
         self._settle(normals)
-        self._check(self.L.ccg_fpfh(self.h, float(r), _ptr(normals), stride, _ptr(out), _ptr(sp)))
+        self._check(self.L.ccg_fpfh(self.h, float(r), _rowptr(normals), stride, _ptr(out), _ptr(sp)))
         return (out, sp) if want_spfh else out
 
     def knn_graph(self, k, inverse_sigma, device_out=None):
@@ -364,7 +380,7 @@ class Context:
         b2s = self._out(dev, (self.n,), np.int32)
         nv = C.c_int64(0)
         self._settle(points)
-        self._check(self.L.ccg_voxel_downsample(self.h, _ptr(points), stride, nf, float(resolution), 1 if as_written else 0,
+        self._check(self.L.ccg_voxel_downsample(self.h, _rowptr(points), stride, nf, float(resolution), 1 if as_written else 0,
                                                 _ptr(b2s), C.byref(nv)))
         out = self._out(dev, (nv.value, nf), np.float32)
         if nv.value:
@@ -452,6 +468,7 @@ class Context:
     def eigen_scalar(self, eig3, which):
         n = eig3.shape[0]
         out = self._out(_is_torch(eig3) and eig3.is_cuda, (n,), np.float32)
+        self._settle(eig3)
         self._check(self.L.ccg_eigen_scalar(self.h, _ptr(eig3), n, which, _ptr(out)))
         return out
 
@@ -475,6 +492,7 @@ class Context:
         if not _is_torch(cloud_to_grid):
             cloud_to_grid = np.ascontiguousarray(cloud_to_grid, np.int32)
         out = self._out(dev, (self.n, 4), np.float32)
+        self._settle(cloud_to_grid)
         missing = C.c_int32(0)
         self._check(self.L.ccg_grid_normals(self.h, _ptr(cloud_to_grid), scan_w, scan_h, 1 if fallback else 0, _ptr(out),
                                             C.byref(missing)))

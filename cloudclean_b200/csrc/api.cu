@@ -1,6 +1,6 @@
 // api.cu — the extern "C" surface of libccgpu.so (include/ccgpu.h): argument checking, host/device pointer
 // detection, output staging, and the few O(n) glue kernels (SOR mask, voxel prefilter).
-#include "common.cuh"
+#include "tile.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <stdarg.h>
 #include <stdlib.h>
@@ -174,12 +174,21 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
     a.tile_order = dv.Current();
     a.async_side = 1;
     int launches = ctx->stats.launches;
+    // An early exit must not leave copies of earlier chunks in flight: the caller may free its (pinned) output buffers as
+    // soon as the call returns, and the next call may overwrite ctx->out[] while the copy stream still reads it.
+    auto bail = [&](int rc) {
+        cudaStreamSynchronize(cs);
+        cudaStreamSynchronize(st);
+        if (ctx->side_stream) cudaStreamSynchronize(ctx->side_stream);
+        ctx->side_pending = 0;
+        return rc;
+    };
     for (int c = 0; c < nch; ++c) {
-        if (ctx->cancel && *ctx->cancel) return set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller");
+        if (ctx->cancel && *ctx->cancel) return bail(set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller"));
         a.begin = (size_t)slot[c] * kLeaf;
         a.end = (size_t)slot[c + 1] * kLeaf;
         ctx->stats.launches = 0;
-        CCG_TRY(launch_tile_query(ctx, a));
+        { const int rc = launch_tile_query(ctx, a); if (rc != CCG_OK) return bail(rc); }
         launches += ctx->stats.launches;
         CCG_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[c], st));
         CCG_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[c], 0));
@@ -233,13 +242,13 @@ __global__ void __launch_bounds__(256) k_normal_stdev(const int32_t *__restrict_
     const int m = count[i];
     float res = 0.f;
     if (cx == cx && m >= 3) {
-        const float cn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(cx, cx), __fmul_rn(cy, cy)), __fmul_rn(cz, cz)));
+        const float cn = __fsqrt_rn(eigen_dot3(cx, cy, cz, cx, cy, cz));
         float sum = 0.f, sumsq = 0.f;
         for (int j = 0; j < m; ++j) {
             const float *nb = reinterpret_cast<const float *>(normals + (size_t)idx[i * k + j] * stride);
             const float x = nb[0], y = nb[1], z = nb[2];
-            const float dot = __fadd_rn(__fadd_rn(__fmul_rn(x, cx), __fmul_rn(y, cy)), __fmul_rn(z, cz));
-            const float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+            const float dot = eigen_dot3(x, y, z, cx, cy, cz);
+            const float nn = __fsqrt_rn(eigen_dot3(x, y, z, x, y, z));
             float cosine = __fmul_rn(__fdiv_rn(dot, nn), cn);
             cosine = cosine < 0.f ? 0.f : (cosine > 1.f ? 1.f : cosine);
             const float angle = (float)((double)acosf(cosine) / 3.14159265358979323846);
@@ -267,7 +276,7 @@ __global__ void __launch_bounds__(256) k_stdev_dist(const float4 *__restrict__ o
     for (int j = 0; j < m; ++j) {
         const float4 p = orig[idx[i * k + j]];
         const float dx = __fsub_rn(p.x, rx), dy = __fsub_rn(p.y, ry), dz = __fsub_rn(p.z, rz);
-        const float dist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        const float dist = __fsqrt_rn(eigen_dot3(dx, dy, dz, dx, dy, dz));
         sum = __fadd_rn(sum, dist);
         sumsq = __fadd_rn(sumsq, __fmul_rn(dist, dist));
     }
@@ -391,7 +400,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
     ctx->vox_out.release();
     ctx->ptx_bytes.release(); ctx->ptx_starts.release(); ctx->ptx_points.release(); ctx->ptx_c2g.release();
-    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release(); ctx->defer_b.release();
+    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release(); ctx->defer_b.release(); ctx->rule_T.release(); ctx->rule_I.release();
     for (int i = 0; i < 2; ++i) if (ctx->ev_side[i]) cudaEventDestroy(ctx->ev_side[i]);
     if (ctx->ev_tile) cudaEventDestroy(ctx->ev_tile);
     if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
@@ -512,6 +521,16 @@ int ccg_normal_stdev(ccg_ctx *ctx, double r, int max_nn, const void *normals, si
     OutBuf oo;
     CCG_TRY(oo.open(ctx, 0, out, n * 4));
     CCG_TRY(query_begin(ctx));
+    if (max_nn == 0 || max_nn > CCG_MAX_K) {                  // no list: streaming epilogue in traversal order (radsel.cu)
+        if (max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "max_nn must be >= 0");
+        const float rb = radius_bound(r, 1);
+        const float *Tp; const int32_t *Ip;
+        CCG_TRY(launch_radius_rule(ctx, rb, max_nn, &Tp, &Ip));
+        CCG_TRY(launch_rule_normal_stdev(ctx, rb, Tp, Ip, nd, stride_bytes, oo.dev<float>()));
+        CCG_TRY(query_end(ctx));
+        CCG_TRY(oo.close());
+        return finish_call(ctx);
+    }
     int32_t *idx, *cnt;
     CCG_TRY(radius_lists_internal(ctx, r, max_nn, 1, &idx, &cnt));
     k_normal_stdev<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(idx, cnt, n, max_nn, (const char *)nd, stride_bytes, oo.dev<float>());
@@ -530,6 +549,17 @@ int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const floa
     OutBuf oo;
     CCG_TRY(oo.open(ctx, 0, out, n * 4));
     CCG_TRY(query_begin(ctx));
+    if (max_nn == 0 || max_nn > CCG_MAX_K) {
+        if (max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "max_nn must be >= 0");
+        const float rb = radius_bound(r, 0);
+        const float zero[3] = {0.f, 0.f, 0.f};
+        const float *Tp; const int32_t *Ip;
+        CCG_TRY(launch_radius_rule(ctx, rb, max_nn, &Tp, &Ip));
+        CCG_TRY(launch_rule_stdev_dist(ctx, rb, Tp, Ip, use_depth ? 1 : 0, centre3 ? centre3 : zero, oo.dev<float>()));
+        CCG_TRY(query_end(ctx));
+        CCG_TRY(oo.close());
+        return finish_call(ctx);
+    }
     int32_t *idx, *cnt;
     CCG_TRY(radius_lists_internal(ctx, r, max_nn, 0, &idx, &cnt));
     const float3 c = centre3 ? make_float3(centre3[0], centre3[1], centre3[2]) : make_float3(0.f, 0.f, 0.f);
@@ -560,6 +590,17 @@ int ccg_neighbour_hist(ccg_ctx *ctx, double r, int max_nn, int bins, int which, 
     OutBuf oo;
     CCG_TRY(oo.open(ctx, 0, hist, n * (size_t)bins * 4));
     CCG_TRY(query_begin(ctx));
+    if (max_nn == 0 || max_nn > CCG_MAX_K) {                  // counts per bin are order-independent: bit-exact without a list
+        if (max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "max_nn must be >= 0");
+        if (!(r >= 0.0)) return set_error(ctx, CCG_ERR_INVALID, "radius must be >= 0");
+        const float rb = radius_bound(r, 1);
+        const float *Tp; const int32_t *Ip;
+        CCG_TRY(launch_radius_rule(ctx, rb, max_nn, &Tp, &Ip));
+        CCG_TRY(launch_rule_hist(ctx, rb, Tp, Ip, bins, which, r, ad, attr_stride_bytes, oo.dev<float>()));
+        CCG_TRY(query_end(ctx));
+        CCG_TRY(oo.close());
+        return finish_call(ctx);
+    }
     int32_t *idx, *cnt;
     CCG_TRY(radius_lists_internal(ctx, r, max_nn, 1, &idx, &cnt));
     k_neighbour_hist<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->orig.as<float4>(), idx, cnt, n, max_nn, bins, which, r,
@@ -865,19 +906,25 @@ int ccg_pca_radius(ccg_ctx *ctx, double r, int max_nn, int cov_norm, int normali
     // FLANN caps only when 0 < max_nn < n; otherwise every point inside the radius is used
     bool uncapped = (max_nn == 0) || ((size_t)max_nn >= ctx->n);
     if (!uncapped && max_nn > CCG_MAX_K) {
-        // a cap this loose only matters for neighbourhoods denser than max_nn: count first, refuse if any is
+        // a cap beyond the register lists: per-query counting select of the max_nn-th distance, then one streaming pass over
+        // {d2 < T or (d2 == T and index <= I)} — FLANN's "max_nn nearest inside r" for any cap (radsel.cu)
+        if (cov_norm < 0 || cov_norm > 2) return set_error(ctx, CCG_ERR_INVALID, "cov_norm must be 0, 1 or 2");
+        const size_t n = ctx->n;
+        OutBuf oe, on, oc;
+        CCG_TRY(oe.open(ctx, 0, eig3, n * 12));
+        CCG_TRY(on.open(ctx, 1, normal4, n * 16));
+        CCG_TRY(oc.open(ctx, 2, count, n * 4));
+        CCG_TRY(query_begin(ctx));
+        const float *Tp; const int32_t *Ip;
+        CCG_TRY(launch_radius_rule(ctx, rb, max_nn, &Tp, &Ip));
         StreamArgs s{};
-        CCG_CUDA(ctx, ctx->tmp[0].reserve(ctx->n * 4 + 16));
-        s.mode = 0; s.rb = rb; s.count_cap = max_nn + 1; s.begin = 0; s.end = ctx->n; s.count = ctx->tmp[0].as<int32_t>();
-        CCG_TRY(launch_tile_stream(ctx, s));
-        CCG_CUDA(ctx, ctx->hpin[0].reserve(ctx->n * 4));
-        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, ctx->tmp[0].p, ctx->n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        const int32_t *c = ctx->hpin[0].as<int32_t>();
-        for (size_t i = 0; i < ctx->n; ++i)
-            if (c[i] > max_nn)
-                return set_error(ctx, CCG_ERR_UNSUPPORTED, "max_nn=%d > %d with neighbourhoods denser than the cap (point %zu)", max_nn, CCG_MAX_K, i);
-        uncapped = true;
+        s.cov_norm = cov_norm; s.min_pts = 3; s.normalise_hist = normalise_hist; s.has_vp = viewpoint3 ? 1 : 0;
+        if (viewpoint3) for (int i = 0; i < 3; ++i) s.vp[i] = viewpoint3[i];
+        s.eig3 = oe.dev<float>(); s.normal4 = on.dev<float>(); s.count = oc.dev<int32_t>();
+        CCG_TRY(launch_rule_pca(ctx, rb, Tp, Ip, s));
+        CCG_TRY(query_end(ctx));
+        CCG_TRY(oe.close()); CCG_TRY(on.close()); CCG_TRY(oc.close());
+        return finish_call(ctx);
     }
     return pca_common(ctx, max_nn, rb, cov_norm, normalise_hist, viewpoint3, 0, ctx->n, 0, eig3, normal4, count, uncapped);
 }

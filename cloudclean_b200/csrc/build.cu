@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) k_ingest(const char *__restrict__ src, si
     }
 }
 
-constexpr int kMortonBits = 16;
+constexpr int kMortonBits = 13;     // bits per axis of the curve key (39-bit keys: 5 radix passes; leaf quality equals 16 bits, tools/sim_tiles.cpp)
 
 __device__ __forceinline__ unsigned long long spread21(unsigned v) {
     unsigned long long x = v & 0x1fffffull;
@@ -113,13 +113,16 @@ __device__ __forceinline__ unsigned long long hilbert_key(unsigned x, unsigned y
 }
 
 // Space-filling-curve key of every point (kMortonBits per axis, cubic cells over the bounding box) + identity values.
-// 16 bits per axis = 48-bit keys = 6 radix passes instead of 8 (the sort is 60 % of the build): cells of extent/65536
-// (1.5 mm on a 100 m scan) are below the point spacing almost everywhere, and points sharing a cell simply keep their
-// original (scan) order — the order is only a permutation, search results do not depend on it.
+// 13 bits per axis = 39-bit keys = 5 radix passes (the sort is the largest stage of the build): cells of extent/8192
+// (1.2 cm on a 100 m scan); points sharing a cell simply keep their original (scan) order — the order is only a
+// permutation, search results do not depend on it, and the leaf quality measured by tools/sim_tiles.cpp (candidate leaves
+// scanned per tile) is the same at 12 and at 16 bits per axis.
 // The bounding box is read from the ingest scratch ON THE DEVICE (no host round trip in the middle of the build).
+// The point's index rides in the low `ib` bits of the same 64-bit word (key << ib | i), so the sort moves 8 bytes per
+// point and pass instead of a 12-byte (key, value) pair, and only the key bits [ib, ib + kb) are sorted.
 template <bool HILBERT>
 __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig, int n, const IngestScratch *__restrict__ sc,
-                                                unsigned long long *__restrict__ keys, unsigned *__restrict__ vals) {
+                                                int ib, int drop, unsigned long long *__restrict__ keys) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float lx = ord2f(sc->lo[0]), ly = ord2f(sc->lo[1]), lz = ord2f(sc->lo[2]);
@@ -130,8 +133,8 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
     unsigned qx = (unsigned)fminf(fmaxf((p.x - lx) * inv_cell, 0.f), qmax);
     unsigned qy = (unsigned)fminf(fmaxf((p.y - ly) * inv_cell, 0.f), qmax);
     unsigned qz = (unsigned)fminf(fmaxf((p.z - lz) * inv_cell, 0.f), qmax);
-    keys[i] = HILBERT ? hilbert_key(qx, qy, qz) : (spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2));
-    vals[i] = (unsigned)i;
+    const unsigned long long key = HILBERT ? hilbert_key(qx, qy, qz) : (spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2));
+    keys[i] = ((key >> drop) << ib) | (unsigned long long)(unsigned)i;
 }
 
 
@@ -143,7 +146,9 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
 // permutation); this one calls a point isolated when the distance to its nearer neighbour along the curve is more than
 // kIsoFactor times the median of that distance over its aligned 32-point window.  One warp per window.
 constexpr float kIsoFactor = 8.f;
-__global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ orig, const unsigned *__restrict__ order, int n,
+// Also unpacks the sorted words: order32[i] = index bits of packed[i].
+__global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ orig, const unsigned long long *__restrict__ packed,
+                                                    unsigned long long idx_mask, int n, unsigned *__restrict__ order32,
                                                     unsigned char *__restrict__ dense) {
     const int win = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -151,12 +156,16 @@ __global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ o
     if (win * 32 >= n) return;
     const bool valid = i < n;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (valid) p = orig[order[i]];
+    if (valid) {
+        const unsigned o = (unsigned)(packed[i] & idx_mask);
+        order32[i] = o;
+        p = orig[o];
+    }
     float px = __shfl_up_sync(kFull, p.x, 1), py = __shfl_up_sync(kFull, p.y, 1), pz = __shfl_up_sync(kFull, p.z, 1);
     float nx = __shfl_down_sync(kFull, p.x, 1), ny = __shfl_down_sync(kFull, p.y, 1), nz = __shfl_down_sync(kFull, p.z, 1);
     bool has_prev = valid && i > 0, has_next = valid && i + 1 < n;
-    if (lane == 0 && has_prev) { const float4 t = orig[order[i - 1]]; px = t.x; py = t.y; pz = t.z; }
-    if (lane == 31 && has_next) { const float4 t = orig[order[i + 1]]; nx = t.x; ny = t.y; nz = t.z; }
+    if (lane == 0 && has_prev) { const float4 t = orig[(unsigned)(packed[i - 1] & idx_mask)]; px = t.x; py = t.y; pz = t.z; }
+    if (lane == 31 && has_next) { const float4 t = orig[(unsigned)(packed[i + 1] & idx_mask)]; nx = t.x; ny = t.y; nz = t.z; }
     float gp = INFINITY, gn = INFINITY;
     if (has_prev) { const float x = p.x - px, y = p.y - py, z = p.z - pz; gp = x * x + y * y + z * z; }
     if (has_next) { const float x = p.x - nx, y = p.y - ny, z = p.z - nz; gn = x * x + y * y + z * z; }
@@ -324,41 +333,52 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
         else k_ingest<false><<<blocks, 256, 0, st>>>(src_dev, stride, (int)n, ctx->orig.as<float4>(), ctx->scratch.as<IngestScratch>());
         ctx->stats.launches_build++;
     }
-    // ---- Morton keys + radix sort ---------------------------------------------------------------------
+    // ---- curve keys + radix sort ------------------------------------------------------------------------
+    int ib = 1;
+    while (ib < 32 && ((n - 1) >> ib)) ++ib;                       // bits of the largest index
+    int kb = 3 * kMortonBits;
+    if (kb > 64 - ib) kb = (64 - ib) / 3 * 3;                      // > 2^25 points: the key gives up low bits to the index
+    const int drop = 3 * kMortonBits - kb;
     {
         int blocks = (int)((n + 255) / 256);
         if (ctx->curve_hilbert)
-            k_morton<true><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(),
-                                                   ctx->keys[0].as<unsigned long long>(), ctx->vals[0].as<unsigned>());
+            k_morton<true><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, drop,
+                                                   ctx->keys[0].as<unsigned long long>());
         else
-            k_morton<false><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(),
-                                                    ctx->keys[0].as<unsigned long long>(), ctx->vals[0].as<unsigned>());
+            k_morton<false><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, drop,
+                                                    ctx->keys[0].as<unsigned long long>());
         ctx->stats.launches_build++;
     }
+    int ksel = 0;
     {
         cub::DoubleBuffer<unsigned long long> dk(ctx->keys[0].as<unsigned long long>(), ctx->keys[1].as<unsigned long long>());
-        cub::DoubleBuffer<unsigned> dv(ctx->vals[0].as<unsigned>(), ctx->vals[1].as<unsigned>());
         size_t tmp_bytes = 0;
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, 3 * kMortonBits, st));
+        CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, dk, (int)n, ib, ib + kb, st));
         CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, (int)n, 0, 3 * kMortonBits, st));
-        ctx->order_sel = dv.selector;
-        ctx->stats.launches_build += 2 + (3 * kMortonBits + 7) / 8;   // onesweep: histogram + scan + one pass per 8-bit digit
+        CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(ctx->sort_tmp.p, tmp_bytes, dk, (int)n, ib, ib + kb, st));
+        ksel = dk.selector;
+        ctx->stats.launches_build += 2 + (kb + 7) / 8;            // onesweep: histogram + scan + one pass per 8-bit digit
     }
-    // ---- isolated points to the end of the order ----------------------------------------------------------
-    if (ctx->split_sparse && n > 64) {
-        const unsigned *ord = ctx->vals[ctx->order_sel].as<unsigned>();
-        unsigned *ord2 = ctx->vals[ctx->order_sel ^ 1].as<unsigned>();
-        unsigned char *flags = ctx->keys[0].as<unsigned char>();          // the keys are not needed any more
+    // ---- unpack the order; isolated points to the end of it ------------------------------------------------
+    {
+        const unsigned long long *packed = ctx->keys[ksel].as<unsigned long long>();
+        const unsigned long long mask = (1ull << ib) - 1ull;
+        unsigned *ord = ctx->vals[0].as<unsigned>();
+        unsigned *ord2 = ctx->vals[1].as<unsigned>();
+        unsigned char *flags = ctx->keys[ksel ^ 1].as<unsigned char>();    // the other key buffer is free now
         int *nsel = (int *)((char *)ctx->scratch.p + 2048);
         const int nwin = (int)((n + 31) / 32);
-        k_flag_dense<<<(nwin + 7) / 8, 256, 0, st>>>(ctx->orig.as<float4>(), ord, (int)n, flags);
-        size_t tmp_bytes = 0;
-        CCG_CUDA(ctx, cub::DevicePartition::Flagged(nullptr, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
-        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
-        CCG_CUDA(ctx, cub::DevicePartition::Flagged(ctx->sort_tmp.p, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
-        ctx->order_sel ^= 1;
-        ctx->stats.launches_build += 3;
+        k_flag_dense<<<(nwin + 7) / 8, 256, 0, st>>>(ctx->orig.as<float4>(), packed, mask, (int)n, ord, flags);
+        ctx->stats.launches_build++;
+        ctx->order_sel = 0;
+        if (ctx->split_sparse && n > 64) {
+            size_t tmp_bytes = 0;
+            CCG_CUDA(ctx, cub::DevicePartition::Flagged(nullptr, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
+            CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+            CCG_CUDA(ctx, cub::DevicePartition::Flagged(ctx->sort_tmp.p, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
+            ctx->order_sel = 1;
+            ctx->stats.launches_build += 2;
+        }
     }
     // ---- leaves + box levels ----------------------------------------------------------------------------
     {

@@ -95,6 +95,7 @@ struct ccg_ctx {
     int64_t vox_n = 0; int vox_nf = 0;
     ccg::DevBuf ptx_bytes, ptx_starts, ptx_points, ptx_c2g;   // last ccg_ptx_parse: file bytes, line starts, 32-byte rows, cloud_to_grid_map
     int64_t ptx_n = 0;
+    ccg::DevBuf rule_T, rule_I;   // per sorted position: d2 threshold / tie index threshold of a capped radius search (radsel.cu)
     ccg::DevBuf defer, defer_b;   // [count | query list | output rows] of queries deferred to the exact point kernel (double buffer)
     int defer_sel = 0, side_pending = 0, last_side = 0;
     cudaStream_t side_stream = nullptr;  // the point kernel of launch i runs here, next to tile launch i+1
@@ -201,6 +202,14 @@ struct PointArgs {
     int mean_k; float *mean_d;
 };
 int launch_point_query(ccg_ctx *ctx, const PointArgs &a);
+
+// radsel.cu: capped radius neighbourhoods for any cap (rule arrays) and the list-free reductions over them
+int launch_radius_rule(ccg_ctx *ctx, float rb, int max_nn, const float **Tpos, const int32_t **Ipos);
+int launch_rule_pca(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, const StreamArgs &a);
+int launch_rule_stdev_dist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, int use_depth, const float centre[3], float *out);
+int launch_rule_normal_stdev(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, const void *normals, size_t stride, float *out);
+int launch_rule_hist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, int bins, int which, double radius, const void *attr,
+                     size_t stride, float *hist);
 
 int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count);
 int launch_tile_attrsum2(ccg_ctx *ctx, float rb1, float rb2, const void *attr_dev, size_t stride, float *sum1, int32_t *count1,

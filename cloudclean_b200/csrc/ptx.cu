@@ -23,6 +23,8 @@
 // what fscanf("%f") uses.  More than 19 significant digits, magnitudes outside [1e-37, 3e38] (other than 0), "nan",
 // "inf" and hex floats are reported as unsupported (the line number is returned) — never guessed.
 #include "common.cuh"
+#include <locale.h>
+#include <limits.h>
 #include <cub/block/block_reduce.cuh>
 #include <cub/block/block_scan.cuh>
 #include <cub/device/device_scan.cuh>
@@ -360,7 +362,10 @@ struct Kept {
 };
 
 // decimation rule of pointcloud.cpp:219-230 on the line number (blank lines do not count), the (0,0,0) drop of :263-265,
-// and the first sampled line that could not be parsed (the reference returns false there, :237-252)
+// and the first sampled line that could not be parsed.  STRICTER THAN THE REFERENCE, on purpose: there a failed fscanf without
+// a stream error `continue`s (:247-257) with the file position left in the middle of the bad line, so every later row is
+// read from wherever the stream happens to stand; this loader refuses the file with the line number instead (documented in
+// include/ccgpu.h and INTEGRATION.md).  Only a stream error makes the reference return false (:259-264).
 __global__ void __launch_bounds__(256) k_ptx_classify(const float4 *__restrict__ vals, const unsigned char *__restrict__ status,
                                                       const unsigned long long *__restrict__ lineno, size_t nlines, long long file_width,
                                                       long long line_count, int dec, unsigned char *__restrict__ keep,
@@ -410,16 +415,28 @@ __global__ void __launch_bounds__(256) k_ptx_emit(const float4 *__restrict__ val
 // ---------------------------------------------------------------------------------------------------
 static int parse_header(ccg_ctx *ctx, const char *text, size_t len, int dec, ccg_ptx_info *info) {
     // text is NUL-terminated (len bytes + 0)
-    int off = 0, used = 0;
-    int w = 0, h = 0;
-    if (sscanf(text, "%d %d%n", &w, &h, &used) != 2) return set_error(ctx, CCG_ERR_INVALID, "PTX header: cannot read the grid size");
-    off += used;
-    if (w <= 0 || h <= 0) return set_error(ctx, CCG_ERR_INVALID, "PTX header: grid %d x %d", w, h);
+    // The reference parses these 14 numbers with fscanf under setlocale(LC_NUMERIC, "C") (pointcloud.cpp:132: the Qt host
+    // application runs in the user's locale).  A library must not touch the process locale, so the numbers are read with
+    // strtol / strtof_l against an explicit "C" locale object: same grammar as fscanf's %d / %f (leading white space
+    // skipped, longest valid prefix), independent of LC_NUMERIC.
+    static locale_t c_loc = newlocale(LC_ALL_MASK, "C", (locale_t)0);
+    const char *cur = text;
+    char *end = nullptr;
+    const long wl = strtol(cur, &end, 10);
+    if (end == cur) return set_error(ctx, CCG_ERR_INVALID, "PTX header: cannot read the grid size");
+    cur = end;
+    const long hl = strtol(cur, &end, 10);
+    if (end == cur) return set_error(ctx, CCG_ERR_INVALID, "PTX header: cannot read the grid size");
+    cur = end;
+    const int w = (int)wl, h = (int)hl;
+    if (wl <= 0 || hl <= 0 || wl > INT_MAX || hl > INT_MAX) return set_error(ctx, CCG_ERR_INVALID, "PTX header: grid %ld x %ld", wl, hl);
     float f[12];
     for (int i = 0; i < 12; ++i) {
-        if (sscanf(text + off, "%f%n", &f[i], &used) != 1) return set_error(ctx, CCG_ERR_INVALID, "PTX header: cannot read scanner pose value %d", i);
-        off += used;
+        f[i] = c_loc ? strtof_l(cur, &end, c_loc) : strtof(cur, &end);
+        if (end == cur) return set_error(ctx, CCG_ERR_INVALID, "PTX header: cannot read scanner pose value %d", i);
+        cur = end;
     }
+    const int off = (int)(cur - text);
     // five fgets: the rest of the current line, then the 4x4 transform (:175-180)
     size_t p = (size_t)off;
     for (int i = 0; i < 5; ++i) {

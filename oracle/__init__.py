@@ -239,6 +239,24 @@ def binary_potential(points, idx, inverse_sigma):
     return np.where(idx < 0, 0.0, w)
 
 
+def _eigen_sum3(a0, a1, a2):
+    """Sum of a fixed-size 3-vector expression as Eigen <= 3.2 evaluates it for Vector3f / Map<Vector3f> (.dot(), .norm(),
+    .sum()): not vectorised (12 bytes), completely unrolled by redux_novec_unroller, which halves the range —
+    func(a0, func(a1, a2)) [EXT Eigen/src/Core/Redux.h].  float32 in, float32 out."""
+    F = np.float32
+    return (a0.astype(F) + (a1.astype(F) + a2.astype(F)).astype(F)).astype(F)
+
+
+def _capped_lists(pts, r, max_nn, strict_lt):
+    """radiusSearch(i, r, idx, d2, max_nn) for every point: the max_nn nearest inside r in ascending (d2, index) order;
+    max_nn == 0 or >= n means every point inside r (FLANN caps only when 0 < max_nn < n)."""
+    T = Tree(pts)
+    n = pts.shape[0]
+    if max_nn <= 0 or max_nn >= n:
+        max_nn = int(max(1, T.radius(r, strict_lt=strict_lt, lists=False)["total"].max()))
+    return T.radius(r, cap=max_nn, strict_lt=strict_lt)
+
+
 def normal_stdev(points, normals, r, max_nn):
     """f2 — normal_stdev (cv.h:123-206) as written: strict radius, the max_nn nearest in ascending (d2, index) order,
     cosine = dot / |neighbour| * |current| (sic), clamp, angle = float(acosf / pi [double]), float sums in neighbour
@@ -246,18 +264,18 @@ def normal_stdev(points, normals, r, max_nn):
     F = np.float32
     pts = _cloud(points)
     nr = np.ascontiguousarray(normals, dtype=F)[:, :3]
-    res = Tree(pts).radius(r, cap=max_nn, strict_lt=True)
+    res = _capped_lists(pts, r, max_nn, True)
     idx, cnt = res["idx"], res["count"]
     n = pts.shape[0]
     cur = nr
     with np.errstate(all="ignore"):
-        cn = np.sqrt(((cur[:, 0] * cur[:, 0]).astype(F) + (cur[:, 1] * cur[:, 1]).astype(F)).astype(F) + (cur[:, 2] * cur[:, 2]).astype(F)).astype(F)
+        cn = np.sqrt(_eigen_sum3(cur[:, 0] * cur[:, 0], cur[:, 1] * cur[:, 1], cur[:, 2] * cur[:, 2])).astype(F)
         s = np.zeros(n, F); sq = np.zeros(n, F)
-        for j in range(max_nn):
+        for j in range(idx.shape[1]):
             live = j < cnt
             nb = nr[np.where(live, idx[:, j], 0)]
-            dot = (((nb[:, 0] * cur[:, 0]).astype(F) + (nb[:, 1] * cur[:, 1]).astype(F)).astype(F) + (nb[:, 2] * cur[:, 2]).astype(F)).astype(F)
-            nn = np.sqrt(((nb[:, 0] * nb[:, 0]).astype(F) + (nb[:, 1] * nb[:, 1]).astype(F)).astype(F) + (nb[:, 2] * nb[:, 2]).astype(F)).astype(F)
+            dot = _eigen_sum3(nb[:, 0] * cur[:, 0], nb[:, 1] * cur[:, 1], nb[:, 2] * cur[:, 2])
+            nn = np.sqrt(_eigen_sum3(nb[:, 0] * nb[:, 0], nb[:, 1] * nb[:, 1], nb[:, 2] * nb[:, 2])).astype(F)
             cosine = ((dot / nn).astype(F) * cn).astype(F)
             cosine = np.where(cosine < 0, F(0), np.where(cosine > 1, F(1), cosine)).astype(F)       # clamp(): NaN passes through
             angle = (np.arccos(cosine).astype(F).astype(np.float64) / np.pi).astype(F)
@@ -276,16 +294,16 @@ def stdev_dist(points, r, max_nn, use_depth=False, centre=None):
     F = np.float32
     pts = _cloud(points)
     xyz = pts[:, :3]
-    res = Tree(pts).radius(r, cap=max_nn, strict_lt=False)
+    res = _capped_lists(pts, r, max_nn, False)
     idx, cnt = res["idx"], res["count"]
     n = pts.shape[0]
     ref = np.broadcast_to(np.asarray(centre, F), (n, 3)) if use_depth else xyz
     s = np.zeros(n, F); sq = np.zeros(n, F)
-    for j in range(max_nn):
+    for j in range(idx.shape[1]):
         live = j < cnt
         p = xyz[np.where(live, idx[:, j], 0)]
         d = (p - ref).astype(F)
-        dist = np.sqrt(((d[:, 0] * d[:, 0]).astype(F) + (d[:, 1] * d[:, 1]).astype(F)).astype(F) + (d[:, 2] * d[:, 2]).astype(F)).astype(F)
+        dist = np.sqrt(_eigen_sum3(d[:, 0] * d[:, 0], d[:, 1] * d[:, 1], d[:, 2] * d[:, 2])).astype(F)
         s = np.where(live, (s + dist).astype(F), s)
         sq = np.where(live, (sq + (dist * dist).astype(F)).astype(F), sq)
     m = cnt.astype(F)
@@ -299,13 +317,13 @@ def neighbour_hist(points, r, max_nn, bins, attr=None):
     max_nn nearest, < 3 neighbours -> zeros, every neighbour adds float(1.0/m) to its bin (clamped to [0, bins-1])."""
     F = np.float32
     pts = _cloud(points)
-    res = Tree(pts).radius(r, cap=max_nn, strict_lt=True)
+    res = _capped_lists(pts, r, max_nn, True)
     idx, cnt, d2 = res["idx"], res["count"], res["d2"]
     n = pts.shape[0]
     hist = np.zeros((n, bins), F)
     inc = (1.0 / np.maximum(cnt, 1).astype(np.float64)).astype(F)
     rows = np.arange(n)
-    for j in range(max_nn):
+    for j in range(idx.shape[1]):
         live = (j < cnt) & (cnt >= 3)
         if attr is None:
             b = ((np.sqrt(np.where(live, d2[:, j], 0).astype(F)).astype(np.float64) / float(r)) * (bins - 1)).astype(np.int64)

@@ -164,18 +164,13 @@ def test_pca_knn_fused_features_equal_standalone(gpu_ctx):
 
 # ---- a4 / a5 / a6 radius + PCA (getPCA / getHist) -------------------------------------------------------
 @pytest.mark.parametrize("name", ["uniform", "coplanar", "clusters_outliers", "n2", "lattice_ties"])
-@pytest.mark.parametrize("r,max_nn", [(0.2, 20), (0.1, 64), (0.15, 0), (0.2, 1000)])
+@pytest.mark.parametrize("r,max_nn", [(0.2, 20), (0.1, 64), (0.15, 0), (0.2, 1000), (0.3, 100), (0.5, 700)])
 def test_pca_radius_getpca(gpu_ctx, name, r, max_nn):
     pts = SMALL[name]
     n = pts.shape[0]
     T = oracle.Tree(pts)
     total = T.radius(r, strict_lt=True, lists=False)["total"]
     gpu_ctx.set_cloud(pts)
-    if max_nn > cc.MAX_K and max_nn < n and (total > max_nn).any():
-        with pytest.raises(cc.CcgError) as e:
-            gpu_ctx.pca_radius(r, max_nn)
-        assert e.value.code == -5
-        return
     cap = n if (max_nn == 0 or max_nn >= n) else max_nn          # FLANN caps only when 0 < max_nn < n
     lists = T.radius(r, cap=cap, strict_lt=True)
     ref = oracle.pca_lists(pts, lists["idx"], count=lists["count"], cov_norm=cc.COV_NM1)
@@ -386,6 +381,42 @@ def test_pipelined_host_outputs_are_identical(monkeypatch, shuffle, chunks):
     assert np.array_equal(got[5], rmask) and np.array_equal(got[6], rmd)
 
 
+def test_cancel_inside_a_pipelined_call_leaves_nothing_in_flight(monkeypatch):
+    """The cancel flag (PointCloud::deleting_, normalestimation.cpp:305-306) raised from another thread while a
+    host-output call is shipping chunks: the call ends with CCG_OK or CCG_ERR_CANCELLED, no copy is still running when it
+    returns (the output buffers are dropped right away), and the context answers the next call correctly."""
+    import threading
+    monkeypatch.setenv("CCG_PIPELINE_CHUNKS", "8")
+    monkeypatch.setenv("CCG_PIPELINE_MIN_POINTS", "0")
+    scan = synth.make_scan_np(640, 480, scene="room", seed=22)
+    pts = np.ascontiguousarray(scan["points"])
+    n = pts.shape[0]
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        flag = ctypes.c_int(0)
+        ctx.L.ccg_set_cancel_flag(ctx.h, ctypes.byref(flag))
+        seen = set()
+        for delay in (0.0, 0.0005, 0.002, 0.005):
+            eig = np.empty((n, 3), np.float32); nrm = np.empty((n, 4), np.float32); feat = np.empty((n, 7), np.float32)
+            flag.value = 0
+            t = threading.Timer(delay, lambda: setattr(flag, "value", 1))
+            t.start()
+            try:
+                ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat)
+                seen.add(0)
+            except cc.CcgError as e:
+                assert e.code == -6
+                seen.add(-6)
+            t.join()
+            del eig, nrm, feat                                    # a caller frees its buffers as soon as the call is back
+        flag.value = 0
+        ctx.L.ccg_set_cancel_flag(ctx.h, None)
+        idx, _ = ctx.knn(8)
+        ri, _ = oracle.Tree(pts).knn(8)
+        assert np.array_equal(idx, ri)
+        assert seen                                               # at least one of the two outcomes happened, none crashed
+
+
 # ---- f1: voxel downsample (octreeDownsample, utils.h:16-62) -------------------------------------------------
 @pytest.mark.parametrize("res", [0.02, 0.1, 0.5])
 @pytest.mark.parametrize("as_written", [True, False])
@@ -481,13 +512,42 @@ def test_stdev_dist(gpu_ctx, r, max_nn, use_depth):
     assert np.array_equal(got, want)       # fp32 +,*,/,sqrt in the same order on both sides: identical bits
 
 
-def test_reductions_reject_uncapped(gpu_ctx):
+@pytest.mark.parametrize("r,max_nn", [(0.1, 0), (0.3, 100), (0.3, 0), (0.5, 1000)])
+def test_reductions_without_a_list(gpu_ctx, r, max_nn):
+    """max_nn == 0 (every point inside r) and caps beyond the list kernels (the reference's max_nn_ is whatever the GUI
+    holds: featureeval.cpp:816,999,1032): the neighbour SET is the oracle's (counts and histograms bit-exact), the two fp32
+    sums run in traversal order instead of ascending distance and are held to 1e-5 of the value range."""
     pts, nrm = _scan_with_normals()
     gpu_ctx.set_cloud(pts)
-    with pytest.raises(cc.CcgError):
-        gpu_ctx.normal_stdev(0.1, 0, nrm, device_out=False)
-    with pytest.raises(cc.CcgError):
-        gpu_ctx.stdev_dist(0.1, 1000, device_out=False)
+    got = gpu_ctx.normal_stdev(r, max_nn, nrm, device_out=False)
+    want = oracle.normal_stdev(pts, nrm, r, max_nn)
+    assert np.all(got[::97] == 0)
+    assert np.abs(got.astype(np.float64) ** 2 - want.astype(np.float64) ** 2).max() <= 1e-5
+    centre = np.array([0.1, -0.2, 0.3], np.float32)
+    for use_depth in (False, True):
+        g = gpu_ctx.stdev_dist(r, max_nn, use_depth, centre, device_out=False)
+        w = oracle.stdev_dist(pts, r, max_nn, use_depth, centre)
+        assert np.abs(g - w).max() <= 1e-5 * max(1.0, float(np.abs(w).max()))
+    for bins in (20, 70):
+        gd = gpu_ctx.neighbour_hist(r, max_nn, bins, device_out=False)
+        assert np.array_equal(gd, oracle.neighbour_hist(pts, r, max_nn, bins))
+        inten = pts[:, 4]
+        gi = gpu_ctx.neighbour_hist(r, max_nn, bins, attr=inten, device_out=False)
+        assert np.array_equal(gi, oracle.neighbour_hist(pts, r, max_nn, bins, attr=inten))
+
+
+def test_capped_radius_ties_follow_the_index_order(gpu_ctx):
+    """A cap that cuts through a class of equidistant candidates (integer lattice): the admitted ones are those with the
+    smallest indices, exactly as the (d2, index) order of the oracle's kd-tree search says."""
+    pts = SMALL["lattice_ties"]
+    T = oracle.Tree(pts)
+    gpu_ctx.set_cloud(pts)
+    for r, cap in ((0.35, 70), (0.5, 90), (0.5, 200)):
+        lists = T.radius(r, cap=cap, strict_lt=True)
+        ref = oracle.pca_lists(pts, lists["idx"], count=lists["count"], cov_norm=cc.COV_NM1)
+        eig, nrm, count = gpu_ctx.pca_radius(r, cap, cc.COV_NM1, want_normals=True)
+        assert np.array_equal(count, lists["count"])
+        check_pca(eig, nrm, ref)
 
 
 @pytest.mark.parametrize("r,max_nn,bins", [(0.1, 20, 20), (0.3, 64, 8), (0.05, 10, 33)])

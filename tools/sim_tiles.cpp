@@ -52,6 +52,8 @@ int main(int argc, char **argv) {
     if (argc < 3) { fprintf(stderr, "usage: sim_tiles cloud.f32 curve(0 morton,1 hilbert) [sample_stride] [leaf]\n"); return 1; }
     const int curve = atoi(argv[2]);
     const int sstride = argc > 3 ? atoi(argv[3]) : 37;
+    const int kbits = argc > 4 ? atoi(argv[4]) : 16;      // bits per axis actually kept in the key (low bits dropped)
+    const int kdrop = argc > 5 ? atoi(argv[5]) : 0;       // extra low KEY bits dropped after interleaving
     FILE *f = fopen(argv[1], "rb");
     fseek(f, 0, SEEK_END); const size_t n = ftell(f) / 12; fseek(f, 0, SEEK_SET);
     std::vector<P3> pts(n);
@@ -66,7 +68,8 @@ int main(int argc, char **argv) {
     for (size_t i = 0; i < n; ++i) {
         unsigned qx = (unsigned)fminf(fmaxf((pts[i].x - lo.x) * inv, 0.f), 65535.f), qy = (unsigned)fminf(fmaxf((pts[i].y - lo.y) * inv, 0.f), 65535.f),
                  qz = (unsigned)fminf(fmaxf((pts[i].z - lo.z) * inv, 0.f), 65535.f);
-        kv[i] = {curve ? hilbert(qx, qy, qz, 16) : morton(qx, qy, qz), (unsigned)i};
+        qx >>= (16 - kbits); qy >>= (16 - kbits); qz >>= (16 - kbits);
+        kv[i] = {(curve ? hilbert(qx, qy, qz, kbits) : morton(qx, qy, qz)) >> kdrop, (unsigned)i};
     }
     std::stable_sort(kv.begin(), kv.end(), [](auto &a, auto &b) { return a.first < b.first; });
     // isolated-point split (k_flag_dense)
