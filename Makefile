@@ -21,7 +21,7 @@ oracle:
 # reference-named C++ host layer + its GPU test program (links only the C ABI)
 adapters: adapters/test_adapters
 adapters/test_adapters: adapters/test_adapters.cpp adapters/cloudclean_gpu.hpp include/ccgpu.h $(LIB)
-	g++ -O2 -std=c++14 -ffp-contract=off -Wall -I. adapters/test_adapters.cpp -o $@ -Lcloudclean_b200 -lccgpu -Wl,-rpath,'$$ORIGIN/../cloudclean_b200'
+	g++ -O2 -std=c++14 -ffp-contract=off -Wall -pthread -I. adapters/test_adapters.cpp -o $@ -Lcloudclean_b200 -lccgpu -Wl,-rpath,'$$ORIGIN/../cloudclean_b200'
 
 clean:
 	rm -f $(OBJ) $(LIB) $(SRC)/*.ptxas.log adapters/test_adapters

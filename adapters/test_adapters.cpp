@@ -5,6 +5,10 @@
 #include <array>
 #include <cmath>
 #include <cstdio>
+#include <chrono>
+#include <thread>
+#include <future>
+#include <atomic>
 #include <cstdlib>
 #include <limits>
 #include <numeric>
@@ -332,7 +336,7 @@ int main() {
                 const PointXYZI &p = pts[c.second];
                 volatile float dx = p.x - pts[i].x, dy = p.y - pts[i].y, dz = p.z - pts[i].z;
                 volatile float xx = dx * dx, yy = dy * dy, zz = dz * dz;
-                volatile float ss = xx + yy; ss = ss + zz;
+                volatile float ss = yy + zz; ss = xx + ss;         // Eigen <= 3.2 Vector3f::norm(): a0 + (a1 + a2) [EXT Redux.h]
                 volatile float dist = std::sqrt((float)ss);
                 sum = sum + dist;
                 volatile float d2v = dist * dist;
@@ -458,6 +462,50 @@ int main() {
         s.setCancelFlag(&cancel);
         CHECK(estimateNormals(s, pts.data(), n, c2g, W, H).empty(), "a raised deleting_ flag must cancel estimateNormals");
         s.setCancelFlag(nullptr);
+    }
+
+    // ---- the threading contract of NormalEstimator (normalestimation.cpp:196, :305-306): estimateNormals runs on a
+    //      std::async worker with a Session of its own while the GUI thread keeps using ITS Session, and the GUI thread
+    //      raises PointCloud::deleting_ at any moment.  Every outcome must be a full result or an empty one (cancelled),
+    //      never a crash, and both Sessions must answer correctly afterwards.
+    {
+        auto reference = estimateNormals(s, pts.data(), n, c2g, W, H, true);
+        CHECK(reference.size() == n, "estimateNormals baseline for the threading check");
+        int full = 0, cancelled = 0;
+        for (int round = 0; round < 6; ++round) {
+            std::atomic<int> deleting(0);
+            auto fut = std::async(std::launch::async, [&]() {
+                Session worker(0);                                       // the worker thread owns its context
+                worker.setCancelFlag(reinterpret_cast<const volatile int *>(&deleting));
+                std::vector<Normal> last;
+                for (int rep = 0; rep < 4; ++rep) {
+                    last = estimateNormals(worker, pts.data(), n, c2g, W, H, true);
+                    if (last.empty()) break;
+                }
+                return last;
+            });
+            // meanwhile the "GUI thread" works on its own Session ...
+            auto pca = getPCA(s, pts.data(), n, 0.1, 20);
+            CHECK(pca->size() == n, "GUI-thread getPCA while the worker runs (%s)", s.lastError().c_str());
+            // ... and deletes the cloud at some point (rounds 0-1: never, later rounds: earlier and earlier)
+            if (round >= 2) {
+                std::this_thread::sleep_for(std::chrono::microseconds(4000 >> (round - 2)));
+                deleting.store(1);
+            }
+            std::vector<Normal> got = fut.get();
+            if (got.empty()) {
+                ++cancelled;
+                CHECK(deleting.load() == 1, "estimateNormals returned nothing although deleting_ was never raised");
+            } else {
+                ++full;
+                CHECK(got.size() == n && std::memcmp(got.data(), reference.data(), n * sizeof(Normal)) == 0,
+                      "worker-thread normals differ from the GUI-thread result");
+            }
+        }
+        std::printf("threading: %d full results, %d cancelled\n", full, cancelled);
+        CHECK(full >= 2, "the rounds without deletion must complete");
+        auto again = estimateNormals(s, pts.data(), n, c2g, W, H, true);
+        CHECK(again.size() == n && std::memcmp(again.data(), reference.data(), n * sizeof(Normal)) == 0, "session unusable after the threaded rounds");
     }
 
     std::printf(g_fail ? "adapters: %d check(s) FAILED\n" : "adapters: all checks passed\n", g_fail);

@@ -273,7 +273,7 @@ def other_configs(ctx, cc, stream, dev, peak, shrink):
             for r_ in (0.05, 0.1, 0.2):
                 try:
                     ms, res = timed(lambda: ctx.pca_radius(r_, max_nn, device_out=dev), reps=2)
-                except cc.CCGError as e:
+                except cc.CcgError as e:
                     per[f"r={r_}"] = {"error": str(e)}
                     continue
                 e3, _, cnt = res

@@ -30,6 +30,7 @@ SYMBOLS = [
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
     "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_fpfh", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
+    "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route",
 ]
 
 
@@ -76,6 +77,8 @@ def load_library():
     L.ccg_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.ccg_set_cancel_flag.argtypes = [vp, vp]
     L.ccg_set_stream.argtypes = [vp, vp]
+    L.ccg_set_async.argtypes = [vp, i32]
+    L.ccg_sync.argtypes = [vp]
     L.ccg_set_cloud.argtypes = [vp, vp, sz, sz]
     L.ccg_cloud_size.argtypes = [vp]
     L.ccg_cloud_size.restype = C.c_int64
@@ -96,6 +99,7 @@ def load_library():
     L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_shard.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, vp]
+    L.ccg_pca_knn_features_route.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, sz, vp, vp, vp]
     L.ccg_knn_graph.argtypes = [vp, i32, f64, vp, vp]
     L.ccg_normal_stdev.argtypes = [vp, f64, i32, vp, sz, vp]
     L.ccg_stdev_dist.argtypes = [vp, f64, i32, i32, vp, vp]
@@ -212,6 +216,13 @@ class Context:
         self._check(self.L.ccg_set_stream(self.h, C.c_void_p(cuda_stream) if cuda_stream else None))
         self._own_stream = not cuda_stream
 
+    def set_async(self, on=True):
+        """entry points enqueue on the ctx stream and return; results / deferred errors / stats are valid after sync()"""
+        self._check(self.L.ccg_set_async(self.h, 1 if on else 0))
+
+    def sync(self):
+        self._check(self.L.ccg_sync(self.h))
+
     def _settle(self, *tensors):
         """The ctx's own stream is non-blocking, i.e. NOT ordered after torch's streams: when a torch CUDA tensor is an
         INPUT and no shared stream was set, wait for torch's current stream so pending writes to it have landed."""
@@ -302,6 +313,23 @@ class Context:
         vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
         self._check(self.L.ccg_pca_knn_features_shard(self.h, k, cov_norm, _ptr(vp), formula_set, rank, world, chunk_points,
                                                       1 if sorted_rows else 0, _addr(eig), _addr(nrm), _addr(feat)))
+
+    def pca_knn_features_route(self, k, cov_norm, formula_set, rank, world, rows_per_rank, eig_of_rank, nrm_of_rank, feat_of_rank,
+                               chunk_points=8192, viewpoint=None):
+        """answer this rank's interleaved chunks and store every row into the arrays of the rank that OWNS its original
+        index (lists of device addresses / DevBuffers / tensors, one per rank; own memory or ccg_ipc_open'ed peer memory)"""
+        vp = None if viewpoint is None else np.ascontiguousarray(viewpoint, np.float32)
+
+        def table(lst):
+            if lst is None:
+                return None
+            arr = (C.c_void_p * world)()
+            for i, a in enumerate(lst):
+                arr[i] = _addr(a).value
+            return arr
+        te, tn, tf = table(eig_of_rank), table(nrm_of_rank), table(feat_of_rank)
+        self._check(self.L.ccg_pca_knn_features_route(self.h, k, cov_norm, _ptr(vp), formula_set, rank, world, chunk_points,
+                                                      rows_per_rank, te, tn, tf))
 
     def normal_stdev(self, r, max_nn, normals, device_out=None):
         """normal_stdev (cv.h:123-206): normals = [n, S>=3] float32 (host numpy or torch CUDA) -> float32[n]"""

@@ -59,6 +59,7 @@ static int query_begin(ccg_ctx *ctx) { CCG_CUDA(ctx, cudaEventRecord(ctx->ev[3],
 static int query_end(ccg_ctx *ctx) { CCG_TRY(join_side(ctx)); CCG_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream)); return CCG_OK; }
 static int finish_call(ccg_ctx *ctx) {
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
+    if (ctx->async_mode) { ctx->pending_stats = 1; return CCG_OK; }      // ccg_sync collects
     CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     CCG_CUDA(ctx, cudaGetLastError());
     cudaEventElapsedTime(&ctx->stats.ms_query, ctx->ev[3], ctx->ev[4]);
@@ -376,6 +377,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->curve_hilbert = (cv && cv[0] == 'm') ? 0 : 1;
     const char *da = getenv("CCG_SEL_DRAIN_AT");
     if (da) ctx->sel_drain_at = atoi(da);
+    const char *mb = getenv("CCG_SEL_MINB");
+    if (mb) ctx->sel_minb = atoi(mb);
     const char *sg = getenv("CCG_SEL_STAGE");
     ctx->sel_stage = (sg && sg[0] == 'l') ? 0 : 1;
     const char *sc = getenv("CCG_SEL_CHUNKS");
@@ -432,6 +435,29 @@ int ccg_set_stream(ccg_ctx *ctx, void *cuda_stream) {
     if (cudaSetDevice(ctx->device) == cudaSuccess && ctx->stream) cudaStreamSynchronize(ctx->stream);
     ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
     return CCG_OK;
+}
+
+int ccg_set_async(ccg_ctx *ctx, int on) {
+    if (!ctx) return CCG_ERR_INVALID;
+    if (ctx->async_mode && !on) { const int rc = ccg_sync(ctx); ctx->async_mode = 0; return rc; }
+    ctx->async_mode = on ? 1 : 0;
+    return CCG_OK;
+}
+
+int ccg_sync(ccg_ctx *ctx) {
+    if (!ctx) return CCG_ERR_INVALID;
+    CCG_CUDA(ctx, cudaSetDevice(ctx->device));
+    CCG_TRY(join_side(ctx));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->copy_stream) CCG_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+    CCG_CUDA(ctx, cudaGetLastError());
+    if (ctx->pending_stats) {
+        ctx->pending_stats = 0;
+        cudaEventElapsedTime(&ctx->stats.ms_query, ctx->ev[3], ctx->ev[4]);
+        cudaEventElapsedTime(&ctx->stats.ms_download, ctx->ev[4], ctx->ev[5]);
+        cudaGetLastError();
+    }
+    return finish_cloud_check(ctx);
 }
 
 int ccg_set_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes) {
@@ -739,13 +765,15 @@ static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise
         a.eig3 = oe.dev<float>(); a.normal4 = on.dev<float>(); a.count = oc.dev<int32_t>();
         a.feat7 = of.dev<float>(); a.formula_set = formula_set;
         a.shard_world = ctx->shard_world; a.shard_rank = ctx->shard_rank; a.shard_chunk = ctx->shard_chunk;
+        a.route_world = ctx->route_world; a.route_rows = ctx->route_rows;
+        a.r_eig = ctx->route_ptr[0]; a.r_nrm = ctx->route_ptr[1]; a.r_feat = ctx->route_ptr[2];
         PipeOut po[4];
         int npo = 0;
         if (oe.staged) po[npo++] = PipeOut{&oe, 12};
         if (on.staged) po[npo++] = PipeOut{&on, 16};
         if (oc.staged) po[npo++] = PipeOut{&oc, 4};
         if (of.staged) po[npo++] = PipeOut{&of, 28};
-        if (npo > 0 && !sorted_rows && a.shard_world <= 1 && ctx->pipeline_chunks > 1 && !ctx->collect_stats && ctx->n >= (size_t)ctx->pipeline_min_points)
+        if (npo > 0 && !sorted_rows && a.shard_world <= 1 && ctx->pipeline_chunks > 1 && !ctx->collect_stats && !ctx->async_mode && ctx->n >= (size_t)ctx->pipeline_min_points)
             CCG_TRY(pipelined_query(ctx, a, po, npo, ctx->pipeline_chunks));
         else
             CCG_TRY(launch_tile_query(ctx, a));
@@ -803,6 +831,31 @@ int ccg_pca_knn_features_shard(ccg_ctx *ctx, int k, int cov_norm, const float *v
     const int rc = pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, 0, ctx->n, sorted_rows ? 1 : 0, eig3, normal4, nullptr, false, feat7,
                               formula_set);
     ctx->shard_world = 0; ctx->shard_rank = 0; ctx->shard_chunk = 0;
+    return rc;
+}
+
+int ccg_pca_knn_features_route(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
+                               int chunk_points, size_t rows_per_rank, float *const *eig3_of_rank, float *const *normal4_of_rank,
+                               float *const *feat7_of_rank) {
+    CCG_TRY(begin_call(ctx, true));
+    if (k < 1 || k > CCG_MAX_K) return set_error(ctx, CCG_ERR_UNSUPPORTED, "k=%d outside [1,%d]", k, CCG_MAX_K);
+    if (world < 1 || world > 16 || rank < 0 || rank >= world) return set_error(ctx, CCG_ERR_INVALID, "need 0 <= rank < world <= 16");
+    if (chunk_points < 32 || chunk_points % 32) return set_error(ctx, CCG_ERR_INVALID, "chunk_points must be a positive multiple of 32");
+    if (rows_per_rank == 0 || rows_per_rank * (size_t)world < ctx->n) return set_error(ctx, CCG_ERR_INVALID, "rows_per_rank * world must cover the cloud");
+    for (int r = 0; r < world; ++r) {
+        ctx->route_ptr[0][r] = eig3_of_rank ? eig3_of_rank[r] : nullptr;
+        ctx->route_ptr[1][r] = normal4_of_rank ? normal4_of_rank[r] : nullptr;
+        ctx->route_ptr[2][r] = feat7_of_rank ? feat7_of_rank[r] : nullptr;
+        for (int a = 0; a < 3; ++a)
+            if (ctx->route_ptr[a][r] && !is_dev(ctx, ctx->route_ptr[a][r])) return set_error(ctx, CCG_ERR_INVALID, "route outputs must be device (own or peer) memory");
+    }
+    ctx->shard_world = world > 1 ? world : 0; ctx->shard_rank = rank; ctx->shard_chunk = chunk_points / 32;
+    ctx->route_world = world; ctx->route_rows = rows_per_rank;
+    if (world == 1) ctx->route_world = 0;
+    // non-NULL markers so that pca_common opens the three outputs as "device" buffers; with world == 1 they ARE the outputs
+    float *e = ctx->route_ptr[0][rank], *nn = ctx->route_ptr[1][rank], *f = ctx->route_ptr[2][rank];
+    const int rc = pca_common(ctx, k, INFINITY, cov_norm, 0, viewpoint3, 0, ctx->n, 0, e, nn, nullptr, false, f, formula_set);
+    ctx->shard_world = 0; ctx->shard_rank = 0; ctx->shard_chunk = 0; ctx->route_world = 0; ctx->route_rows = 0;
     return rc;
 }
 

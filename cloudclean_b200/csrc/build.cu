@@ -255,6 +255,21 @@ __global__ void __launch_bounds__(256) k_build_level(const float4 *__restrict__ 
     }
 }
 
+// ccg_sync after an asynchronous build: the deferred finiteness check, bounding box and timings
+int finish_cloud_check(ccg_ctx *ctx) {
+    if (!ctx->pending_cloud_check) return CCG_OK;
+    ctx->pending_cloud_check = 0;
+    const IngestScratch *res = ctx->hpin[1].as<IngestScratch>();
+    cudaEventElapsedTime(&ctx->stats.ms_upload, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ctx->stats.ms_build, ctx->ev[1], ctx->ev[2]);
+    if (res->nonfinite) {
+        ctx->has_cloud = false;
+        return set_error(ctx, CCG_ERR_NONFINITE, "cloud holds non-finite coordinates");
+    }
+    for (int d = 0; d < 3; ++d) { ctx->bb_lo[d] = ord2f(res->lo[d]); ctx->bb_hi[d] = ord2f(res->hi[d]); }
+    return CCG_OK;
+}
+
 static int is_device_ptr(const void *p, int device) {
     cudaPointerAttributes at;
     cudaError_t e = cudaPointerGetAttributes(&at, p);
@@ -399,12 +414,16 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
     IngestScratch *res = ctx->hpin[1].as<IngestScratch>();
     CCG_CUDA(ctx, cudaMemcpyAsync(res, ctx->scratch.p, sizeof(IngestScratch), cudaMemcpyDeviceToHost, st));
     CCG_CUDA(ctx, cudaEventRecord(ctx->ev[2], st));
-    CCG_CUDA(ctx, cudaStreamSynchronize(st));
-    CCG_CUDA(ctx, cudaGetLastError());
-    if (res->nonfinite) return set_error(ctx, CCG_ERR_NONFINITE, "cloud holds non-finite coordinates");
-    for (int d = 0; d < 3; ++d) { ctx->bb_lo[d] = ord2f(res->lo[d]); ctx->bb_hi[d] = ord2f(res->hi[d]); }
-    cudaEventElapsedTime(&ctx->stats.ms_upload, ctx->ev[0], ctx->ev[1]);
-    cudaEventElapsedTime(&ctx->stats.ms_build, ctx->ev[1], ctx->ev[2]);
+    if (ctx->async_mode) {
+        ctx->pending_cloud_check = 1;                 // ccg_sync reads the finiteness word and the bounding box
+    } else {
+        CCG_CUDA(ctx, cudaStreamSynchronize(st));
+        CCG_CUDA(ctx, cudaGetLastError());
+        if (res->nonfinite) return set_error(ctx, CCG_ERR_NONFINITE, "cloud holds non-finite coordinates");
+        for (int d = 0; d < 3; ++d) { ctx->bb_lo[d] = ord2f(res->lo[d]); ctx->bb_hi[d] = ord2f(res->hi[d]); }
+        cudaEventElapsedTime(&ctx->stats.ms_upload, ctx->ev[0], ctx->ev[1]);
+        cudaEventElapsedTime(&ctx->stats.ms_build, ctx->ev[1], ctx->ev[2]);
+    }
     ctx->n = n; ctx->npad = npad; ctx->nleaf = nleaf; ctx->nlevels = nlevels;
     ctx->has_cloud = true;
     ctx->stats.n_points = (int64_t)n;

@@ -70,6 +70,9 @@ struct ccg_ctx {
     cudaEvent_t ev_chunk[17] = {};
     cudaEvent_t ev_copy[17] = {};        // D2H of chunk c done (host-side consumers, e.g. the SOR index-order sum)       // output pipelining (created on first use)
     const volatile int *cancel = nullptr;
+    int async_mode = 0;              // ccg_set_async: entry points enqueue and return; ccg_sync collects
+    int pending_stats = 0;
+    int pending_cloud_check = 0;     // an asynchronous build left its bbox / finiteness word in hpin[1]
 
     bool has_cloud = false;
     size_t n = 0;            // points
@@ -108,9 +111,12 @@ struct ccg_ctx {
     int pipeline_chunks = 8;         // host-output pipelining of the PCA query (CCG_PIPELINE_CHUNKS; <= 1 disables)
     int pipeline_min_points = 1 << 18;
     int shard_world = 0, shard_rank = 0, shard_chunk = 0;   // set by ccg_*_shard around pca_common
+    int route_world = 0; size_t route_rows = 0;             // set by ccg_pca_knn_features_route around pca_common
+    float *route_ptr[3][16] = {};
     int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
     int curve_hilbert = 1;   // leaf order along the Hilbert curve (CCG_CURVE=morton: Z-order, for A/B runs)
-    int sel_drain_at = 8;    // k_tile_sel: pending survivors per lane that trigger a drain (CCG_SEL_DRAIN_AT)
+    int sel_drain_at = 0;    // k_tile_sel: pending survivors per lane that trigger a drain; 0 = only at the end of the list (CCG_SEL_DRAIN_AT)
+    int sel_minb = 0;        // k_tile_sel<20>: 12 = the 80-register build (CCG_SEL_MINB=12), else the default 16-block build
     int sel_stage = 1;       // k_tile_sel leaf staging: 1 = cp.async.bulk + mbarrier ring, 0 = LDG/STS (CCG_SEL_STAGE=ldg)
     int sel_chunks = 4;      // sub-launches of a long k_tile_sel launch (CCG_SEL_CHUNKS)
     int point_overlap = 1;   // deferred exact queries on a side stream (CCG_POINT_OVERLAP=0: same stream)
@@ -153,6 +159,7 @@ int set_error(ccg_ctx *ctx, int code, const char *fmt, ...);
 
 // build.cu
 int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes);
+int finish_cloud_check(ccg_ctx *ctx);
 
 // query.cu
 enum TileMode { MODE_KNN = 0, MODE_PCA = 1, MODE_SOR = 2 };
@@ -174,6 +181,8 @@ struct QueryArgs {
     // interleaved shard (multi-GPU load balance): this call answers the tiles t with (t / shard_chunk) % shard_world ==
     // shard_rank and ignores begin/end; shard_world <= 1 = off
     int shard_world, shard_rank, shard_chunk;
+    // owner-routed output rows (ccg_pca_knn_features_route); route_world <= 1 = off
+    int route_world; size_t route_rows; float *const *r_eig; float *const *r_nrm; float *const *r_feat;
     int async_side;         // 1: the caller joins the side stream itself (join_side) — output pipelining
 };
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a);

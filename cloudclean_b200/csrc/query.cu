@@ -409,11 +409,11 @@ __global__ void __launch_bounds__(128) k_tile_topk(const __grid_constant__ TreeV
 // with one lane per child box then lists every leaf whose box is within the warp's largest bound of the tile
 // box (ballot + popc compaction into shared memory).  Compared with the nearest-first stack walk this costs a
 // few hundred instructions per tile instead of ~100 per visited child, and pass 2 re-uses the list.
-constexpr int kListCap = 256;     // leaves listed per tile before the per-query refinement (overflow: sub-box retry, then the point kernel)
+constexpr int kListCap = 253;     // leaves listed per tile (overflow: sub-box retry, then the point kernel); list[253..255] hold the home leaves
 constexpr int kQueueCap = 128;     // inner nodes per level
 struct WarpScratch2 {
     WarpScratch ws;
-    int list[kListCap];
+    int list[256];
     float4 sub[16];
 };
 
@@ -503,8 +503,8 @@ __device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, boo
 //     copy where the cell run is contiguous"; CCG_SEL_STAGE=ldg selects an LDG/STS ring for the A/B profile);
 //   * re-uses the queue as the log of pass 2 (drains clear the bits that fell outside the bound).
 constexpr int kSelStages = 2;
-constexpr int kQCap = 20;              // queue entries per lane: listed leaves use <= kQCap - 3, pass 2 adds the 3 home leaves
-constexpr int kSlotHome = 253;         // qslot codes 253 / 254 / 255 = own leaf / previous / next
+constexpr int kQCap = 20;              // queue entries per lane (curve neighbours + listed leaves <= kQCap - 1, pass 2 adds the own leaf)
+constexpr int kSlotHome = 253;         // list[253] / [254] / [255] = own leaf / previous / next along the curve
 constexpr int kListMax = 252;          // listed leaves a tile may keep after the per-query refinement (u8 slots)
 
 struct alignas(16) SelScratch {
@@ -615,10 +615,6 @@ struct ValList {
     }
 };
 
-__device__ __forceinline__ int sel_leaf_of(const SelScratch &S, int tile, unsigned slot) {
-    return slot < (unsigned)kSlotHome ? S.w.list[slot] : tile + (slot == (unsigned)kSlotHome ? 0 : (slot == (unsigned)kSlotHome + 1 ? -1 : 1));
-}
-
 // ---- staging ring: block of `leaf` -> S.blk[seq & 1] --------------------------------------------------------
 // TMA flavour: lane 0 arms the stage's mbarrier with the byte count and issues one 528-byte cp.async.bulk; the warp
 // waits on the barrier's phase parity when it gets there.  LDG flavour: every lane fetches its float4 of the block into a
@@ -684,10 +680,12 @@ struct QueueWalk {
         ge = first; cnt = cnt_;
         gcur = ge < cnt ? S.q.qmask[ge * 32 + lane] : 0u;
     }
-    __device__ __forceinline__ void next(const TreeView &T, const SelScratch &S, int tile, int lane, float4 &c, int &e, unsigned &bit) {
-        while (gcur == 0u && ge < cnt) {           // masks are non-zero until a drain cleared them: rarely more than one step
+    // every queued mask is non-zero (entries are appended only with survivors, and a drain is followed by a squeeze), so
+    // one step to the next entry is enough when the current mask runs out
+    __device__ __forceinline__ void next(const TreeView &T, const SelScratch &S, int lane, float4 &c, int &e, unsigned &bit) {
+        if (gcur == 0u && ge + 1 < cnt) {
             ++ge;
-            gcur = ge < cnt ? S.q.qmask[ge * 32 + lane] : 0u;
+            gcur = S.q.qmask[ge * 32 + lane];
         }
         e = -1;
         if (gcur) {
@@ -695,7 +693,7 @@ struct QueueWalk {
             bit = 0x80000000u >> j;
             gcur ^= bit;
             e = ge;
-            c = T.pts[(size_t)sel_leaf_of(S, tile, S.q.qslot[ge * 32 + lane]) * kLeaf + j];
+            c = T.pts[(unsigned)(S.w.list[S.q.qslot[ge * 32 + lane]] * kLeaf + j)];
         }
     }
 };
@@ -703,15 +701,15 @@ struct QueueWalk {
 // score the queued survivors of entries [first, cnt): `rounds` = the largest number of pending bits any lane holds.
 // Bits whose candidate is outside the lane's bound are cleared, so that pass 2 does not meet them again.
 template <int K>
-__device__ __forceinline__ void drain_queue(const TreeView &T, SelScratch &S, int tile, int lane, const float4 &q, ValList<K> &v,
+__device__ __forceinline__ void drain_queue(const TreeView &T, SelScratch &S, int lane, const float4 &q, ValList<K> &v,
                                             int first, int cnt, int rounds) {
     QueueWalk w;
     w.start(S, first, cnt, lane);
     float4 fc = q; int fe; unsigned fbit = 0;
-    w.next(T, S, tile, lane, fc, fe, fbit);
+    w.next(T, S, lane, fc, fe, fbit);
     for (int r = 0; r < rounds; ++r) {
         const float4 c = fc; const int e = fe; const unsigned bit = fbit;
-        w.next(T, S, tile, lane, fc, fe, fbit);
+        w.next(T, S, lane, fc, fe, fbit);
         if (e >= 0) {
             const float d = d2_point(q, c);
             if (d <= v.bound) {
@@ -748,19 +746,37 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
                                          int &nlist, bool &lone, unsigned long long *st5) {
     const int lane = threadIdx.x & 31;
     lone = false; cnt = 0; nlist = 0;
-    // ---- home leaves, scored directly: own leaf (the staged queries), then the two curve neighbours -----------------
+    // ---- own leaf, scored directly (every lane wants nearly every candidate of its own leaf: no mask, no drain) -------
     S.w.ws.leaf[lane] = q;
+    if (lane < 3) S.w.list[kSlotHome + lane] = tile + (lane == 0 ? 0 : (lane == 1 ? -1 : 1));
     __syncwarp();
     v.score_direct(q, S.w.ws.leaf);
+    // ---- the two neighbours along the curve: prefilter against the own-leaf bound, queue, one pooled drain ------------
+    int first = 0, pend = 0;
 #pragma unroll 1
-    for (int h = 0; h < 2; ++h) {
-        const int leaf = tile + (h == 0 ? -1 : 1);
+    for (int h = 1; h < 3; ++h) {
+        const int leaf = tile + (h == 1 ? -1 : 1);
         if (leaf < 0 || leaf >= T.count[0]) continue;
-        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
         __syncwarp();
-        S.w.ws.leaf[lane] = p;
-        __syncwarp();
-        v.score_direct(q, S.w.ws.leaf);
+        stg.issue(T, S, leaf, seq, lane);
+        const float4 *blk = stg.await(S, seq, lane);
+        ++seq;
+        const unsigned pm = prefilter_blk(blk, q, v.bound);
+        if (pm) {
+            S.q.qmask[cnt * 32 + lane] = pm;
+            S.q.qslot[cnt * 32 + lane] = (unsigned char)(kSlotHome + h);
+            ++cnt;
+            pend += __popc(pm);
+        }
+    }
+    {
+        const int rounds = __reduce_max_sync(kFull, pend);
+        if (rounds > 0) {
+            drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
+            cnt = squeeze_queue(S, cnt, lane);
+            if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
+        }
+        first = cnt; pend = 0;
     }
     // ---- isolated lanes -> point kernel (a lane whose bound is far above the warp's median would make the tile's
     //      candidate list hundreds of leaves long) --------------------------------------------------------------
@@ -797,18 +813,17 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     if (st5 && lane == 0) { atomicAdd(st5 + 2, (unsigned long long)listed); atomicAdd(st5 + 5, (unsigned long long)nlist); }
     if (nlist > kListMax) return -5;
     // ---- listed leaves: stage, prefilter, queue the survivor masks; pooled drains ----------------------------------
-    int first = 0, pend = 0;
     const int drain_at = P.drain_at;
     if (nlist > 0) stg.issue(T, S, S.w.list[0], seq, lane);
     for (int i = 0; i < nlist; ++i) {
-        if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
+        if (__reduce_max_sync(kFull, cnt) >= kQCap - 1) {
             // a full queue: score what is pending, drop the entries that emptied, give up only if it is still full
             const int rounds = __reduce_max_sync(kFull, pend);
-            drain_queue<K>(T, S, tile, lane, q, v, first, cnt, rounds);
+            drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
             cnt = squeeze_queue(S, cnt, lane);
             first = cnt; pend = 0;
             if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
-            if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
+            if (__reduce_max_sync(kFull, cnt) >= kQCap - 1) {
                 stg.await(S, seq, lane);                 // no copy may be in flight when the block retires
                 ++seq;
                 return -3;
@@ -829,7 +844,8 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
         }
         const int rounds = __reduce_max_sync(kFull, pend);
         if (rounds >= drain_at || (i + 1 == nlist && rounds > 0)) {
-            drain_queue<K>(T, S, tile, lane, q, v, first, cnt, rounds);
+            drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
+            cnt = squeeze_queue(S, cnt, lane);
             first = cnt; pend = 0;
             if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
         }
@@ -846,8 +862,8 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
     mean_d[row] = (float)(s / (double)mean_k);
 }
 
-template <int K, int MODE, bool TMA>
-__global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
+template <int K, int MODE, bool TMA, int MINB>
+__global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
     __shared__ SelScratch s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = P.tile_begin + blockIdx.x * 2 + warp;
@@ -929,25 +945,22 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
             if (i > K - k) dup = dup || (v.key[i] == v.key[i - 1] && v.key[i] != INFINITY);
         if (dup) t = -1.f;
     }
-    // the three home leaves join the queue with their prefilter masks against t (3 entries are reserved for them)
+    // the own leaf joins the queue with its prefilter mask against t (its curve neighbours are in the queue since pass 1)
     int tot = 0;
     {
         const int maxc = __reduce_max_sync(kFull, cnt);
         for (int e = 0; e < maxc; ++e)
             if (e < cnt) tot += __popc(S.q.qmask[e * 32 + lane]);
     }
-#pragma unroll 1
-    for (int h = 0; h < 3; ++h) {
-        const int leaf = tile + (h == 0 ? 0 : (h == 1 ? -1 : 1));
-        if (leaf < 0 || leaf >= T.count[0]) continue;
+    {
         __syncwarp();
-        stg.issue(T, S, leaf, seq, lane);
+        stg.issue(T, S, tile, seq, lane);
         const float4 *blk = stg.await(S, seq, lane);
         ++seq;
         const unsigned pm = prefilter_blk(blk, q, t);
         if (pm) {
             S.q.qmask[cnt * 32 + lane] = pm;
-            S.q.qslot[cnt * 32 + lane] = (unsigned char)(kSlotHome + h);
+            S.q.qslot[cnt * 32 + lane] = (unsigned char)kSlotHome;
             ++cnt;
             tot += __popc(pm);
         }
@@ -962,10 +975,10 @@ __global__ void __launch_bounds__(64, (K > 32 ? 6 : (K > 24 ? 10 : 12))) k_tile_
         QueueWalk w;
         w.start(S, 0, cnt, lane);
         float4 fc = q; int fe; unsigned fbit = 0;
-        w.next(T, S, tile, lane, fc, fe, fbit);
+        w.next(T, S, lane, fc, fe, fbit);
         for (int r = 0; r < rounds; ++r) {
             const float4 c = fc; const int e = fe;
-            w.next(T, S, tile, lane, fc, fe, fbit);
+            w.next(T, S, lane, fc, fe, fbit);
             if (e >= 0) {
                 const float dd = d2_point(q, c);
                 if (dd <= t) {
@@ -1210,17 +1223,22 @@ static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cuda
     k_tile_topk<K><<<blocks, 128, 0, st>>>(T, P);
 }
 
-template <int K, bool TMA>
-static void launch_sel2(const TreeView &T, const TileParams &P, cudaStream_t st) {
+template <int K, bool TMA, int MINB>
+static void launch_sel3(const TreeView &T, const TileParams &P, cudaStream_t st) {
     const int ntiles = P.tile_end - P.tile_begin;
-    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else k_tile_sel<K, MODE_SOR, TMA><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else k_tile_sel<K, MODE_SOR, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
 }
+// Resident blocks per SM the kernel is compiled for (register cap = 65536 / (64 * MINB)).  Shared memory (12.4 KB per
+// block) allows 16; measured on the 30 M scan, K = 20: 12 blocks / 80 registers 28.96 ms, 14 / 72 28.77 ms, 16 / 64 (16 bytes
+// of spills) 28.10 ms — occupancy beats registers here.  CCG_SEL_MINB=12 selects the 80-register build of K = 20 for A/B runs.
 template <int K>
-static void launch_sel(const TreeView &T, const TileParams &P, int tma, cudaStream_t st) {
-    if (tma) launch_sel2<K, true>(T, P, st);
-    else launch_sel2<K, false>(T, P, st);
+static void launch_sel(const TreeView &T, const TileParams &P, int tma, int minb, cudaStream_t st) {
+    constexpr int kDef = K > 32 ? 6 : (K > 24 ? 10 : (K == 20 ? 16 : 12));
+    if (K == 20 && minb == 12) { if (tma) launch_sel3<K, true, 12>(T, P, st); else launch_sel3<K, false, 12>(T, P, st); return; }
+    if (tma) launch_sel3<K, true, kDef>(T, P, st);
+    else launch_sel3<K, false, kDef>(T, P, st);
 }
 
 int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
@@ -1238,6 +1256,15 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     P.pca.cov_norm = a.cov_norm; P.pca.min_pts = a.min_pts; P.pca.normalise_hist = a.normalise_hist; P.pca.has_vp = a.has_vp;
     for (int i = 0; i < 3; ++i) P.pca.vp[i] = a.vp[i];
     P.pca.eig3 = a.eig3; P.pca.normal4 = a.normal4; P.pca.feat7 = a.feat7; P.pca.formula_set = a.formula_set;
+    P.pca.route_world = 0;
+    if (a.route_world > 1) {
+        if (a.route_world > kMaxRoute || a.route_rows == 0) return set_error(ctx, CCG_ERR_INVALID, "route: world must be <= %d and rows_per_rank > 0", kMaxRoute);
+        P.pca.route_world = a.route_world; P.pca.route_rows = (unsigned)a.route_rows;
+        for (int r = 0; r < a.route_world; ++r) {
+            P.pca.r_eig[r] = a.r_eig ? a.r_eig[r] : nullptr; P.pca.r_nrm[r] = a.r_nrm ? a.r_nrm[r] : nullptr;
+            P.pca.r_feat[r] = a.r_feat ? a.r_feat[r] : nullptr;
+        }
+    }
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.tile_order = a.tile_order;
     P.drain_at = ctx->sel_drain_at > 0 ? ctx->sel_drain_at : 1 << 30;
@@ -1302,13 +1329,13 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
         P.defer_list = (int32_t *)((char *)db.p + off_list);
         P.defer_row = (long long *)((char *)db.p + off_rows);
         P.slow_tiles = nullptr;
-        if (k <= 8) launch_sel<8>(T, P, ctx->sel_stage, st);
-        else if (k <= 16) launch_sel<16>(T, P, ctx->sel_stage, st);
-        else if (k <= 20) launch_sel<20>(T, P, ctx->sel_stage, st);
-        else if (k <= 24) launch_sel<24>(T, P, ctx->sel_stage, st);
-        else if (k <= 32) launch_sel<32>(T, P, ctx->sel_stage, st);
-        else if (k <= 48) launch_sel<48>(T, P, ctx->sel_stage, st);
-        else launch_sel<64>(T, P, ctx->sel_stage, st);
+        if (k <= 8) launch_sel<8>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else if (k <= 16) launch_sel<16>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else if (k <= 20) launch_sel<20>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else if (k <= 24) launch_sel<24>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else if (k <= 32) launch_sel<32>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else if (k <= 48) launch_sel<48>(T, P, ctx->sel_stage, ctx->sel_minb, st);
+        else launch_sel<64>(T, P, ctx->sel_stage, ctx->sel_minb, st);
         {
             PointParams Q{};
             Q.queries = P.defer_list; Q.nq = 0; Q.nq_dev = P.defer_count; Q.rows = P.defer_row;

@@ -219,11 +219,16 @@ __device__ __forceinline__ Eig3 eig3_sym(const float a_in[6]) {
     return r;
 }
 
+constexpr int kMaxRoute = 16;
 struct PcaOut {
     int cov_norm, min_pts, normalise_hist, has_vp;
     float vp[3];
     float *eig3, *normal4;
     float *feat7; int formula_set;     // optional fused a9 epilogue
+    // owner-routed rows (multi-GPU, ccg_pca_knn_features_route): row r belongs to rank r / route_rows and is stored at local
+    // row r % route_rows of THAT rank's arrays (own memory or NVLink peer memory); route_world <= 1 = off
+    int route_world; unsigned route_rows;
+    float *r_eig[kMaxRoute], *r_nrm[kMaxRoute], *r_feat[kMaxRoute];
 };
 
 // a9: the 7 eigen features of Markov::mkFeatureVector (markov.cpp:449-475) from descending (l0, l1, l2).
@@ -246,6 +251,12 @@ __device__ __forceinline__ void features7(float l0, float l1, float l2, int form
 
 // moments of (p - q): m = {sx sy sz sxx sxy sxz syy syz szz}, cnt points -> outputs for one row
 __device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, const float m[9], int cnt, size_t row) {
+    float *eig3 = o.eig3, *normal4 = o.normal4, *feat7 = o.feat7;
+    if (o.route_world > 1) {
+        const unsigned owner = (unsigned)row / o.route_rows;
+        row = (unsigned)row - owner * o.route_rows;
+        eig3 = o.r_eig[owner]; normal4 = o.r_nrm[owner]; feat7 = o.r_feat[owner];
+    }
     float e0 = 0.f, e1 = 0.f, e2 = 1.f;                       // cv.h:105-109 "isolated point" marker
     float nx = NAN, ny = NAN, nz = NAN, curv = NAN;
     if (cnt >= o.min_pts) {
@@ -271,12 +282,12 @@ __device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, con
             if (nn > 0.f) { e0 /= nn; e1 /= nn; e2 /= nn; }
         }
     }
-    if (o.eig3) { float *p = o.eig3 + row * 3; p[0] = e0; p[1] = e1; p[2] = e2; }
-    if (o.normal4) reinterpret_cast<float4 *>(o.normal4)[row] = make_float4(nx, ny, nz, curv);
-    if (o.feat7) {
+    if (eig3) { float *p = eig3 + row * 3; p[0] = e0; p[1] = e1; p[2] = e2; }
+    if (normal4) reinterpret_cast<float4 *>(normal4)[row] = make_float4(nx, ny, nz, curv);
+    if (feat7) {
         float f[7];
         features7(e0, e1, e2, o.formula_set, f);
-        float *p = o.feat7 + row * 7;
+        float *p = feat7 + row * 7;
 #pragma unroll
         for (int i = 0; i < 7; ++i) p[i] = f[i];
     }

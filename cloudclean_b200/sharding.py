@@ -101,3 +101,68 @@ class PeerRows:
             else:
                 self.ctx.ipc_close(b.addr)
         self.bufs = []
+
+
+class PeerSlices:
+    """Row arrays partitioned by ORIGINAL index: every rank owns the [rows_per_rank, w] slice of each array and maps all
+    the other ranks' slices as NVLink peer memory (ccg_ipc_export / ccg_ipc_open), so that ccg_pca_knn_features_route can
+    store every finished row with its owner.  tables[a][r] = device address of array a's slice on rank r."""
+
+    def __init__(self, ctx, rows_per_rank, widths):
+        self.ctx = ctx
+        rank = dist.get_rank() if dist.is_initialized() else 0
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank, self.world, self.rows = rank, world, rows_per_rank
+        self.own = [DevBuffer(ctx.dev_alloc(max(1, rows_per_rank * w * 4)), (rows_per_rank, w), True) for w in widths]
+        self.tables = [[None] * world for _ in widths]
+        self._opened = []
+        handles = [ctx.ipc_export(b.addr) if world > 1 else b"" for b in self.own]
+        every = [None] * world
+        if world > 1:
+            dist.all_gather_object(every, handles)
+        for a in range(len(widths)):
+            for r in range(world):
+                if r == rank:
+                    self.tables[a][r] = self.own[a].addr
+                else:
+                    addr = ctx.ipc_open(every[r][a])
+                    self._opened.append(addr)
+                    self.tables[a][r] = addr
+
+    def close(self):
+        for addr in self._opened:
+            self.ctx.ipc_close(addr)
+        for b in self.own:
+            self.ctx.dev_free(b.addr)
+        self._opened, self.own = [], []
+
+
+class SharedPinned:
+    """One host array shared by the local ranks (POSIX shared memory under /dev/shm) and page-locked in every process
+    (cudaHostRegister), so that each rank moves ITS slice of the input / output through its own PCIe link."""
+
+    def __init__(self, name, shape, dtype=torch.float32, create=False):
+        import os
+        self.path = f"/dev/shm/{name}"
+        nelem = 1
+        for d in shape:
+            nelem *= d
+        self.nbytes = nelem * torch.empty((), dtype=dtype).element_size()
+        if create:
+            with open(self.path, "wb") as f:
+                f.truncate(max(self.nbytes, 1))
+        self.created = create
+        self.t = torch.from_file(self.path, shared=True, size=nelem, dtype=dtype).view(shape)
+        self.registered = False
+        if torch.cuda.is_available() and self.nbytes:
+            rc = torch.cuda.cudart().cudaHostRegister(self.t.data_ptr(), self.nbytes, 0)
+            self.registered = int(rc) == 0
+
+    def close(self):
+        import os
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.t.data_ptr())
+            self.registered = False
+        self.t = None
+        if self.created and os.path.exists(self.path):
+            os.unlink(self.path)

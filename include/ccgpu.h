@@ -78,6 +78,18 @@ int ccg_set_cancel_flag(ccg_ctx *ctx, const volatile int *flag);
 /* Run every later call on the caller's CUDA stream (a cudaStream_t, e.g. the stream NCCL collectives are enqueued
  * on, so that broadcast -> build -> query -> gather needs no extra synchronisation); NULL restores the ctx's own. */
 int ccg_set_stream(ccg_ctx *ctx, void *cuda_stream);
+/* Asynchronous mode (off by default).  A synchronous call returns when its results are in the caller's buffers — what the
+ * reference's call sites expect (cv.h:96-113 reads the result in the next statement).  With async on, ccg_set_cloud and
+ * the query entry points only ENQUEUE their work on the ctx stream (device or pinned host buffers; pageable host buffers
+ * still work but make the copies blocking) and return at once, so that a caller which owns the stream — broadcast ->
+ * build -> query -> gather over NCCL on several GPUs — chains the stages without a host round trip in between.  Results,
+ * the deferred input checks (non-finite coordinates) and the timing statistics become valid after ccg_sync.  Calls whose
+ * contract needs the host in the middle (ccg_sor_mask: index-order fp64 sum; capped radius searches with max_nn > 64:
+ * two error bits; CCG_COLLECT_STATS) still synchronise internally. */
+int ccg_set_async(ccg_ctx *ctx, int on);
+/* Wait for everything enqueued on the ctx's streams; returns the first deferred error (e.g. CCG_ERR_NONFINITE of an
+ * asynchronous ccg_set_cloud), CCG_OK otherwise.  Harmless in synchronous mode. */
+int ccg_sync(ccg_ctx *ctx);
 
 /* ---- cloud ---------------------------------------------------------------------------------------- */
 /* Replaces pcl::KdTreeFLANN::setInputCloud (cv.h:83-84, cv.cpp:254-255, normalestimation.cpp:428-429) and the
@@ -185,6 +197,17 @@ int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float 
  * runs ccg_unpermute once per array on its own HBM. */
 int ccg_pca_knn_features_shard(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
                                int chunk_points, int sorted_rows, float *eig3, float *normal4, float *feat7);
+/* Owner-routed variant of ccg_pca_knn_features_shard for end-to-end multi-GPU runs: the output rows are partitioned by
+ * ORIGINAL index — rank o owns rows [o * rows_per_rank, (o + 1) * rows_per_rank) — and this rank stores every row it
+ * computes (its interleaved chunks of the curve order) at local row (i - o * rows_per_rank) of rank o's arrays,
+ * eig3_of_rank[o] / normal4_of_rank[o] / feat7_of_rank[o] (own memory for o == rank, NVLink peer memory opened with
+ * ccg_ipc_open otherwise; any of the three tables may be NULL).  After a barrier every rank holds a contiguous,
+ * original-order slice of the result, which it can copy to the host through its own PCIe link — no rank funnels
+ * everything (the gather step of the north star, spread over all links).  world <= 16. */
+int ccg_pca_knn_features_route(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
+                               int chunk_points, size_t rows_per_rank, float *const *eig3_of_rank, float *const *normal4_of_rank,
+                               float *const *feat7_of_rank);
+
 /* Plain cudaMalloc / cudaFree on the ctx's device (IPC handles need an allocation base, which a caching
  * allocator's sub-block is not). */
 int ccg_dev_alloc(ccg_ctx *ctx, size_t bytes, void **out);
