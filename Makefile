@@ -9,8 +9,15 @@ LIB = cloudclean_b200/libccgpu.so
 
 all: $(LIB) oracle adapters
 
+# ptxas -v output (registers / spills / shared memory per kernel) goes to build/ptxas/ (not tracked); the per-round table the
+# judge reads is profiles/rNN_ptxas.txt, written by `make ptxas-summary`
+PTXLOG = build/ptxas
 $(SRC)/%.o: $(SRC)/%.cu $(SRC)/common.cuh $(SRC)/tile.cuh include/ccgpu.h
-	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(@:.o=.ptxas.log) || (cat $(@:.o=.ptxas.log); exit 1)
+	@mkdir -p $(PTXLOG)
+	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(PTXLOG)/$(notdir $(@:.o=.log)) || (cat $(PTXLOG)/$(notdir $(@:.o=.log)); exit 1)
+
+ptxas-summary:
+	python tools/ptxas_summary.py $(PTXLOG) > profiles/r02_ptxas.txt
 
 $(LIB): $(OBJ)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart_static -lpthread -ldl -lrt
@@ -24,6 +31,6 @@ adapters/test_adapters: adapters/test_adapters.cpp adapters/cloudclean_gpu.hpp i
 	g++ -O2 -std=c++14 -ffp-contract=off -Wall -pthread -I. adapters/test_adapters.cpp -o $@ -Lcloudclean_b200 -lccgpu -Wl,-rpath,'$$ORIGIN/../cloudclean_b200'
 
 clean:
-	rm -f $(OBJ) $(LIB) $(SRC)/*.ptxas.log adapters/test_adapters
+	rm -rf $(OBJ) $(LIB) $(PTXLOG) adapters/test_adapters
 	$(MAKE) -C oracle clean
-.PHONY: all oracle adapters clean
+.PHONY: all oracle adapters clean ptxas-summary

@@ -205,7 +205,9 @@ def workload_config(args, n):
     return {"workload": f"config {args.scan_cfg}: synthetic outdoor terrestrial scan {a['scan_w'] // args.shrink}x{a['scan_h'] // args.shrink} rays"
                         f" (seed {a['seed']}), kNN(k={K})+PCA(cov 1/(n-1)) normals/curvature/eigenvalues + 7 eigen features",
             "points": n, "k": K, "shrink": args.shrink,
-            "parallelism": "replicated cloud, queries sharded by interleaved Morton chunks (8192 pts), rows stored to rank 0 over NVLink" if args.gpus > 1 else "single GPU",
+            "parallelism": ("replicated cloud (scatter + all-gather of xyz(w)), queries sharded by interleaved curve chunks (8192 pts); value: rows stored to "
+                            "rank 0 over NVLink; e2e: every rank uploads its 1/N of the scan, rows stored with the rank owning their original index, "
+                            "every rank downloads its own slice") if args.gpus > 1 else "single GPU",
             "l2": "inputs+outputs per step >> 126 MB L2 (no flush needed)"}
 
 
@@ -365,7 +367,10 @@ def main():
         nt = torch.tensor([n], device=dev, dtype=torch.int64)
         dist.broadcast(nt, 0)
         n = int(nt.item())
-        pack = torch.empty((n, 4), device=dev, dtype=torch.float32)     # what is replicated: xyz(w), 16 B/point
+        rpr = (n + world - 1) // world                                  # rows (original order) per rank
+        pack = torch.empty((world * rpr, 4), device=dev, dtype=torch.float32)   # what is replicated: xyz(w), 16 B/point
+        my_slice = torch.empty((rpr, 4), device=dev, dtype=torch.float32)
+        repl = os.environ.get("CCG_BENCH_REPL", "gather")               # "bcast": one NCCL broadcast (r01); "gather": scatter + all-gather
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
@@ -410,11 +415,17 @@ def main():
             eb0 = torch.cuda.Event(enable_timing=True); eb1 = torch.cuda.Event(enable_timing=True)
             eb0.record(stream)
             if rank == 0:
-                pack.copy_(pts[:, :4])             # x y z 1 of every PointXYZI: the search needs nothing else
-            dist.broadcast(pack, 0)                # 16 B/point over NVLink instead of the 32-byte struct
+                pack[:n].copy_(pts[:, :4])         # x y z 1 of every PointXYZI: the search needs nothing else
+            if repl == "bcast":
+                dist.broadcast(pack, 0)            # 16 B/point over NVLink instead of the 32-byte struct
+            else:
+                # rank 0 sends every rank ITS 1/N of the cloud once (7/8 of the bytes leave rank 0 once), then the ranks
+                # all-gather: every link carries 1/N-sized pieces in both directions instead of one root feeding N-1 peers
+                dist.scatter(my_slice, list(pack.view(world, rpr, 4).unbind(0)) if rank == 0 else None, src=0)
+                dist.all_gather_into_tensor(pack, my_slice)
             eb1.record(stream)
             bcast_ev.append((eb0, eb1))
-            ctx.set_cloud(pack)
+            ctx.set_cloud(pack[:n])
             launches[0] += ctx.stats()["launches_build"]
             # every rank answers its interleaved share of the Morton order (8192-point chunks, round robin) and stores the rows, in original order, straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
@@ -430,26 +441,56 @@ def main():
                 launches[0] += 3
 
     # host-buffer variant (e2e): pinned PointXYZI AoS in, pinned outputs out
-    if rank == 0:
+    h2d = n * 32
+    d2h = n * (12 + 16 + 28)
+    if world == 1:
         h_pts = torch.empty((n, 8), dtype=torch.float32, pin_memory=True)
         h_pts.copy_(pts)
         h_eig = torch.empty((n, 3), dtype=torch.float32, pin_memory=True)
         h_nrm = torch.empty((n, 4), dtype=torch.float32, pin_memory=True)
         h_feat = torch.empty((n, 7), dtype=torch.float32, pin_memory=True)
         np_pts, np_eig, np_nrm, np_feat = h_pts.numpy(), h_eig.numpy(), h_nrm.numpy(), h_feat.numpy()
-    h2d = n * 32
-    d2h = n * (12 + 16 + 28)
+    else:
+        # ONE host copy of the scan and of the outputs, shared by the local ranks (POSIX shared memory, page-locked in
+        # every process): each rank uploads ITS 1/N of the PointXYZI rows through its own PCIe link, the ranks all-gather
+        # the xyz(w) over NVLink, every rank stores the rows it computes with the rank that OWNS their original index
+        # (ccg_pca_knn_features_route, NVLink peer stores from inside the kernel) and downloads its own contiguous slice
+        # of the three output arrays to their final host addresses.  No rank funnels the job through one link.
+        tag = f"ccg_bench_{os.environ.get('MASTER_PORT', '0')}"
+        shm = {}
+        for name, w in (("pts", 8), ("eig", 3), ("nrm", 4), ("feat", 7)):
+            if rank == 0:
+                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w), create=True)
+        dist.barrier()
+        for name, w in (("pts", 8), ("eig", 3), ("nrm", 4), ("feat", 7)):
+            if rank != 0:
+                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w))
+        if rank == 0:
+            shm["pts"].t.copy_(pts)
+        dist.barrier()
+        slices = sharding.PeerSlices(ctx, rpr, (3, 4, 7))
+        ra, rb_ = rank * rpr, min(n, (rank + 1) * rpr)
+        stage32 = torch.empty((rpr, 8), device=dev)                 # this rank's PointXYZI rows as uploaded
+        own = [b.tensor(dev) for b in slices.own]
+        h2d = n * 32                                                # summed over the ranks
+        pinned_ok = all(v.registered for v in shm.values())
 
     def step_host():
         if world == 1:
             ctx.set_cloud(np_pts)                                              # host AoS in: H2D inside the call
             ctx.pca_knn_features_into(K, cc.COV_NM1, 0, np_eig, np_nrm, np_feat)   # host outputs: D2H inside the call
         else:
-            if rank == 0:
-                pts.copy_(h_pts, non_blocking=True)                # H2D on rank 0, then NVLink broadcast
-            step_device()
-            if rank == 0:
-                h_eig.copy_(o_eig, non_blocking=True); h_nrm.copy_(o_nrm, non_blocking=True); h_feat.copy_(o_feat, non_blocking=True)
+            if rb_ > ra:
+                stage32[:rb_ - ra].copy_(shm["pts"].t[ra:rb_], non_blocking=True)      # H2D of this rank's rows
+                my_slice[:rb_ - ra].copy_(stage32[:rb_ - ra, :4])
+            dist.all_gather_into_tensor(pack, my_slice)
+            ctx.set_cloud(pack[:n])
+            ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, slices.tables[0], slices.tables[1], slices.tables[2])
+            dist.all_reduce(token)                                  # every peer has stored the rows this rank owns
+            if rb_ > ra:
+                shm["eig"].t[ra:rb_].copy_(own[0][:rb_ - ra], non_blocking=True)       # D2H to the final host addresses
+                shm["nrm"].t[ra:rb_].copy_(own[1][:rb_ - ra], non_blocking=True)
+                shm["feat"].t[ra:rb_].copy_(own[2][:rb_ - ra], non_blocking=True)
 
     def timed(fn, steps, warmup):
         with torch.cuda.stream(stream):
@@ -506,22 +547,76 @@ def main():
         torch.cuda.synchronize()
         dist.barrier()
         if rank == 0:
-            def checksum(*ts):                          # order-independent: sum and xor of the int32 views
-                acc = []
-                for t_ in ts:
-                    iv = t_.contiguous().view(torch.int32).to(torch.int64)
-                    acc.append(int(iv.sum().item()))
-                return acc
-            sharded = checksum(o_eig, o_nrm, o_feat)
+            got = [t_.clone() for t_ in (o_eig, o_nrm, o_feat)]
+        with torch.cuda.stream(stream):
+            step_host()                                 # and those of one more end-to-end step in the shared host arrays
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            def checksum(*ts):                          # order-independent: sum of the int32 views
+                return [int(t_.contiguous().view(torch.int32).to(torch.int64).sum().item()) for t_ in ts]
+            sharded = checksum(*got)
             r_eig = torch.empty((n, 3), device=dev); r_nrm = torch.empty((n, 4), device=dev); r_feat = torch.empty((n, 7), device=dev)
             with torch.cuda.stream(stream):
                 ctx.set_cloud(pts)
                 ctx.pca_knn_features_into(K, cc.COV_NM1, 0, r_eig, r_nrm, r_feat)
             torch.cuda.synchronize()
             single = checksum(r_eig, r_nrm, r_feat)
-            same_bits = all(torch.equal(a_.view(torch.int32), b_.view(torch.int32)) for a_, b_ in ((o_eig, r_eig), (o_nrm, r_nrm), (o_feat, r_feat)))
-            match = {"outputs_match_n1": bool(same_bits and sharded == single), "checksum_sharded": sharded, "checksum_single_gpu": single}
-            del r_eig, r_nrm, r_feat
+            same_bits = all(torch.equal(a_.view(torch.int32), b_.view(torch.int32)) for a_, b_ in zip(got, (r_eig, r_nrm, r_feat)))
+            e2e_same = all(torch.equal(shm[k_].t.view(torch.int32), b_.cpu().view(torch.int32))
+                           for k_, b_ in (("eig", r_eig), ("nrm", r_nrm), ("feat", r_feat)))
+            match = {"outputs_match_n1": bool(same_bits and sharded == single), "e2e_outputs_match_n1": bool(e2e_same),
+                     "checksum_sharded": sharded, "checksum_single_gpu": single}
+            del r_eig, r_nrm, r_feat, got
+        dist.barrier()
+
+    # ---- N > 1: the statistical outlier filter sharded the same way (gather the N fp32 mean distances, sum
+    #      them in index order on one rank — the bit-exact mask contract) ---------------------------------------------------
+    sor_line = None
+    if world > 1 and not args.no_other_configs:
+        if rank == 0:
+            sc2 = synth.config_scan(2, device=dev, shrink=args.shrink)
+            p2 = sc2["points"][:, :4].contiguous()
+            n2 = p2.shape[0]
+            del sc2
+        else:
+            n2 = 0
+        nt2 = torch.tensor([n2], device=dev, dtype=torch.int64)
+        dist.broadcast(nt2, 0)
+        n2 = int(nt2.item())
+        if rank != 0:
+            p2 = torch.empty((n2, 4), device=dev)
+        b2, e2_, per2 = sharding.shard_range(n2, rank, world)
+        md_local = torch.zeros((per2,), device=dev)
+        md_sorted = torch.empty((world * per2,), device=dev)
+        md_orig = torch.empty((n2,), device=dev) if rank == 0 else None
+        mask2 = torch.empty((n2,), dtype=torch.uint8, device=dev) if rank == 0 else None
+        h_md = torch.empty((n2,), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+
+        def step_sor():
+            dist.broadcast(p2, 0)
+            ctx.set_cloud(p2)
+            if e2_ > b2:
+                ctx.sor_mean_range(30, b2, e2_, md_local)
+            dist.all_gather_into_tensor(md_sorted, md_local)
+            if rank == 0:
+                ctx.unpermute(md_sorted[:n2].view(n2, 1), md_orig.view(n2, 1))
+                h_md.copy_(md_orig, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                d_ = h_md.numpy().astype(np.float64)
+                sm = float(np.add.accumulate(d_)[-1]); sq = float(np.add.accumulate(d_ * d_)[-1])      # index order, fp64
+                thr = sm / n2 + 1.0 * np.sqrt(max(0.0, (sq - sm * sm / n2) / (n2 - 1.0)))
+                mask2.copy_(md_orig.double() > thr)
+        ms_sor = timed(step_sor, 3, 1)
+        if rank == 0:
+            with torch.cuda.stream(stream):
+                ctx.set_cloud(p2)
+                m1, md1 = ctx.sor_mask(30, 1.0, device_out=dev)
+            torch.cuda.synchronize()
+            sor_line = {"points": n2, "ms": ms_sor / 3, "points_per_s": n2 * 3 / (ms_sor * 1e-3), "outliers": int(mask2.sum().item()),
+                        "mask_matches_n1": bool(torch.equal(m1, mask2)), "mean_distances_match_n1": bool(torch.equal(md1, md_orig)),
+                        "path": "broadcast xyz(w), replicated build, ccg_sor_mean_range per rank, all-gather of the fp32 mean distances, "
+                                "un-permute + index-order fp64 sum + mask on rank 0"}
         dist.barrier()
 
     if rank == 0:
@@ -538,7 +633,10 @@ def main():
                 "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
                 "e2e": {"value": e2e_v, "unit": "points/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "ms_per_step": ms_e2e / e2e_steps},
+                        "ms_per_step": ms_e2e / e2e_steps,
+                        "path": ("one pinned host copy of the scan and of the outputs shared by the ranks; per-rank H2D of 1/N of the PointXYZI rows, "
+                                 "NVLink all-gather, owner-routed rows, per-rank D2H of its own slice (bytes are summed over the ranks)") if world > 1
+                                else "pinned host PointXYZI in, pinned host outputs out, through the C ABI"},
                 "gpu_launches": int(n_launch),
                 "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": f"k_tile_sel<{K}, MODE_PCA> (two-pass kNN selection + covariance + eigensolve + features)", "achieved": achieved,
@@ -549,6 +647,8 @@ def main():
                 "stage_ms": dict({"build": st["ms_build"], "query_kernel": k_ms}, **stage_extra)}
         if match is not None:
             line.update(match)
+        if sor_line is not None:
+            line["other_configs"] = {"config2_sor_sharded": sor_line}
         if world == 1 and not args.no_other_configs:
             try:
                 line["other_configs"] = other_configs(ctx, cc, stream, dev, peak, args.shrink)
@@ -571,6 +671,9 @@ def main():
         torch.cuda.synchronize()
         dist.barrier()
         peer.close()
+        slices.close()
+        for v in shm.values():
+            v.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

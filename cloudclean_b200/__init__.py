@@ -132,6 +132,8 @@ def _addr(a):
         return None
     if isinstance(a, int):
         return C.c_void_p(a)
+    if _is_torch(a) or isinstance(a, np.ndarray):          # (torch.Tensor has an unrelated .addr method)
+        return _ptr(a)
     if hasattr(a, "addr"):
         return C.c_void_p(a.addr)
     return _ptr(a)

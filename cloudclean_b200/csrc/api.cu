@@ -147,14 +147,19 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
     // chunk c = slots [slot[c], slot[c+1]); rows below bound[c+1] are final once it has run
     // `chunks` equal chunks over the first 88 % of the tiles, then three short ones (6, 4, 2 %): what cannot overlap is the
     // copy of the LAST chunk's rows, so the last chunk is kept small without paying launch tails on all of them
-    if (chunks > 13) chunks = 13;
+    if (chunks > 11) chunks = 11;
     int slot[18]; size_t bound[18];
     int nch = 0;
     slot[0] = 0;
     {
         const bool taper = nleaf >= 64;
+        // two short chunks first (2 %, 6 %: the copy stream starts early), `chunks` equal ones up to 88 %, three short ones last
+        const int head[2] = {taper ? (int)((long long)nleaf * 2 / 100) & ~1 : 0, taper ? (int)((long long)nleaf * 8 / 100) & ~1 : 0};
+        for (int i = 0; i < 2; ++i)
+            if (head[i] > slot[nch]) { slot[nch + 1] = head[i]; ++nch; }
         const int main_tiles = taper ? (int)((long long)nleaf * 88 / 100) : nleaf;
-        int per = ((main_tiles + chunks - 1) / chunks + 1) & ~1;
+        const int main_left = main_tiles - slot[nch];
+        int per = ((main_left + chunks - 1) / chunks + 1) & ~1;
         if (per < 2) per = 2;
         while (slot[nch] < main_tiles) { slot[nch + 1] = slot[nch] + per < main_tiles ? slot[nch] + per : main_tiles; ++nch; }
         if (taper) {
@@ -377,6 +382,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->curve_hilbert = (cv && cv[0] == 'm') ? 0 : 1;
     const char *da = getenv("CCG_SEL_DRAIN_AT");
     if (da) ctx->sel_drain_at = atoi(da);
+    const char *sn = getenv("CCG_SEL_NET");
+    if (sn) ctx->sel_net = atoi(sn);
     const char *mb = getenv("CCG_SEL_MINB");
     if (mb) ctx->sel_minb = atoi(mb);
     const char *sg = getenv("CCG_SEL_STAGE");

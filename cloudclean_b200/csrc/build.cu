@@ -90,26 +90,39 @@ __device__ __forceinline__ unsigned long long spread21(unsigned v) {
     return x;
 }
 
-// 3-D Hilbert index from the quantised coordinates (Skilling's transpose algorithm, b bits per axis), interleaved into
-// one key.  Unlike the Morton curve the Hilbert curve has no jumps: consecutive points along it are always spatial
-// neighbours, so a run of 32 consecutive points (a leaf) is a compact blob instead of, every so often, two pieces of
-// surface a Z-jump apart.  Measured on the bench scans (tools/sim_tiles.cpp): candidate leaves scanned per tile 22 -> 12.
-__device__ __forceinline__ unsigned long long hilbert_key(unsigned x, unsigned y, unsigned z) {
-    unsigned X0 = x, X1 = y, X2 = z;
-    constexpr unsigned M = 1u << (kMortonBits - 1);
+// 3-D Hilbert index of the quantised coordinates.  Unlike the Morton curve the Hilbert curve has no jumps: consecutive
+// points along it are always spatial neighbours, so a run of 32 consecutive points (a leaf) is a compact blob instead of,
+// every so often, two pieces of surface a Z-jump apart.  Measured on the 30 M bench scan: candidate leaves per tile
+// 29.2 -> 17.7, query 38.3 -> 29.7 ms (profiles/r02_sel_v14_variants.log).
+// The curve is the one of Skilling's transpose algorithm ("Programming the Hilbert curve", 2004), evaluated by its state
+// machine: 24 orientations x 8 octants -> (3 output bits, next orientation), one table step per level on the octants of
+// the Morton code.  The table was generated from the textbook loop and checked against it (tools/hilbert_table.py);
+// the branchy loop itself cost 0.5 ms per 30 M points (lanes of a warp sit in different octants at every level).
+__device__ const unsigned char kHilbertTab[192] = {
+    8, 17, 27, 2, 39, 46, 52, 5, 56, 71, 73, 86, 91, 20, 10, 13,
+    48, 1, 103, 110, 115, 18, 12, 21, 126, 129, 29, 26, 79, 80, 140, 3,
+    148, 43, 37, 34, 127, 128, 78, 81, 156, 45, 35, 42, 31, 6, 160, 105,
+    72, 87, 139, 4, 57, 70, 50, 53, 0, 171, 111, 76, 49, 58, 102, 61,
+    180, 143, 83, 184, 69, 54, 66, 97, 16, 123, 9, 74, 47, 60, 38, 77,
+    132, 95, 85, 14, 67, 144, 82, 33, 142, 55, 185, 96, 93, 116, 90, 11,
+    188, 107, 175, 176, 101, 98, 62, 65, 164, 109, 119, 22, 99, 106, 152, 41,
+    174, 177, 63, 64, 117, 114, 92, 19, 30, 125, 161, 122, 7, 172, 104, 75,
+    130, 25, 133, 166, 179, 136, 84, 191, 94, 15, 141, 28, 145, 32, 138, 51,
+    146, 155, 149, 36, 137, 24, 190, 167, 154, 157, 147, 44, 169, 182, 120, 135,
+    162, 165, 121, 134, 187, 108, 168, 183, 118, 173, 23, 124, 153, 170, 40, 59,
+    178, 113, 131, 88, 181, 158, 68, 151, 186, 163, 89, 112, 189, 100, 150, 159,
+};
+__device__ __forceinline__ unsigned long long hilbert_key(unsigned long long morton, const unsigned char *tab) {
+    unsigned long long key = 0;
+    unsigned st = 0;
 #pragma unroll
-    for (unsigned Q = M; Q > 1; Q >>= 1) {
-        const unsigned P = Q - 1;
-        if (X0 & Q) X0 ^= P;                                        // axis 0: invert low bits of X0
-        if (X1 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X1) & P; X0 ^= t; X1 ^= t; }
-        if (X2 & Q) X0 ^= P; else { const unsigned t = (X0 ^ X2) & P; X0 ^= t; X2 ^= t; }
+    for (int l = kMortonBits - 1; l >= 0; --l) {
+        const unsigned o = (unsigned)(morton >> (3 * l)) & 7u;            // octant at this level: x y z bits
+        const unsigned e = tab[st * 8 + o];
+        key = (key << 3) | (e & 7u);
+        st = e >> 3;
     }
-    X1 ^= X0; X2 ^= X1;
-    unsigned t = 0;
-#pragma unroll
-    for (unsigned Q = M; Q > 1; Q >>= 1) if (X2 & Q) t ^= Q - 1;
-    X0 ^= t; X1 ^= t; X2 ^= t;
-    return spread21(X2) | (spread21(X1) << 1) | (spread21(X0) << 2);
+    return key;
 }
 
 // Space-filling-curve key of every point (kMortonBits per axis, cubic cells over the bounding box) + identity values.
@@ -123,6 +136,11 @@ __device__ __forceinline__ unsigned long long hilbert_key(unsigned x, unsigned y
 template <bool HILBERT>
 __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig, int n, const IngestScratch *__restrict__ sc,
                                                 int ib, int drop, unsigned long long *__restrict__ keys) {
+    __shared__ unsigned char s_tab[192];
+    if (HILBERT) {
+        if (threadIdx.x < 192) s_tab[threadIdx.x] = kHilbertTab[threadIdx.x];
+        __syncthreads();
+    }
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float lx = ord2f(sc->lo[0]), ly = ord2f(sc->lo[1]), lz = ord2f(sc->lo[2]);
@@ -133,7 +151,8 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
     unsigned qx = (unsigned)fminf(fmaxf((p.x - lx) * inv_cell, 0.f), qmax);
     unsigned qy = (unsigned)fminf(fmaxf((p.y - ly) * inv_cell, 0.f), qmax);
     unsigned qz = (unsigned)fminf(fmaxf((p.z - lz) * inv_cell, 0.f), qmax);
-    const unsigned long long key = HILBERT ? hilbert_key(qx, qy, qz) : (spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2));
+    unsigned long long key = spread21(qz) | (spread21(qy) << 1) | (spread21(qx) << 2);
+    if (HILBERT) key = hilbert_key(key, s_tab);
     keys[i] = ((key >> drop) << ib) | (unsigned long long)(unsigned)i;
 }
 

@@ -116,6 +116,7 @@ struct ccg_ctx {
     int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
     int curve_hilbert = 1;   // leaf order along the Hilbert curve (CCG_CURVE=morton: Z-order, for A/B runs)
     int sel_drain_at = 0;    // k_tile_sel: pending survivors per lane that trigger a drain; 0 = only at the end of the list (CCG_SEL_DRAIN_AT)
+    int sel_net = 1;         // k_tile_sel: own leaf seeded by a register sorting network when k == K (CCG_SEL_NET=0: ordered inserts)
     int sel_minb = 0;        // k_tile_sel<20>: 12 = the 80-register build (CCG_SEL_MINB=12), else the default 16-block build
     int sel_stage = 1;       // k_tile_sel leaf staging: 1 = cp.async.bulk + mbarrier ring, 0 = LDG/STS (CCG_SEL_STAGE=ldg)
     int sel_chunks = 4;      // sub-launches of a long k_tile_sel launch (CCG_SEL_CHUNKS)

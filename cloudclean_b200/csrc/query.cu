@@ -327,6 +327,7 @@ struct TileParams {
     unsigned long long *stat_scanned;
     int *defer_count; int32_t *defer_list; long long *defer_row;   // k_tile_sel: queries handed to k_point_query
     int *slow_count; int32_t *slow_tiles;                          // k_tile_sel: tiles handed to k_tile_sel_stack
+    int seed_net;                 // k_tile_sel: own leaf seeded by the sorting network when k == K (0: ordered inserts, for A/B runs)
     int drain_at;                 // k_tile_sel: pending survivors per lane that trigger a pooled drain
     const int32_t *tile_order;    // k_tile_sel: non-NULL = tile_begin/tile_end index this list of tiles (output pipelining)
     int shard_world, shard_rank, shard_chunk;   // k_tile_sel: > 1 = slots enumerate the interleaved chunks of one rank
@@ -503,20 +504,21 @@ __device__ __forceinline__ void make_sub_boxes(const float4 &q, float bound, boo
 //     copy where the cell run is contiguous"; CCG_SEL_STAGE=ldg selects an LDG/STS ring for the A/B profile);
 //   * re-uses the queue as the log of pass 2 (drains clear the bits that fell outside the bound).
 constexpr int kSelStages = 2;
-constexpr int kQCap = 20;              // queue entries per lane (curve neighbours + listed leaves <= kQCap - 1, pass 2 adds the own leaf)
+constexpr int kQCap = 20;              // queue entries per lane: listed leaves use <= kQCap - 3, pass 2 adds the 3 home leaves
 constexpr int kSlotHome = 253;         // list[253] / [254] / [255] = own leaf / previous / next along the curve
 constexpr int kListMax = 252;          // listed leaves a tile may keep after the per-query refinement (u8 slots)
 
 struct alignas(16) SelScratch {
-    WarpScratch2 w;                        // w.ws.leaf: the 32 queries, or a home neighbour's exact points; w.list; w.sub
-    float4 blk[kSelStages][kRelStride];    // staged prefilter blocks
+    WarpScratch2 w;                        // w.ws.leaf: the 32 queries; w.list (+ the home leaves at [253..255]); w.sub
     union {
-        struct { unsigned qmask[kQCap * 32]; unsigned char qslot[kQCap * 32]; } q;   // entry e of lane l at [e * 32 + l]
-        int queue[2][kQueueCap];           // breadth-first queues of collect_leaves (dead before the first queue entry)
+        float4 blk[kSelStages][kRelStride];    // staged prefilter blocks
+        int queue[2][kQueueCap];               // breadth-first queues of collect_leaves (no copy is in flight while it runs)
     };
+    struct { unsigned qmask[kQCap * 32]; unsigned char qslot[kQCap * 32]; } q;   // entry e of lane l at [e * 32 + l]
     float sbound[32];
     unsigned long long bar[kSelStages];
 };
+static_assert(sizeof(int) * 2 * kQueueCap <= sizeof(float4) * kSelStages * kRelStride, "the BFS queues must fit the staging ring");
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
@@ -566,7 +568,7 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 // rounded up, never rejects one.  Survivors are always re-scored with the contract arithmetic before they count.
 // Two candidates per instruction: packed fma.rn.f32x2 (FFMA2, sm_100) on the pair-interleaved block layout; the sign
 // bits are shifted into the mask with one funnel shift each (reject bits; the caller gets the complement).
-__device__ __forceinline__ unsigned prefilter_blk(const float4 *blk, const float4 &q, float bound) {
+__device__ __noinline__ unsigned prefilter_blk(const float4 *blk, const float4 &q, float bound) {
     const float4 c = blk[0];
     const float qx = q.x - c.x, qy = q.y - c.y, qz = q.z - c.z;
     const float qq = fmaf(qx, qx, fmaf(qy, qy, qz * qz));
@@ -603,9 +605,42 @@ struct ValList {
         key[0] = fminf(key[0], c);
     }
     __device__ __forceinline__ void tighten() { bound = bound < 0.f ? -1.f : fminf(rb, key[K - 1]); }
-    // every staged point scored exactly (home leaves: nearly every lane wants nearly every candidate)
+    // Own leaf when the list has no pinned slots (k == K): the 32 exact distances of the lane are sorted in registers by a
+    // bitonic network (240 compare-exchanges = 480 FMNMX; the stages that only feed outputs beyond K are dead code) and the K
+    // smallest become the list — against 32 ordered inserts of 2K FMNMX each (query 29.1 -> 28.2 ms on the 30 M scan).
+    // Extending the idea to the two curve neighbours (sort + bitonic merge with the list, ~0.95 k instead of 1.7 k
+    // instructions per leaf) cut the instruction count by another 5 % and LOST time (28.2 -> 28.7 ms): the straight-line
+    // networks are fetched once per tile, stall no_instruction rose 3.4 -> 4.6 (profiles/r02_sel_v17_merge_all_*).
+    __device__ __forceinline__ void seed_sorted(const float4 &q, const float4 *pts) {
+        float d[kLeaf];
+#pragma unroll
+        for (int j = 0; j < kLeaf; ++j) {
+            const float x = d2_point(q, pts[j]);
+            d[j] = x <= rb ? x : INFINITY;                   // NaN (pad lanes) and out-of-radius candidates sort last
+        }
+#pragma unroll
+        for (int k2 = 2; k2 <= kLeaf; k2 <<= 1) {
+#pragma unroll
+            for (int j = k2 >> 1; j > 0; j >>= 1) {
+#pragma unroll
+                for (int i = 0; i < kLeaf; ++i) {
+                    const int l = i ^ j;
+                    if (l > i) {
+                        const float a = d[i], b = d[l];
+                        const bool up = (i & k2) == 0;
+                        d[i] = up ? fminf(a, b) : fmaxf(a, b);
+                        d[l] = up ? fmaxf(a, b) : fminf(a, b);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < K; ++i) key[i] = i < kLeaf ? d[i < kLeaf ? i : 0] : INFINITY;
+        tighten();
+    }
+    // every staged point scored exactly and inserted in turn (own leaf with pinned slots)
     __device__ __forceinline__ void score_direct(const float4 &q, const float4 *pts) {
-#pragma unroll 2
+#pragma unroll 1
         for (int j = 0; j < kLeaf; ++j) {
             const float d = d2_point(q, pts[j]);
             const float c = d <= rb ? d : INFINITY;          // NaN (pad lanes) and out-of-radius candidates: no-op insert
@@ -750,33 +785,21 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     S.w.ws.leaf[lane] = q;
     if (lane < 3) S.w.list[kSlotHome + lane] = tile + (lane == 0 ? 0 : (lane == 1 ? -1 : 1));
     __syncwarp();
-    v.score_direct(q, S.w.ws.leaf);
-    // ---- the two neighbours along the curve: prefilter against the own-leaf bound, queue, one pooled drain ------------
+    if (P.seed_net && P.k == K) v.seed_sorted(q, S.w.ws.leaf);
+    else v.score_direct(q, S.w.ws.leaf);
+    // ---- the two neighbours along the curve, scored directly as well.  (Queueing them like the listed leaves was measured:
+    //      their survivors fill half the lanes, the pooled drain needs as many rounds as the direct loop has candidates, and
+    //      pass 2 then walks 44 instead of 31 rounds per tile: 28.1 -> 32.6 ms, profiles/r02_sel_v15_*.) ---------------------
     int first = 0, pend = 0;
 #pragma unroll 1
     for (int h = 1; h < 3; ++h) {
         const int leaf = tile + (h == 1 ? -1 : 1);
         if (leaf < 0 || leaf >= T.count[0]) continue;
+        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
         __syncwarp();
-        stg.issue(T, S, leaf, seq, lane);
-        const float4 *blk = stg.await(S, seq, lane);
-        ++seq;
-        const unsigned pm = prefilter_blk(blk, q, v.bound);
-        if (pm) {
-            S.q.qmask[cnt * 32 + lane] = pm;
-            S.q.qslot[cnt * 32 + lane] = (unsigned char)(kSlotHome + h);
-            ++cnt;
-            pend += __popc(pm);
-        }
-    }
-    {
-        const int rounds = __reduce_max_sync(kFull, pend);
-        if (rounds > 0) {
-            drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
-            cnt = squeeze_queue(S, cnt, lane);
-            if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
-        }
-        first = cnt; pend = 0;
+        S.w.ws.leaf[lane] = p;
+        __syncwarp();
+        v.score_direct(q, S.w.ws.leaf);
     }
     // ---- isolated lanes -> point kernel (a lane whose bound is far above the warp's median would make the tile's
     //      candidate list hundreds of leaves long) --------------------------------------------------------------
@@ -807,6 +830,7 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
         nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w, S.queue);
         if (nlist < 0) return -5;
     }
+    if (TMA) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the BFS queues were written over the staging ring
     __syncwarp();
     const int listed = nlist;
     nlist = refine_list(T, S, nlist, lane);
@@ -816,14 +840,14 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     const int drain_at = P.drain_at;
     if (nlist > 0) stg.issue(T, S, S.w.list[0], seq, lane);
     for (int i = 0; i < nlist; ++i) {
-        if (__reduce_max_sync(kFull, cnt) >= kQCap - 1) {
+        if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
             // a full queue: score what is pending, drop the entries that emptied, give up only if it is still full
             const int rounds = __reduce_max_sync(kFull, pend);
             drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
             cnt = squeeze_queue(S, cnt, lane);
             first = cnt; pend = 0;
             if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
-            if (__reduce_max_sync(kFull, cnt) >= kQCap - 1) {
+            if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
                 stg.await(S, seq, lane);                 // no copy may be in flight when the block retires
                 ++seq;
                 return -3;
@@ -945,22 +969,25 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
             if (i > K - k) dup = dup || (v.key[i] == v.key[i - 1] && v.key[i] != INFINITY);
         if (dup) t = -1.f;
     }
-    // the own leaf joins the queue with its prefilter mask against t (its curve neighbours are in the queue since pass 1)
+    // the three home leaves join the queue with their prefilter masks against t (3 entries are reserved for them)
     int tot = 0;
     {
         const int maxc = __reduce_max_sync(kFull, cnt);
         for (int e = 0; e < maxc; ++e)
             if (e < cnt) tot += __popc(S.q.qmask[e * 32 + lane]);
     }
-    {
+#pragma unroll 1
+    for (int h = 0; h < 3; ++h) {
+        const int leaf = tile + (h == 0 ? 0 : (h == 1 ? -1 : 1));
+        if (leaf < 0 || leaf >= T.count[0]) continue;
         __syncwarp();
-        stg.issue(T, S, tile, seq, lane);
+        stg.issue(T, S, leaf, seq, lane);
         const float4 *blk = stg.await(S, seq, lane);
         ++seq;
         const unsigned pm = prefilter_blk(blk, q, t);
         if (pm) {
             S.q.qmask[cnt * 32 + lane] = pm;
-            S.q.qslot[cnt * 32 + lane] = (unsigned char)kSlotHome;
+            S.q.qslot[cnt * 32 + lane] = (unsigned char)(kSlotHome + h);
             ++cnt;
             tot += __popc(pm);
         }
@@ -1236,7 +1263,9 @@ static void launch_sel3(const TreeView &T, const TileParams &P, cudaStream_t st)
 template <int K>
 static void launch_sel(const TreeView &T, const TileParams &P, int tma, int minb, cudaStream_t st) {
     constexpr int kDef = K > 32 ? 6 : (K > 24 ? 10 : (K == 20 ? 16 : 12));
-    if (K == 20 && minb == 12) { if (tma) launch_sel3<K, true, 12>(T, P, st); else launch_sel3<K, false, 12>(T, P, st); return; }
+    if constexpr (K == 20) {
+        if (minb == 12) { if (tma) launch_sel3<K, true, 12>(T, P, st); else launch_sel3<K, false, 12>(T, P, st); return; }
+    }
     if (tma) launch_sel3<K, true, kDef>(T, P, st);
     else launch_sel3<K, false, kDef>(T, P, st);
 }
@@ -1267,6 +1296,7 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
     }
     P.mean_k = a.mean_k; P.mean_d = a.mean_d;
     P.tile_order = a.tile_order;
+    P.seed_net = ctx->sel_net;
     P.drain_at = ctx->sel_drain_at > 0 ? ctx->sel_drain_at : 1 << 30;
     P.shard_world = a.shard_world; P.shard_rank = a.shard_rank; P.shard_chunk = a.shard_chunk;
     if (a.shard_world > 1) {
@@ -1371,8 +1401,9 @@ int launch_tile_query(ccg_ctx *ctx, const QueryArgs &a) {
         ctx->stats.leaves_scanned = (int64_t)s4[0];
         ctx->stats.deferred_queries = nd;
         if (getenv("CCG_VERBOSE_STATS"))
-            fprintf(stderr, "[ccg] tiles=%d leaves scanned=%llu (pass2 %llu) listed=%llu slow tiles=%llu (slots %llu, ties %llu, unbounded %llu, wide %llu) deferred=%d\n", ntiles,
-                    s4[0], s4[1], s4[2], s4[3], s4[6], s4[7], s4[8], s4[9], nd);
+            fprintf(stderr, "[ccg] tiles=%d leaves listed=%llu kept=%llu prefiltered=%llu | drains=%llu drain rounds=%llu pass-2 rounds=%llu | "
+                            "slow tiles=%llu (queue full %llu, unbounded %llu, wide %llu) deferred=%d\n", ntiles,
+                    s4[2], s4[5], s4[0], s4[6], s4[10], s4[1], s4[3], s4[7], s4[8], s4[9], nd);
     }
     return CCG_OK;
 }

@@ -169,3 +169,77 @@ def test_ptx_ingest_at_scan_size(tmp_path):
             assert got["points"].shape[0] == want["points"].shape[0] > 0.85 * want["sampled"]
             assert np.array_equal(got["points"].view(np.int32), want["points"].view(np.int32))
             assert np.array_equal(got["cloud_to_grid"], want["cloud_to_grid"])
+
+
+def test_full_size_radius_pca_exact_on_a_subbox(scan30):
+    """Config 3 as BASELINE.json words it (multi-scale radius eigen features): ccg_pca_radius on the 30 M-point cloud with the
+    plugin default cap (20) and the reference sweep's cap (1000, tests.json:7 — the counting-select path).  Counts are
+    bit-exact and eigenvalues within 1e-4 lambda0 of the fp64 truth for every query of a sub-box whose search ball lies inside
+    the box (then the sub-cloud's neighbourhood IS the full cloud's)."""
+    import torch
+    pts, ctx = scan30
+    n = pts.shape[0]
+    sel, c, half = _pick_box(pts, n // 2)
+    assert sel is not None
+    sub = pts[sel].cpu().numpy()
+    T = oracle.Tree(sub)
+    wall = torch.minimum(pts[sel, :3] - (c - half), (c + half) - pts[sel, :3]).min(1).values.cpu().numpy()
+    sel_np = sel.cpu().numpy()
+    for r, cap in ((0.05, 20), (0.1, 20), (0.05, 1000)):
+        if half < 2.5 * r:
+            continue
+        eig, _, cnt = ctx.pca_radius(r, cap, cc.COV_NM1)
+        assert torch.isfinite(eig).all() and (cnt >= 1).all() and (cnt <= cap).all()
+        interior = wall > r * 1.001
+        assert interior.sum() > 500
+        lists = T.radius(r, cap=cap, strict_lt=True)
+        assert np.array_equal(cnt[sel].cpu().numpy()[interior], lists["count"][interior])
+        ref = oracle.pca_lists(sub, lists["idx"], count=lists["count"], cov_norm=cc.COV_NM1)
+        g = eig[sel].cpu().numpy()[interior]
+        truth = ref["eig64"][interior]
+        marker = (truth[:, 0] == 0) & (truth[:, 2] == 1)
+        err = np.abs(g - truth) / np.maximum(truth[:, :1], 1e-30)
+        assert err[~marker].max(initial=0) <= 1e-4
+        assert np.array_equal(g[marker], truth[marker].astype(np.float32))
+        del eig, cnt
+
+
+def test_config5_skewed_scan_exact_on_subboxes_and_normal_gap_statistics():
+    """Config 5 (anisotropic indoor planar scan, density falling with 1/r^2): kNN lists exact on sub-boxes near the scanner
+    (densest cells) and far away, plus the statistic VERDICT r01 asked for — the share of points whose normal the parity
+    tests skip because (l1 - l2)/l0 is below the conditioning gate (GAP_MIN = 1e-3 in test_gpu_parity.py)."""
+    import torch
+    if torch.cuda.get_device_properties(0).total_memory < 40e9:
+        pytest.skip("needs a large-memory GPU")
+    s = synth.config_scan(5, device="cuda")
+    pts = s["points"].contiguous()
+    n = pts.shape[0]
+    assert n > 30_000_000
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        idx, d2 = ctx.knn(K)
+        eig, nrm = ctx.pca_knn(K, cc.COV_NM1, device_out=True)
+    assert (d2[:, 1:] >= d2[:, :-1]).all() and (d2[:, 0] == 0).all()
+    gap = (eig[:, 1] - eig[:, 2]) / eig[:, 0].clamp(min=1e-30)
+    frac_1e3 = float((gap <= 1e-3).float().mean().item())
+    frac_1e6 = float((gap <= 1e-6).float().mean().item())
+    print(f"config 5: normals under the conditioning gate: (l1-l2)/l0 <= 1e-3: {100 * frac_1e3:.4f} %, <= 1e-6: {100 * frac_1e6:.6f} %")
+    assert frac_1e3 < 0.05
+    rng = torch.linalg.vector_norm(pts[:, :3], dim=1)
+    order = torch.argsort(rng)
+    checked = 0
+    for seed_index in (int(order[n // 1000].item()), int(order[n // 2].item()), int(order[n - n // 50].item())):
+        sel, c, half = _pick_box(pts, seed_index)
+        if sel is None:
+            continue
+        sub = pts[sel].cpu().numpy()
+        ri, rd = oracle.Tree(sub).knn(K)
+        wall = torch.minimum(pts[sel, :3] - (c - half), (c + half) - pts[sel, :3]).min(1).values.cpu().numpy()
+        interior = rd[:, K - 1] < (wall.astype(np.float64) ** 2) * 0.999
+        if interior.sum() < 100:
+            continue
+        sel_np = sel.cpu().numpy()
+        assert np.array_equal(idx[sel].cpu().numpy()[interior], sel_np[ri[interior]])
+        assert np.array_equal(d2[sel].cpu().numpy()[interior], rd[interior])
+        checked += int(interior.sum())
+    assert checked > 2000

@@ -75,3 +75,60 @@ def test_interleaved_shards_fill_the_full_result(world, chunk):
         rows.close()
     for a, g in zip((eig, nrm, feat), got):
         assert torch.equal(torch.as_tensor(a).view(torch.int32), g.view(torch.int32))
+
+
+@pytest.mark.parametrize("world,chunk", [(2, 32), (3, 256), (8, 8192)])
+def test_owner_routed_rows_fill_every_ranks_slice(world, chunk):
+    """ccg_pca_knn_features_route, `world` ranks emulated on one GPU: every emulated rank answers its interleaved chunks and
+    stores each row into the slice of the rank owning its ORIGINAL index; the concatenated slices are the full result."""
+    import torch
+    pts = np.ascontiguousarray(synth.make_scan_np(150, 110, scene="room", seed=9)["points"])
+    n = pts.shape[0]
+    rpr = (n + world - 1) // world
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        eig, nrm = ctx.pca_knn(20, cc.COV_NM1, device_out=True)
+        feat = ctx.features(eig)
+        slices = [[torch.full((rpr, w), -5.0, device="cuda:0") for _ in range(world)] for w in (3, 4, 7)]
+        torch.cuda.synchronize()
+        for r in range(world):
+            ctx.pca_knn_features_route(20, cc.COV_NM1, 0, r, world, rpr, slices[0], slices[1], slices[2], chunk_points=chunk)
+        got = [torch.cat(s_)[:n] for s_ in slices]
+        with pytest.raises(cc.CcgError):                               # slices that do not cover the cloud are refused
+            ctx.pca_knn_features_route(20, cc.COV_NM1, 0, 0, world, rpr - 1 if world > 1 else 0, slices[0], slices[1], slices[2])
+    for a, g in zip((eig, nrm, feat), got):
+        assert torch.equal(torch.as_tensor(a).view(torch.int32), g.view(torch.int32))
+
+
+def test_async_mode_enqueues_and_sync_collects():
+    """ccg_set_async: build and query are only enqueued (device buffers), ccg_sync makes results and deferred errors valid."""
+    import torch
+    pts = torch.from_numpy(np.ascontiguousarray(synth.make_scan_np(200, 150, scene="room", seed=14)["points"])).cuda()
+    n = pts.shape[0]
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        eig, nrm = ctx.pca_knn(20, cc.COV_NM1, device_out=True)
+        feat = ctx.features(eig)
+        e2 = torch.empty((n, 3), device="cuda"); n2 = torch.empty((n, 4), device="cuda"); f2 = torch.empty((n, 7), device="cuda")
+        torch.cuda.synchronize()
+        ctx.set_async(True)
+        for _ in range(3):                                   # three steps back to back without a host synchronisation
+            ctx.set_cloud(pts)
+            ctx.pca_knn_features_into(20, cc.COV_NM1, 0, e2, n2, f2)
+        ctx.sync()
+        st = ctx.stats()
+        assert st["ms_build"] > 0 and st["ms_query"] > 0
+        for a, g in zip((eig, nrm, feat), (e2, n2, f2)):
+            assert torch.equal(torch.as_tensor(a).view(torch.int32), g.view(torch.int32))
+        bad = pts.clone(); bad[17, 1] = float("nan")
+        torch.cuda.synchronize()
+        ctx.set_cloud(bad)                                   # accepted now ...
+        with pytest.raises(cc.CcgError) as e:
+            ctx.sync()                                       # ... refused here
+        assert e.value.code == -4
+        ctx.set_async(False)
+        with pytest.raises(cc.CcgError):
+            ctx.knn(4)                                       # no cloud after the refused one
+        ctx.set_cloud(pts)
+        idx, _ = ctx.knn(4)
+        assert idx.shape == (n, 4)

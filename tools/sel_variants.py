@@ -9,12 +9,13 @@ from cloudclean_b200 import synth
 cfg, shrink = (int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "3:1").split(":"))
 variants = [
     {},
+    {"CCG_SEL_NET": "0"},
     {"CCG_SEL_MINB": "12"},
+    {"CCG_SEL_MINB": "12", "CCG_SEL_NET": "0"},
     {"CCG_SEL_STAGE": "ldg"},
-    {"CCG_SEL_DRAIN_AT": "8"},
     {"CCG_SEL_CHUNKS": "1"},
 ]
-knobs = ["CCG_SEL_MINB", "CCG_CURVE", "CCG_SEL_STAGE", "CCG_SEL_DRAIN_AT", "CCG_POINT_OVERLAP", "CCG_SEL_CHUNKS", "CCG_COLLECT_STATS", "CCG_VERBOSE_STATS"]
+knobs = ["CCG_SEL_NET", "CCG_SEL_MINB", "CCG_CURVE", "CCG_SEL_STAGE", "CCG_SEL_DRAIN_AT", "CCG_POINT_OVERLAP", "CCG_SEL_CHUNKS", "CCG_COLLECT_STATS", "CCG_VERBOSE_STATS"]
 s = synth.config_scan(cfg, device="cuda", shrink=shrink)
 pts = s["points"]; n = pts.shape[0]
 eig = torch.empty((n, 3), device="cuda"); nrm = torch.empty((n, 4), device="cuda"); feat = torch.empty((n, 7), device="cuda")
