@@ -370,7 +370,10 @@ def main():
         rpr = (n + world - 1) // world                                  # rows (original order) per rank
         pack = torch.empty((world * rpr, 4), device=dev, dtype=torch.float32)   # what is replicated: xyz(w), 16 B/point
         my_slice = torch.empty((rpr, 4), device=dev, dtype=torch.float32)
-        repl = os.environ.get("CCG_BENCH_REPL", "gather")               # "bcast": one NCCL broadcast (r01); "gather": scatter + all-gather
+        # how the cloud is replicated: "bcast" = one NCCL broadcast (r01); "gather" = NCCL scatter + all-gather;
+        # "pull" = copy-engine pulls over NVLink peer memory: every rank pulls ITS 1/N from rank 0, then the other N-1 slices
+        # from their owners (rank 0's links carry the cloud once, every other link 1/N-sized pieces in both directions)
+        repl = os.environ.get("CCG_BENCH_REPL", "pull")
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
@@ -393,6 +396,17 @@ def main():
         peer = sharding.PeerRows(ctx, npad if staged else n, (3, 4, 7), collector=0)
         p_eig, p_nrm, p_feat = peer.bufs
         token = torch.zeros(1, device=dev)
+        in_slices = sharding.PeerSlices(ctx, rpr, (4,))                 # every rank's xyz(w) slice, visible to all ranks
+        in_own = in_slices.own[0].tensor(dev)
+        in_peer = [sharding.DevBuffer(in_slices.tables[0][o], (rpr, 4), False).tensor(dev) for o in range(world)]
+        src_rows = sharding.PeerRows(ctx, world * rpr, (4,), collector=0)   # rank 0's packed cloud, visible to all ranks
+        src_all = src_rows.bufs[0].tensor(dev)
+
+        def all_gather_by_pulls():
+            dist.all_reduce(token)                                      # every slice is complete before anybody pulls it
+            for i in range(world):
+                o = (rank + i) % world                                  # staggered: no two ranks start on the same owner
+                pack[o * rpr:(o + 1) * rpr].copy_(in_peer[o] if o != rank else in_own)
         if rank == 0:
             if staged:
                 s_eig, s_nrm, s_feat = (b.tensor(dev) for b in peer.bufs)
@@ -402,11 +416,14 @@ def main():
     launches = [0]
     kernel_ms = []
     bcast_ev = []
+    e2e_ev = []
+    build_ms = []
 
     def step_device():
         if world == 1:
             ctx.set_cloud(pts)
-            launches[0] += ctx.stats()["launches_build"]
+            sb = ctx.stats()
+            launches[0] += sb["launches_build"]; build_ms.append(sb["ms_build"])
             ctx.pca_knn_features_into(K, cc.COV_NM1, 0, eig, nrm, feat)
             st = ctx.stats()
             launches[0] += st["launches"]
@@ -414,9 +431,13 @@ def main():
         else:
             eb0 = torch.cuda.Event(enable_timing=True); eb1 = torch.cuda.Event(enable_timing=True)
             eb0.record(stream)
-            if rank == 0:
-                pack[:n].copy_(pts[:, :4])         # x y z 1 of every PointXYZI: the search needs nothing else
-            if repl == "bcast":
+            if rank == 0:                          # x y z 1 of every PointXYZI: the search needs nothing else (16 B/point, not 32)
+                (src_all if repl == "pull" else pack)[:n].copy_(pts[:, :4])
+            if repl == "pull":
+                dist.all_reduce(token)             # rank 0's packed cloud is complete
+                in_own.copy_(src_all[rank * rpr:(rank + 1) * rpr])
+                all_gather_by_pulls()
+            elif repl == "bcast":
                 dist.broadcast(pack, 0)            # 16 B/point over NVLink instead of the 32-byte struct
             else:
                 # rank 0 sends every rank ITS 1/N of the cloud once (7/8 of the bytes leave rank 0 once), then the ranks
@@ -426,7 +447,8 @@ def main():
             eb1.record(stream)
             bcast_ev.append((eb0, eb1))
             ctx.set_cloud(pack[:n])
-            launches[0] += ctx.stats()["launches_build"]
+            sb = ctx.stats()
+            launches[0] += sb["launches_build"]; build_ms.append(sb["ms_build"])
             # every rank answers its interleaved share of the Morton order (8192-point chunks, round robin) and stores the rows, in original order, straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
             ctx.pca_knn_features_shard(K, cc.COV_NM1, 0, rank, world, p_eig, p_nrm, p_feat, sorted_rows=staged)
@@ -480,17 +502,30 @@ def main():
             ctx.set_cloud(np_pts)                                              # host AoS in: H2D inside the call
             ctx.pca_knn_features_into(K, cc.COV_NM1, 0, np_eig, np_nrm, np_feat)   # host outputs: D2H inside the call
         else:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
+            ev[0].record(stream)
             if rb_ > ra:
                 stage32[:rb_ - ra].copy_(shm["pts"].t[ra:rb_], non_blocking=True)      # H2D of this rank's rows
                 my_slice[:rb_ - ra].copy_(stage32[:rb_ - ra, :4])
-            dist.all_gather_into_tensor(pack, my_slice)
+            ev[1].record(stream)
+            if repl == "pull":
+                in_own.copy_(my_slice)
+                all_gather_by_pulls()
+            else:
+                dist.all_gather_into_tensor(pack, my_slice)
+            ev[2].record(stream)
             ctx.set_cloud(pack[:n])
+            ev[3].record(stream)
             ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, slices.tables[0], slices.tables[1], slices.tables[2])
+            ev[4].record(stream)
             dist.all_reduce(token)                                  # every peer has stored the rows this rank owns
+            ev[5].record(stream)
             if rb_ > ra:
                 shm["eig"].t[ra:rb_].copy_(own[0][:rb_ - ra], non_blocking=True)       # D2H to the final host addresses
                 shm["nrm"].t[ra:rb_].copy_(own[1][:rb_ - ra], non_blocking=True)
                 shm["feat"].t[ra:rb_].copy_(own[2][:rb_ - ra], non_blocking=True)
+            ev[6].record(stream)
+            e2e_ev.append(ev)
 
     def timed(fn, steps, warmup):
         with torch.cuda.stream(stream):
@@ -522,6 +557,7 @@ def main():
     launches[0] = 0
     kernel_ms.clear()
     bcast_ev.clear()
+    build_ms.clear()
     ms_dev = timed(step_device, args.steps, args.warmup)
     stage_extra = {}
     if world > 1:
@@ -535,8 +571,18 @@ def main():
                        "query_kernel_min_over_ranks": float(tmin[0].item())}
     n_launch = launches[0] * args.steps // (args.steps + args.warmup)
     kms = kernel_ms[args.warmup:]
+    bms_mean = float(np.mean(build_ms[args.warmup:]))
+    e2e_ev.clear()
     ms_e2e = timed(step_host, max(2, args.steps // 2), 1)
     e2e_steps = max(2, args.steps // 2)
+    e2e_stages = None
+    if world > 1 and e2e_ev:
+        names = ["h2d_own_slice", "all_gather", "build", "query_route", "barrier_wait", "d2h_own_slice"]
+        mine = [float(np.mean([evs[i].elapsed_time(evs[i + 1]) for evs in e2e_ev[1:]])) for i in range(6)]
+        tmx = torch.tensor(mine, device=dev, dtype=torch.float64); tmn = tmx.clone()
+        dist.all_reduce(tmx, op=dist.ReduceOp.MAX); dist.all_reduce(tmn, op=dist.ReduceOp.MIN)
+        e2e_stages = {nm: {"max_over_ranks": float(tmx[i].item()), "min_over_ranks": float(tmn[i].item())} for i, nm in enumerate(names)}
+        e2e_stages["host_pinned_registered"] = bool(pinned_ok)
     clocks = sampler.stop() if sampler else None
 
     # ---- N > 1: the sharded result must be the single-GPU result, bit for bit -------------
@@ -636,7 +682,8 @@ def main():
                         "ms_per_step": ms_e2e / e2e_steps,
                         "path": ("one pinned host copy of the scan and of the outputs shared by the ranks; per-rank H2D of 1/N of the PointXYZI rows, "
                                  "NVLink all-gather, owner-routed rows, per-rank D2H of its own slice (bytes are summed over the ranks)") if world > 1
-                                else "pinned host PointXYZI in, pinned host outputs out, through the C ABI"},
+                                else "pinned host PointXYZI in, pinned host outputs out, through the C ABI",
+                        "stage_ms": e2e_stages},
                 "gpu_launches": int(n_launch),
                 "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": f"k_tile_sel<{K}, MODE_PCA> (two-pass kNN selection + covariance + eigensolve + features)", "achieved": achieved,
@@ -644,7 +691,7 @@ def main():
                              "peak_source": peak_src, "algorithmic_bytes_per_point": BYTES_QUERY, "points_per_launch": q_rows,
                              "kernel_ms": k_ms, "kernel_ms_is": "max over ranks" if world > 1 else "this GPU",
                              "whole_step_GBps": (BYTES_QUERY + BYTES_BUILD) * n / (ms_dev / args.steps * 1e-3) / 1e9},
-                "stage_ms": dict({"build": st["ms_build"], "query_kernel": k_ms}, **stage_extra)}
+                "stage_ms": dict({"build": bms_mean, "query_kernel": k_ms}, **stage_extra)}
         if match is not None:
             line.update(match)
         if sor_line is not None:
@@ -672,6 +719,8 @@ def main():
         dist.barrier()
         peer.close()
         slices.close()
+        in_slices.close()
+        src_rows.close()
         for v in shm.values():
             v.close()
     ctx.close()

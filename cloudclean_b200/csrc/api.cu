@@ -378,6 +378,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     ctx->collect_stats = (cs && cs[0] == '1') ? 1 : 0;
     const char *sp = getenv("CCG_SPLIT_SPARSE");
     ctx->split_sparse = (sp && sp[0] == '0') ? 0 : 1;
+    const char *kbits = getenv("CCG_KEY_BITS");
+    if (kbits) ctx->key_bits = atoi(kbits);
     const char *cv = getenv("CCG_CURVE");
     ctx->curve_hilbert = (cv && cv[0] == 'm') ? 0 : 1;
     const char *da = getenv("CCG_SEL_DRAIN_AT");

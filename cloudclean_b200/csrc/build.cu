@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) k_ingest(const char *__restrict__ src, si
     }
 }
 
-constexpr int kMortonBits = 13;     // bits per axis of the curve key (39-bit keys: 5 radix passes; leaf quality equals 16 bits, tools/sim_tiles.cpp)
+constexpr int kMortonBits = 21;     // most bits per axis a curve key can hold (63-bit key); ctx->key_bits of them are used
 
 __device__ __forceinline__ unsigned long long spread21(unsigned v) {
     unsigned long long x = v & 0x1fffffull;
@@ -112,11 +112,11 @@ __device__ const unsigned char kHilbertTab[192] = {
     162, 165, 121, 134, 187, 108, 168, 183, 118, 173, 23, 124, 153, 170, 40, 59,
     178, 113, 131, 88, 181, 158, 68, 151, 186, 163, 89, 112, 189, 100, 150, 159,
 };
-__device__ __forceinline__ unsigned long long hilbert_key(unsigned long long morton, const unsigned char *tab) {
+__device__ __forceinline__ unsigned long long hilbert_key(unsigned long long morton, int bits, const unsigned char *tab) {
     unsigned long long key = 0;
     unsigned st = 0;
-#pragma unroll
-    for (int l = kMortonBits - 1; l >= 0; --l) {
+#pragma unroll 4
+    for (int l = bits - 1; l >= 0; --l) {
         const unsigned o = (unsigned)(morton >> (3 * l)) & 7u;            // octant at this level: x y z bits
         const unsigned e = tab[st * 8 + o];
         key = (key << 3) | (e & 7u);
@@ -125,17 +125,20 @@ __device__ __forceinline__ unsigned long long hilbert_key(unsigned long long mor
     return key;
 }
 
-// Space-filling-curve key of every point (kMortonBits per axis, cubic cells over the bounding box) + identity values.
-// 13 bits per axis = 39-bit keys = 5 radix passes (the sort is the largest stage of the build): cells of extent/8192
-// (1.2 cm on a 100 m scan); points sharing a cell simply keep their original (scan) order — the order is only a
-// permutation, search results do not depend on it, and the leaf quality measured by tools/sim_tiles.cpp (candidate leaves
-// scanned per tile) is the same at 12 and at 16 bits per axis.
+// Space-filling-curve key of every point (`bits` per axis, cubic cells over the bounding box).  Points sharing a cell keep
+// their original (scan) order — the order is only a permutation, search results do not depend on it — but the QUALITY of
+// the leaves does: a cell holding hundreds of points is cut into thin scan-order stripes.  16 bits per axis (1.5 mm cells
+// on a 100 m scan, 6 radix passes of (key, index) pairs) is the default; 13 bits fit key and index of a 33 M-point cloud in
+// one 64-bit word (5 passes of 8 bytes: build 3.48 -> 2.86 ms at 30 M) but cost the query what the build saves at 30 M
+// (27.6 -> 28.3 ms) and 35 % at 100 M, and 12 bits there made it ten times slower (profiles/r02_keybits.log).
 // The bounding box is read from the ingest scratch ON THE DEVICE (no host round trip in the middle of the build).
 // The point's index rides in the low `ib` bits of the same 64-bit word (key << ib | i), so the sort moves 8 bytes per
 // point and pass instead of a 12-byte (key, value) pair, and only the key bits [ib, ib + kb) are sorted.
+// vals == NULL: packed words; vals != NULL: (key, index) pairs — the path of clouds whose index bits leave no room for
+// enough key bits in one word (see build_cloud).
 template <bool HILBERT>
 __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig, int n, const IngestScratch *__restrict__ sc,
-                                                int ib, int drop, unsigned long long *__restrict__ keys) {
+                                                int ib, int bits, unsigned long long *__restrict__ keys, unsigned *__restrict__ vals) {
     __shared__ unsigned char s_tab[192];
     if (HILBERT) {
         if (threadIdx.x < 192) s_tab[threadIdx.x] = kHilbertTab[threadIdx.x];
@@ -145,15 +148,16 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
     if (i >= n) return;
     const float lx = ord2f(sc->lo[0]), ly = ord2f(sc->lo[1]), lz = ord2f(sc->lo[2]);
     const float ext = fmaxf(fmaxf(ord2f(sc->hi[0]) - lx, ord2f(sc->hi[1]) - ly), ord2f(sc->hi[2]) - lz);
-    const float inv_cell = ext > 0.f ? __fdiv_rn((float)(1u << kMortonBits), __fmul_rn(ext, 1.0001f)) : 0.f;
+    const float inv_cell = ext > 0.f ? __fdiv_rn((float)(1u << bits), __fmul_rn(ext, 1.0001f)) : 0.f;
     float4 p = orig[i];
-    constexpr float qmax = (float)((1u << kMortonBits) - 1u);
+    const float qmax = (float)((1u << bits) - 1u);
     unsigned qx = (unsigned)fminf(fmaxf((p.x - lx) * inv_cell, 0.f), qmax);
     unsigned qy = (unsigned)fminf(fmaxf((p.y - ly) * inv_cell, 0.f), qmax);
     unsigned qz = (unsigned)fminf(fmaxf((p.z - lz) * inv_cell, 0.f), qmax);
     unsigned long long key = spread21(qz) | (spread21(qy) << 1) | (spread21(qx) << 2);
-    if (HILBERT) key = hilbert_key(key, s_tab);
-    keys[i] = ((key >> drop) << ib) | (unsigned long long)(unsigned)i;
+    if (HILBERT) key = hilbert_key(key, bits, s_tab);
+    if (vals) { keys[i] = key; vals[i] = (unsigned)i; }
+    else keys[i] = (key << ib) | (unsigned long long)(unsigned)i;
 }
 
 
@@ -166,6 +170,7 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ orig,
 // kIsoFactor times the median of that distance over its aligned 32-point window.  One warp per window.
 constexpr float kIsoFactor = 8.f;
 // Also unpacks the sorted words: order32[i] = index bits of packed[i].
+// packed == NULL: order32 already holds the sorted indices (pairs path).
 __global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ orig, const unsigned long long *__restrict__ packed,
                                                     unsigned long long idx_mask, int n, unsigned *__restrict__ order32,
                                                     unsigned char *__restrict__ dense) {
@@ -176,15 +181,16 @@ __global__ void __launch_bounds__(256) k_flag_dense(const float4 *__restrict__ o
     const bool valid = i < n;
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
-        const unsigned o = (unsigned)(packed[i] & idx_mask);
-        order32[i] = o;
+        unsigned o;
+        if (packed) { o = (unsigned)(packed[i] & idx_mask); order32[i] = o; }
+        else o = order32[i];
         p = orig[o];
     }
     float px = __shfl_up_sync(kFull, p.x, 1), py = __shfl_up_sync(kFull, p.y, 1), pz = __shfl_up_sync(kFull, p.z, 1);
     float nx = __shfl_down_sync(kFull, p.x, 1), ny = __shfl_down_sync(kFull, p.y, 1), nz = __shfl_down_sync(kFull, p.z, 1);
     bool has_prev = valid && i > 0, has_next = valid && i + 1 < n;
-    if (lane == 0 && has_prev) { const float4 t = orig[(unsigned)(packed[i - 1] & idx_mask)]; px = t.x; py = t.y; pz = t.z; }
-    if (lane == 31 && has_next) { const float4 t = orig[(unsigned)(packed[i + 1] & idx_mask)]; nx = t.x; ny = t.y; nz = t.z; }
+    if (lane == 0 && has_prev) { const float4 t = orig[packed ? (unsigned)(packed[i - 1] & idx_mask) : order32[i - 1]]; px = t.x; py = t.y; pz = t.z; }
+    if (lane == 31 && has_next) { const float4 t = orig[packed ? (unsigned)(packed[i + 1] & idx_mask) : order32[i + 1]]; nx = t.x; ny = t.y; nz = t.z; }
     float gp = INFINITY, gn = INFINITY;
     if (has_prev) { const float x = p.x - px, y = p.y - py, z = p.z - pz; gp = x * x + y * y + z * z; }
     if (has_next) { const float x = p.x - nx, y = p.y - ny, z = p.z - nz; gn = x * x + y * y + z * z; }
@@ -234,8 +240,11 @@ __global__ void __launch_bounds__(256) k_reorder_leaves(const float4 *__restrict
         lz = fminf(lz, __shfl_xor_sync(kFull, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(kFull, hx, o));
         hy = fmaxf(hy, __shfl_xor_sync(kFull, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(kFull, hz, o));
     }
+    // lo.w = smallest original index inside the leaf (int bits; INT_MAX pads never win): lets the exact point kernel skip a
+    // box that can only hold candidates TIED with its current k-th distance but with larger indices (duplicate piles)
+    const int mi = __reduce_min_sync(kFull, __float_as_int(p.w));
     if (lane == 0) {
-        lo0[leaf] = make_float4(lx, ly, lz, 0.f);
+        lo0[leaf] = make_float4(lx, ly, lz, __int_as_float(mi));
         hi0[leaf] = make_float4(hx, hy, hz, 0.f);
     }
     const float cx = __fmul_rn(0.5f, __fadd_rn(lx, hx)), cy = __fmul_rn(0.5f, __fadd_rn(ly, hy)), cz = __fmul_rn(0.5f, __fadd_rn(lz, hz));
@@ -258,10 +267,13 @@ __global__ void __launch_bounds__(256) k_build_level(const float4 *__restrict__ 
     if (node >= nparent) return;
     int c = node * kFan + lane;
     float lx = INFINITY, ly = INFINITY, lz = INFINITY, hx = -INFINITY, hy = -INFINITY, hz = -INFINITY;
+    int mi = 0x7fffffff;
     if (c < nchild) {
         float4 a = clo[c], b = chi[c];
         lx = a.x; ly = a.y; lz = a.z; hx = b.x; hy = b.y; hz = b.z;
+        mi = __float_as_int(a.w);
     }
+    mi = __reduce_min_sync(kFull, mi);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         lx = fminf(lx, __shfl_xor_sync(kFull, lx, o)); ly = fminf(ly, __shfl_xor_sync(kFull, ly, o));
@@ -269,7 +281,7 @@ __global__ void __launch_bounds__(256) k_build_level(const float4 *__restrict__ 
         hy = fmaxf(hy, __shfl_xor_sync(kFull, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(kFull, hz, o));
     }
     if (lane == 0) {
-        plo[node] = make_float4(lx, ly, lz, 0.f);
+        plo[node] = make_float4(lx, ly, lz, __int_as_float(mi));       // smallest original index below this node
         phi[node] = make_float4(hx, hy, hz, 0.f);
     }
 }
@@ -368,49 +380,63 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
         ctx->stats.launches_build++;
     }
     // ---- curve keys + radix sort ------------------------------------------------------------------------
+    // key_bits per axis of the curve index are sorted.  When key and index fit one 64-bit word (3 * key_bits + index bits
+    // <= 64) the sort moves packed words (8 B per point and pass, keys only); otherwise (key, index) pairs (12 B).
+    // The resolution matters where the scan is dense: 13 bits over a 100 m box are 1.2 cm cells, which hold hundreds of
+    // points near the scanner, in scan order — leaves inside such a cell are thin stripes.  Measured: the 100 M-point
+    // scan with 12-bit packed keys ran the query 12x slower than with 16 bits (profiles/r02_bench_n8_cfg4_*.json).
     int ib = 1;
     while (ib < 32 && ((n - 1) >> ib)) ++ib;                       // bits of the largest index
-    int kb = 3 * kMortonBits;
-    if (kb > 64 - ib) kb = (64 - ib) / 3 * 3;                      // > 2^25 points: the key gives up low bits to the index
-    const int drop = 3 * kMortonBits - kb;
+    int bits = ctx->key_bits < 4 ? 4 : (ctx->key_bits > kMortonBits ? kMortonBits : ctx->key_bits);
+    const int kb = 3 * bits;
+    const bool packed_sort = kb + ib <= 64;
     {
         int blocks = (int)((n + 255) / 256);
+        unsigned *v0 = packed_sort ? nullptr : ctx->vals[0].as<unsigned>();
         if (ctx->curve_hilbert)
-            k_morton<true><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, drop,
-                                                   ctx->keys[0].as<unsigned long long>());
+            k_morton<true><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, bits,
+                                                   ctx->keys[0].as<unsigned long long>(), v0);
         else
-            k_morton<false><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, drop,
-                                                    ctx->keys[0].as<unsigned long long>());
+            k_morton<false><<<blocks, 256, 0, st>>>(ctx->orig.as<float4>(), (int)n, ctx->scratch.as<IngestScratch>(), ib, bits,
+                                                    ctx->keys[0].as<unsigned long long>(), v0);
         ctx->stats.launches_build++;
     }
-    int ksel = 0;
+    int ksel = 0, vsel = 0;
     {
         cub::DoubleBuffer<unsigned long long> dk(ctx->keys[0].as<unsigned long long>(), ctx->keys[1].as<unsigned long long>());
+        cub::DoubleBuffer<unsigned> dv(ctx->vals[0].as<unsigned>(), ctx->vals[1].as<unsigned>());
         size_t tmp_bytes = 0;
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, dk, (int)n, ib, ib + kb, st));
-        CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
-        CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(ctx->sort_tmp.p, tmp_bytes, dk, (int)n, ib, ib + kb, st));
+        if (packed_sort) {
+            CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, dk, (int)n, ib, ib + kb, st));
+            CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+            CCG_CUDA(ctx, cub::DeviceRadixSort::SortKeys(ctx->sort_tmp.p, tmp_bytes, dk, (int)n, ib, ib + kb, st));
+        } else {
+            CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, kb, st));
+            CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+            CCG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, dk, dv, (int)n, 0, kb, st));
+            vsel = dv.selector;
+        }
         ksel = dk.selector;
         ctx->stats.launches_build += 2 + (kb + 7) / 8;            // onesweep: histogram + scan + one pass per 8-bit digit
     }
-    // ---- unpack the order; isolated points to the end of it ------------------------------------------------
+    // ---- the order (unpacked from the sorted words, or the sorted values); isolated points to the end of it --------
     {
-        const unsigned long long *packed = ctx->keys[ksel].as<unsigned long long>();
+        const unsigned long long *packed = packed_sort ? ctx->keys[ksel].as<unsigned long long>() : nullptr;
         const unsigned long long mask = (1ull << ib) - 1ull;
-        unsigned *ord = ctx->vals[0].as<unsigned>();
-        unsigned *ord2 = ctx->vals[1].as<unsigned>();
+        unsigned *ord = ctx->vals[packed_sort ? 0 : vsel].as<unsigned>();
+        unsigned *ord2 = ctx->vals[packed_sort ? 1 : (vsel ^ 1)].as<unsigned>();
         unsigned char *flags = ctx->keys[ksel ^ 1].as<unsigned char>();    // the other key buffer is free now
         int *nsel = (int *)((char *)ctx->scratch.p + 2048);
         const int nwin = (int)((n + 31) / 32);
         k_flag_dense<<<(nwin + 7) / 8, 256, 0, st>>>(ctx->orig.as<float4>(), packed, mask, (int)n, ord, flags);
         ctx->stats.launches_build++;
-        ctx->order_sel = 0;
+        ctx->order_sel = packed_sort ? 0 : vsel;
         if (ctx->split_sparse && n > 64) {
             size_t tmp_bytes = 0;
             CCG_CUDA(ctx, cub::DevicePartition::Flagged(nullptr, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
             CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
             CCG_CUDA(ctx, cub::DevicePartition::Flagged(ctx->sort_tmp.p, tmp_bytes, ord, flags, ord2, nsel, (int)n, st));
-            ctx->order_sel = 1;
+            ctx->order_sel ^= 1;
             ctx->stats.launches_build += 2;
         }
     }

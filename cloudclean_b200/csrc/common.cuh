@@ -114,6 +114,7 @@ struct ccg_ctx {
     int route_world = 0; size_t route_rows = 0;             // set by ccg_pca_knn_features_route around pca_common
     float *route_ptr[3][16] = {};
     int knn_use_topk = 0;    // CCG_KNN_TOPK=1: ordered lists from the 64-bit keyed k_tile_topk instead of k_tile_sel<MODE_KNN>
+    int key_bits = 16;       // curve-key bits per axis, 4..21 (CCG_KEY_BITS; 13 fits key + index of 33 M points in one word)
     int curve_hilbert = 1;   // leaf order along the Hilbert curve (CCG_CURVE=morton: Z-order, for A/B runs)
     int sel_drain_at = 0;    // k_tile_sel: pending survivors per lane that trigger a drain; 0 = only at the end of the list (CCG_SEL_DRAIN_AT)
     int sel_net = 1;         // k_tile_sel: own leaf seeded by a register sorting network when k == K (CCG_SEL_NET=0: ordered inserts)

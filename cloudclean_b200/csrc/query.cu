@@ -1568,7 +1568,16 @@ __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ Tre
         if (m == 0) { --sp; continue; }
         const bool mine = (m >> lane) & 1u;
         float bd = INFINITY;
-        if (mine) bd = d2_point_box(q, T.lo[lv][base + lane], T.hi[lv][base + lane]);
+        unsigned bmin = 0xffffffffu;                  // smallest original index below this lane's box
+        if (mine) {
+            const float4 blo = T.lo[lv][base + lane];
+            bmin = (unsigned)__float_as_int(blo.w);
+            bd = d2_point_box(q, blo, T.hi[lv][base + lane]);
+            // A box exactly AT the k-th distance can only hold candidates tied with it: they win only with a smaller index.
+            // blo.w = smallest original index below the box, so a pile of duplicates (PTX files are written with 6
+            // decimals: common on real scans) costs one visit of its low-index leaf instead of all of them.
+            if (bd == bound && __float_as_uint(bd) == (unsigned)(worst >> 32) && (unsigned)__float_as_int(blo.w) >= (unsigned)(worst & 0xffffffffu)) bd = INFINITY;
+        }
         if (lv == 0) {
             // A group of up to 32 leaves: rank them ONCE by box distance (bitonic sort of the distance bits with the lane
             // id in the low 5 bits) and score them in that order until the first one beyond the bound — every later one
@@ -1594,6 +1603,8 @@ __global__ void __launch_bounds__(128) k_point_query(const __grid_constant__ Tre
                     if (__float_as_uint(bdc) - __float_as_uint(bound) > 32u) break;
                     continue;
                 }
+                // the list tightened since the group was entered: a leaf AT the k-th distance holding only larger indices is moot
+                if (__float_as_uint(bdc) == (unsigned)(worst >> 32) && __shfl_sync(kFull, bmin, cbit) >= (unsigned)(worst & 0xffffffffu)) continue;
                 const float4 c = T.pts[(size_t)(base + cbit) * kLeaf + lane];
                 const float dd = d2_point(q, c);
                 const u64 ck = ((u64)__float_as_uint(dd) << 32) | (unsigned)__float_as_int(c.w);

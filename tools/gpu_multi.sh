@@ -20,7 +20,7 @@ EXTRA=("$@")
 if [ "$N" -ge 2 ]; then timeout 600 python -m pytest tests/test_gpu_scatter.py -m gpu -q 2>&1 | tail -3; fi
 np=2
 while [ $np -le $N ]; do
-  run n${np}_gather $np CCG_BENCH_REPL=gather
+  run n${np}_pull $np CCG_BENCH_REPL=pull
   run n${np}_bcast $np CCG_BENCH_REPL=bcast
   np=$((np * 2))
 done

@@ -1,20 +1,19 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, the bench line, the ncu launch list and one full capture of the top kernel.
+# One gpurun call: GPU parity tests, the bench line (+ reference arm), the ncu launch list and one full capture of the top kernel.
 set -u
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -3 gpurun_out/pytest_gpu.log
+python -m pytest tests -m gpu -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+grep -E "passed|failed|config 5:|FAILED" gpurun_out/pytest_gpu.log | tail -12
 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-cat gpurun_out/bench.json
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
-cat gpurun_out/bench_ref.json
-CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+cut -c1-1500 gpurun_out/bench.json
+if [ "${REF:-1}" = "1" ]; then
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+cut -c1-1200 gpurun_out/bench_ref.json
+fi
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-other-configs"
 $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^k_|Device" -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu launches rc=$?"
-$CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_tile_sel -s 1 -c 1 -f -o gpurun_out/prof_sel $CMD > gpurun_out/ncu2.log 2>&1
-echo "ncu full rc=$?"
-# next rows: adapters program, PTX ingest timing (8.4 M lines), uncapped radius features at full size
+python tools/launch_times.py gpurun_out/launches.csv > gpurun_out/launches.txt 2>&1; tail -22 gpurun_out/launches.txt
+CCG_SEL_CHUNKS=1 bash tools/gpu_prof.sh k_tile_sel prof_sel_r02_final
 ./adapters/test_adapters > gpurun_out/adapters.log 2>&1; echo "adapters rc=$?"
-python tools/ptx_bench.py 4096 2048 > gpurun_out/ptx_bench.log 2>&1; echo "ptx bench rc=$?"; tail -4 gpurun_out/ptx_bench.log

@@ -62,10 +62,11 @@ tab = [trans[(s, o)][0] | trans[(s, o)][1] << 3 for s in range(ns) for o in rang
 print(tab)
 # verify table against H for random 13-bit coords
 for _ in range(20000):
-    x, y, z = (random.randrange(1 << 13) for _ in range(3))
+    NB = 16
+    x, y, z = (random.randrange(1 << NB) for _ in range(3))
     s = 0; key = 0
-    for l in range(12, -1, -1):
+    for l in range(NB - 1, -1, -1):
         o = (x >> l & 1) << 2 | (y >> l & 1) << 1 | (z >> l & 1)
         e = tab[s * 8 + o]; key = key << 3 | (e & 7); s = e >> 3
-    assert key == H(x, y, z, 13)
+    assert key == H(x, y, z, NB)
 print("table ok")
