@@ -35,7 +35,8 @@ import numpy as np
 K = 20
 BYTES_QUERY = 48 + 16 * K          # own point 16 + k x 16 + outputs 32
 BYTES_BUILD = 144
-DUPLICATES = 100_000              # config 5 adversarial variant: exact copies of one point
+RW = 3                             # floats per point that are replicated across GPUs: the search needs x y z only (12 B, not the 32-byte struct)
+DUPLICATES = 1_000_000            # config 5 adversarial variant: exact copies of one point piled into one cell
 METRIC = "points/s kNN(k=20)+PCA features, 30M-pt scan"
 CPU_SAMPLE_POINTS = 8_000_000     # the in-run cpu_baseline leg: 2 passes over this prefix (~10 s of CPU work)
 
@@ -311,7 +312,7 @@ def other_configs(ctx, cc, stream, dev, peak, shrink):
         eig = torch.empty((n, 3), device=dev); nrm = torch.empty((n, 4), device=dev)
         ms, _ = timed(lambda: (ctx.set_cloud(pts), ctx.pca_knn_into(K, cc.COV_NM1, eig, nrm)), reps=1)
         out["config5_duplicates"] = dict(entry(ms, n, BYTES_BUILD + BYTES_QUERY), points=n, duplicates=DUPLICATES,
-                                         note="all-tied neighbourhoods are decided by the exact point kernel (index tie-break)")
+                                         note="all-tied neighbourhoods are decided by the exact point kernel (index tie-break, index-aware pruning of tied boxes)")
         del sc, pts, eig, nrm
         torch.cuda.empty_cache()
     return out
@@ -351,6 +352,15 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # run next to the GPU: CPU affinity = the cores NVML names as local to this rank's GPU (host copies and first-touch
+        # page placement then use that socket's memory)
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(physical_device_index(local)))
+        except Exception:
+            pass
+    if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}"
@@ -368,12 +378,17 @@ def main():
         dist.broadcast(nt, 0)
         n = int(nt.item())
         rpr = (n + world - 1) // world                                  # rows (original order) per rank
-        pack = torch.empty((world * rpr, 4), device=dev, dtype=torch.float32)   # what is replicated: xyz(w), 16 B/point
-        my_slice = torch.empty((rpr, 4), device=dev, dtype=torch.float32)
-        # how the cloud is replicated: "bcast" = one NCCL broadcast (r01); "gather" = NCCL scatter + all-gather;
-        # "pull" = copy-engine pulls over NVLink peer memory: every rank pulls ITS 1/N from rank 0, then the other N-1 slices
-        # from their owners (rank 0's links carry the cloud once, every other link 1/N-sized pieces in both directions)
-        repl = os.environ.get("CCG_BENCH_REPL", "pull")
+        pack = torch.empty((world * rpr, RW), device=dev, dtype=torch.float32)  # what is replicated: packed xyz, 12 B/point
+        my_slice = torch.empty((rpr, RW), device=dev, dtype=torch.float32)
+        # how the cloud is replicated: "bcast" = one NCCL broadcast; "gather" = NCCL scatter + all-gather; "pull" = copy-engine
+        # pulls over NVLink peer memory (every rank pulls ITS 1/N from rank 0, then the other N-1 slices from their owners).
+        # Measured at N = 8, 481 MB (profiles/r02_bench_n8_*): bcast 2.73 ms, gather 3.18 ms, pull 3.21 ms -> bcast stays.
+        repl = os.environ.get("CCG_BENCH_REPL", "bcast")
+        # where the value path's rows go: "staged" = into rank 0's arrays at their curve position from inside the kernel, then one
+        # un-permute on rank 0; "route" = to the rank owning their original index, then contiguous copy-engine gathers into
+        # rank 0.  Measured at N = 8: staged 13.3 ms/step, route 14.4 ms/step -> staged stays (route is what e2e uses, where
+        # the rows never have to meet on one GPU)
+        out_mode = os.environ.get("CCG_BENCH_OUT", "staged")
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
@@ -396,10 +411,10 @@ def main():
         peer = sharding.PeerRows(ctx, npad if staged else n, (3, 4, 7), collector=0)
         p_eig, p_nrm, p_feat = peer.bufs
         token = torch.zeros(1, device=dev)
-        in_slices = sharding.PeerSlices(ctx, rpr, (4,))                 # every rank's xyz(w) slice, visible to all ranks
+        in_slices = sharding.PeerSlices(ctx, rpr, (RW,))                # every rank's xyz slice, visible to all ranks
         in_own = in_slices.own[0].tensor(dev)
-        in_peer = [sharding.DevBuffer(in_slices.tables[0][o], (rpr, 4), False).tensor(dev) for o in range(world)]
-        src_rows = sharding.PeerRows(ctx, world * rpr, (4,), collector=0)   # rank 0's packed cloud, visible to all ranks
+        in_peer = [sharding.DevBuffer(in_slices.tables[0][o], (rpr, RW), False).tensor(dev) for o in range(world)]
+        src_rows = sharding.PeerRows(ctx, world * rpr, (RW,), collector=0)   # rank 0's packed cloud, visible to all ranks
         src_all = src_rows.bufs[0].tensor(dev)
 
         def all_gather_by_pulls():
@@ -431,8 +446,8 @@ def main():
         else:
             eb0 = torch.cuda.Event(enable_timing=True); eb1 = torch.cuda.Event(enable_timing=True)
             eb0.record(stream)
-            if rank == 0:                          # x y z 1 of every PointXYZI: the search needs nothing else (16 B/point, not 32)
-                (src_all if repl == "pull" else pack)[:n].copy_(pts[:, :4])
+            if rank == 0:                          # x y z of every PointXYZI: the search needs nothing else (12 B/point, not 32)
+                (src_all if repl == "pull" else pack)[:n].copy_(pts[:, :RW])
             if repl == "pull":
                 dist.all_reduce(token)             # rank 0's packed cloud is complete
                 in_own.copy_(src_all[rank * rpr:(rank + 1) * rpr])
@@ -442,14 +457,30 @@ def main():
             else:
                 # rank 0 sends every rank ITS 1/N of the cloud once (7/8 of the bytes leave rank 0 once), then the ranks
                 # all-gather: every link carries 1/N-sized pieces in both directions instead of one root feeding N-1 peers
-                dist.scatter(my_slice, list(pack.view(world, rpr, 4).unbind(0)) if rank == 0 else None, src=0)
+                dist.scatter(my_slice, list(pack.view(world, rpr, RW).unbind(0)) if rank == 0 else None, src=0)
                 dist.all_gather_into_tensor(pack, my_slice)
             eb1.record(stream)
             bcast_ev.append((eb0, eb1))
             ctx.set_cloud(pack[:n])
             sb = ctx.stats()
             launches[0] += sb["launches_build"]; build_ms.append(sb["ms_build"])
-            # every rank answers its interleaved share of the Morton order (8192-point chunks, round robin) and stores the rows, in original order, straight into rank 0's
+            if out_mode == "route":
+                # every rank stores each row with the rank OWNING its original index (all NVLink ports share the traffic), then
+                # rank 0 pulls the N contiguous slices with the copy engines: no un-permute pass, no single ingress port
+                # taking scattered stores
+                ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, slices.tables[0], slices.tables[1], slices.tables[2])
+                st = ctx.stats()
+                launches[0] += st["launches"]
+                kernel_ms.append(st["ms_query"])
+                dist.all_reduce(token)
+                if rank == 0:
+                    for o in range(world):
+                        a_, b_ = o * rpr, min(n, (o + 1) * rpr)
+                        if b_ > a_:
+                            for dst, src in zip((o_eig, o_nrm, o_feat), slice_view[o]):
+                                dst[a_:b_].copy_(src[:b_ - a_])
+                return
+            # every rank answers its interleaved share of the curve order (8192-point chunks, round robin) and stores the rows straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
             ctx.pca_knn_features_shard(K, cc.COV_NM1, 0, rank, world, p_eig, p_nrm, p_feat, sorted_rows=staged)
             st = ctx.stats()
@@ -480,20 +511,40 @@ def main():
         # of the three output arrays to their final host addresses.  No rank funnels the job through one link.
         tag = f"ccg_bench_{os.environ.get('MASTER_PORT', '0')}"
         shm = {}
+        ra, rb_ = rank * rpr, min(n, (rank + 1) * rpr)
         for name, w in (("pts", 8), ("eig", 3), ("nrm", 4), ("feat", 7)):
             if rank == 0:
-                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w), create=True)
+                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w), create=True, register=False)
         dist.barrier()
         for name, w in (("pts", 8), ("eig", 3), ("nrm", 4), ("feat", 7)):
             if rank != 0:
-                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w))
+                shm[name] = sharding.SharedPinned(f"{tag}_{name}", (n, w), register=False)
+        # NUMA placement by first touch: every rank writes ITS rows of the four arrays (the scan rows arrive over NCCL from rank
+        # 0's device copy, untimed set-up) before anybody page-locks the mappings, so that each GPU's host traffic stays on
+        # the memory next to its own PCIe root — what `numactl --interleave` / a NUMA-aware application buffer gives a user
+        sl = torch.empty((rpr, 8), device=dev)
         if rank == 0:
-            shm["pts"].t.copy_(pts)
+            padded = torch.zeros((world * rpr, 8), device=dev)
+            padded[:n].copy_(pts)
+            dist.scatter(sl, list(padded.view(world, rpr, 8).unbind(0)), src=0)
+            del padded
+        else:
+            dist.scatter(sl, None, src=0)
+        if rb_ > ra:
+            shm["pts"].t[ra:rb_].copy_(sl[:rb_ - ra].cpu())
+            for name in ("eig", "nrm", "feat"):
+                shm[name].t[ra:rb_].zero_()
+        del sl
+        dist.barrier()
+        for v in shm.values():
+            v.register()
         dist.barrier()
         slices = sharding.PeerSlices(ctx, rpr, (3, 4, 7))
-        ra, rb_ = rank * rpr, min(n, (rank + 1) * rpr)
         stage32 = torch.empty((rpr, 8), device=dev)                 # this rank's PointXYZI rows as uploaded
         own = [b.tensor(dev) for b in slices.own]
+        # rank 0's views of every rank's output slices (value path with CCG_BENCH_OUT=route)
+        slice_view = [[sharding.DevBuffer(slices.tables[a_][o], (rpr, w_), False).tensor(dev) for a_, w_ in enumerate((3, 4, 7))]
+                      for o in range(world)] if rank == 0 else None
         h2d = n * 32                                                # summed over the ranks
         pinned_ok = all(v.registered for v in shm.values())
 
@@ -506,7 +557,7 @@ def main():
             ev[0].record(stream)
             if rb_ > ra:
                 stage32[:rb_ - ra].copy_(shm["pts"].t[ra:rb_], non_blocking=True)      # H2D of this rank's rows
-                my_slice[:rb_ - ra].copy_(stage32[:rb_ - ra, :4])
+                my_slice[:rb_ - ra].copy_(stage32[:rb_ - ra, :RW])
             ev[1].record(stream)
             if repl == "pull":
                 in_own.copy_(my_slice)

@@ -30,7 +30,7 @@ SYMBOLS = [
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
     "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_fpfh", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
-    "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route",
+    "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route", "ccg_radius_csr",
 ]
 
 
@@ -100,6 +100,7 @@ def load_library():
     L.ccg_pca_knn_features_scatter.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
     L.ccg_pca_knn_features_shard.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, i32, vp, vp, vp]
     L.ccg_pca_knn_features_route.argtypes = [vp, i32, i32, vp, i32, i32, i32, i32, sz, vp, vp, vp]
+    L.ccg_radius_csr.argtypes = [vp, f64, i32, i32, vp, vp, vp, C.c_int64, C.POINTER(C.c_int64)]
     L.ccg_knn_graph.argtypes = [vp, i32, f64, vp, vp]
     L.ccg_normal_stdev.argtypes = [vp, f64, i32, vp, sz, vp]
     L.ccg_stdev_dist.argtypes = [vp, f64, i32, i32, vp, vp]
@@ -473,6 +474,25 @@ class Context:
 
     def ipc_close(self, addr):
         self._check(self.L.ccg_ipc_close(self.h, C.c_void_p(addr)))
+
+    def radius_csr(self, r, max_nn=0, strict_lt=True, want_d2=True, device_out=None):
+        """variable-length radius lists (any cap, 0 = uncapped): (offsets int64[n+1], idx int32[total], d2 float32[total]),
+        every row ascending (d2, index) — what radiusSearch fills into its vectors"""
+        dev = self.on_device if device_out is None else device_out
+        _np = np
+        if dev:
+            import torch
+            off = torch.empty((self.n + 1,), dtype=torch.int64, device=f"cuda:{self.device}")
+        else:
+            off = np.empty(self.n + 1, np.int64)
+        tot = C.c_int64(0)
+        self._check(self.L.ccg_radius_csr(self.h, float(r), max_nn, 1 if strict_lt else 0, _ptr(off), None, None, 0, C.byref(tot)))
+        idx = self._out(dev, (tot.value,), _np.int32)
+        d2 = self._out(dev, (tot.value,), _np.float32) if want_d2 else None
+        if tot.value:
+            self._check(self.L.ccg_radius_csr(self.h, float(r), max_nn, 1 if strict_lt else 0, _ptr(off), _ptr(idx), _ptr(d2), tot.value,
+                                              C.byref(tot)))
+        return off, idx, d2
 
     # ---- a4 / a5 -----------------------------------------------------------------------------------
     def pca_radius(self, r, max_nn=0, cov_norm=COV_NM1, normalise_hist=False, viewpoint=None, want_normals=False,

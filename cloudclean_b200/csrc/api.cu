@@ -754,6 +754,40 @@ int ccg_radius(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int32_t *idx, 
     return finish_call(ctx);
 }
 
+/* ---- a2: variable-length neighbour lists (what radiusSearch fills into std::vector<int> / std::vector<float>) ---- */
+int ccg_radius_csr(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int64_t *offsets, int32_t *idx, float *d2, int64_t capacity,
+                   int64_t *total) {
+    CCG_TRY(begin_call(ctx, true));
+    if (!(r >= 0.0) || max_nn < 0) return set_error(ctx, CCG_ERR_INVALID, "need r >= 0 and max_nn >= 0");
+    if (!offsets || !total) return set_error(ctx, CCG_ERR_INVALID, "offsets and total are required");
+    const size_t n = ctx->n;
+    *total = 0;
+    if (n == 0) { offsets[0] = 0; return CCG_OK; }
+    static_assert(sizeof(long long) == sizeof(int64_t), "int64");
+    const float rb = radius_bound(r, strict_lt);
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, offsets, (n + 1) * 8));
+    CCG_TRY(query_begin(ctx));
+    const float *Tp; const int32_t *Ip;
+    CCG_TRY(launch_radius_rule(ctx, rb, max_nn, &Tp, &Ip));
+    long long tot = 0;
+    CCG_TRY(launch_radius_csr_count(ctx, rb, Tp, Ip, oo.dev<long long>(), &tot));
+    *total = tot;
+    if (idx || d2) {
+        if (tot > capacity) return set_error(ctx, CCG_ERR_INVALID, "radius lists hold %lld entries, capacity is %lld", tot, (long long)capacity);
+        OutBuf oi, od;
+        CCG_TRY(oi.open(ctx, 1, idx, (size_t)tot * 4));
+        CCG_TRY(od.open(ctx, 2, d2, (size_t)tot * 4));
+        CCG_TRY(launch_radius_csr_fill(ctx, rb, Tp, Ip, oo.dev<long long>(), tot, oi.dev<int32_t>(), od.dev<float>()));
+        CCG_TRY(query_end(ctx));
+        CCG_TRY(oi.close()); CCG_TRY(od.close());
+    } else {
+        CCG_TRY(query_end(ctx));
+    }
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
 static int pca_common(ccg_ctx *ctx, int k, float rb, int cov_norm, int normalise_hist, const float *vp, size_t begin, size_t end,
                       int sorted_rows, float *eig3, float *normal4, int32_t *count, bool uncapped, float *feat7 = nullptr,
                       int formula_set = 0) {

@@ -222,6 +222,10 @@ int launch_rule_normal_stdev(ccg_ctx *ctx, float rb, const float *Tpos, const in
 int launch_rule_hist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, int bins, int which, double radius, const void *attr,
                      size_t stride, float *hist);
 
+int launch_radius_csr_count(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, long long *offsets_dev, long long *total_host);
+int launch_radius_csr_fill(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, const long long *offsets_dev, long long total,
+                           int32_t *idx_dev, float *d2_dev);
+
 int launch_tile_attrsum(ccg_ctx *ctx, float rb, const void *attr_dev, size_t stride, float *sum3, int32_t *count);
 int launch_tile_attrsum2(ccg_ctx *ctx, float rb1, float rb2, const void *attr_dev, size_t stride, float *sum1, int32_t *count1,
                          float *sum2, int32_t *count2);

@@ -16,6 +16,8 @@
 // The fp32 sums of the visitors run in traversal order, not in the reference's ascending-distance order: counts, histograms
 // and neighbour SETS are exact, the sums agree to a stated 1e-5 (tests/test_gpu_parity.py).
 #include "tile.cuh"
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_segmented_sort.cuh>
 #include <limits.h>
 
 namespace ccg {
@@ -343,6 +345,51 @@ struct RuleHist : RuleBase {          // calcDistHist / calcIntensityHist (featu
     }
 };
 
+struct RuleCount : RuleBase {         // CSR pass 1: neighbours per point
+    struct Args { long long *count64; };
+    static constexpr int kSmemWords = 0;
+    __device__ __forceinline__ void init(const Args &, const float4 &, unsigned *) {}
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 8
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            count += accept(d2_point(q, c), __float_as_int(c.w)) ? 1 : 0;
+        }
+    }
+    __device__ __forceinline__ void finish(const Args &a, const float4 &, size_t row) { a.count64[row] = count; }
+};
+
+struct RuleFill : RuleBase {          // CSR pass 2: (d2 bits << 32 | index) keys of the neighbours, in traversal order
+    struct Args { const long long *offsets; unsigned long long *keys; };
+    static constexpr int kSmemWords = 0;
+    unsigned long long *dst;
+    __device__ __forceinline__ void init(const Args &a, const float4 &q, unsigned *) {
+        dst = bound >= 0.f ? a.keys + a.offsets[__float_as_int(q.w)] : nullptr;
+    }
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 4
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            const float d2 = d2_point(q, c);
+            if (accept(d2, __float_as_int(c.w))) {
+                dst[count] = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)__float_as_int(c.w);
+                ++count;
+            }
+        }
+    }
+    __device__ __forceinline__ void finish(const Args &, const float4 &, size_t) {}
+};
+
+// sorted keys -> the two output arrays
+__global__ void __launch_bounds__(256) k_csr_unpack(const unsigned long long *__restrict__ keys, long long total, int32_t *__restrict__ idx,
+                                                    float *__restrict__ d2) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const unsigned long long k = keys[i];
+    if (idx) idx[i] = (int32_t)(unsigned)(k & 0xffffffffu);
+    if (d2) d2[i] = __uint_as_float((unsigned)(k >> 32));
+}
+
 template <class V>
 __global__ void __launch_bounds__(128) k_tile_rule(const __grid_constant__ TreeView T, float rb, const float *__restrict__ Tpos,
                                                    const int32_t *__restrict__ Ipos, const __grid_constant__ typename V::Args A) {
@@ -418,6 +465,43 @@ int launch_rule_hist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *I
         RuleHist::Args A{bins, bin0, which, radius, (const char *)attr, stride, hist};
         CCG_TRY(launch_rule<RuleHist>(ctx, rb, Tpos, Ipos, A));
     }
+    return CCG_OK;
+}
+
+// Variable-length neighbour lists (CSR): counts -> offsets (exclusive scan) -> keys in traversal order -> every row sorted
+// ascending by (d2, index) with one segmented radix sort -> idx / d2.  offsets_dev: long long[n + 1] (device).
+int launch_radius_csr_count(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, long long *offsets_dev, long long *total_host) {
+    const size_t n = ctx->n;
+    RuleCount::Args A{offsets_dev};
+    CCG_TRY(launch_rule<RuleCount>(ctx, rb, Tpos, Ipos, A));
+    size_t tmp_bytes = 0;
+    CCG_CUDA(ctx, cudaMemsetAsync(offsets_dev + n, 0, sizeof(long long), ctx->stream));
+    CCG_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, offsets_dev, offsets_dev, (int)(n + 1), ctx->stream));
+    CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+    CCG_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->sort_tmp.p, tmp_bytes, offsets_dev, offsets_dev, (int)(n + 1), ctx->stream));
+    ctx->stats.launches += 2;
+    CCG_CUDA(ctx, cudaMemcpyAsync(total_host, offsets_dev + n, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+    CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return CCG_OK;
+}
+
+int launch_radius_csr_fill(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, const long long *offsets_dev, long long total,
+                           int32_t *idx_dev, float *d2_dev) {
+    if (total <= 0) return CCG_OK;
+    if (total > 0x7fffffffLL) return set_error(ctx, CCG_ERR_UNSUPPORTED, "radius lists: %lld neighbours in total exceed 2^31-1 per call", total);
+    const size_t n = ctx->n;
+    CCG_CUDA(ctx, ctx->tmp[2].reserve((size_t)total * 16 + 64));
+    unsigned long long *k0 = ctx->tmp[2].as<unsigned long long>(), *k1 = k0 + total;
+    RuleFill::Args A{offsets_dev, k0};
+    CCG_TRY(launch_rule<RuleFill>(ctx, rb, Tpos, Ipos, A));
+    cub::DoubleBuffer<unsigned long long> dk(k0, k1);
+    size_t tmp_bytes = 0;
+    CCG_CUDA(ctx, cub::DeviceSegmentedSort::SortKeys(nullptr, tmp_bytes, dk, (int)total, (int)n, offsets_dev, offsets_dev + 1, ctx->stream));
+    CCG_CUDA(ctx, ctx->sort_tmp.reserve(tmp_bytes));
+    CCG_CUDA(ctx, cub::DeviceSegmentedSort::SortKeys(ctx->sort_tmp.p, tmp_bytes, dk, (int)total, (int)n, offsets_dev, offsets_dev + 1, ctx->stream));
+    k_csr_unpack<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(dk.Current(), total, idx_dev, d2_dev);
+    ctx->stats.launches += 4;
+    CCG_CUDA(ctx, cudaGetLastError());
     return CCG_OK;
 }
 

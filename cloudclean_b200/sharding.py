@@ -141,7 +141,7 @@ class SharedPinned:
     """One host array shared by the local ranks (POSIX shared memory under /dev/shm) and page-locked in every process
     (cudaHostRegister), so that each rank moves ITS slice of the input / output through its own PCIe link."""
 
-    def __init__(self, name, shape, dtype=torch.float32, create=False):
+    def __init__(self, name, shape, dtype=torch.float32, create=False, register=True):
         import os
         self.path = f"/dev/shm/{name}"
         nelem = 1
@@ -154,9 +154,17 @@ class SharedPinned:
         self.created = create
         self.t = torch.from_file(self.path, shared=True, size=nelem, dtype=dtype).view(shape)
         self.registered = False
-        if torch.cuda.is_available() and self.nbytes:
+        if register:
+            self.register()
+
+    def register(self):
+        """page-lock the mapping in this process.  Pages that were never touched are allocated HERE, on the caller's NUMA
+        node: let every rank write its own slice first (register=False, touch, barrier, register) so that each GPU's copies
+        go to memory next to its own PCIe root."""
+        if not self.registered and torch.cuda.is_available() and self.nbytes:
             rc = torch.cuda.cudart().cudaHostRegister(self.t.data_ptr(), self.nbytes, 0)
             self.registered = int(rc) == 0
+        return self.registered
 
     def close(self):
         import os

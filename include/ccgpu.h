@@ -197,6 +197,15 @@ int ccg_pca_knn_features_scatter(ccg_ctx *ctx, int k, int cov_norm, const float 
  * runs ccg_unpermute once per array on its own HBM. */
 int ccg_pca_knn_features_shard(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, int rank, int world,
                                int chunk_points, int sorted_rows, float *eig3, float *normal4, float *feat7);
+/* Variable-length neighbour lists in CSR form — what KdTreeFLANN::radiusSearch(i, r, idx, d2, max_nn) fills into its
+ * std::vector<int> / std::vector<float> (cv.h:98, cv.h:162, cv.cpp:273, featureeval/utils.h:50,145, markov.cpp:360-367) for
+ * EVERY cap: max_nn = 0 (all points inside r) or any positive cap (the max_nn nearest, index-ordered ties).  Row i is
+ * idx[offsets[i] .. offsets[i+1]) / d2[...], ascending (d2, index), self first.  offsets: int64[n+1].  Call once with
+ * idx = d2 = NULL to learn *total (and offsets), then with buffers of `capacity` >= *total entries.  One call handles up to
+ * 2^31-1 neighbours in total.  ccg_radius remains the fixed-width form for caps <= 64. */
+int ccg_radius_csr(ccg_ctx *ctx, double r, int max_nn, int strict_lt, int64_t *offsets, int32_t *idx, float *d2, int64_t capacity,
+                   int64_t *total);
+
 /* Owner-routed variant of ccg_pca_knn_features_shard for end-to-end multi-GPU runs: the output rows are partitioned by
  * ORIGINAL index — rank o owns rows [o * rows_per_rank, (o + 1) * rows_per_rank) — and this rank stores every row it
  * computes (its interleaved chunks of the curve order) at local row (i - o * rows_per_rank) of rank o's arrays,

@@ -542,6 +542,27 @@ def test_reductions_without_a_list(gpu_ctx, r, max_nn):
         assert np.array_equal(gi, oracle.neighbour_hist(pts, r, max_nn, bins, attr=inten))
 
 
+@pytest.mark.parametrize("name", ["uniform", "lattice_ties", "clusters_outliers", "n2"])
+@pytest.mark.parametrize("r,cap,strict", [(0.2, 0, True), (0.3, 100, True), (0.15, 20, False), (0.5, 700, True)])
+def test_radius_csr_lists(gpu_ctx, name, r, cap, strict):
+    """ccg_radius_csr: the variable-length rows radiusSearch fills into its vectors, for every cap (0 = all inside r), bit-exact
+    in indices AND distances against the oracle's kd-tree search, rows ascending (d2, index)."""
+    pts = SMALL[name]
+    n = pts.shape[0]
+    T = oracle.Tree(pts)
+    gpu_ctx.set_cloud(pts)
+    off, idx, d2 = gpu_ctx.radius_csr(r, cap, strict_lt=strict, device_out=False)
+    total = T.radius(r, strict_lt=strict, lists=False)["total"]
+    eff = total if (cap == 0 or cap >= n) else np.minimum(total, cap)          # FLANN caps only when 0 < max_nn < n
+    assert off[0] == 0 and np.array_equal(np.diff(off), eff)
+    width = int(max(1, eff.max()))
+    ref = T.radius(r, cap=width, strict_lt=strict)
+    rows = np.repeat(np.arange(n), eff)
+    cols = np.arange(off[-1]) - np.repeat(off[:-1], eff)
+    assert np.array_equal(idx, ref["idx"][rows, cols])
+    assert np.array_equal(d2, ref["d2"][rows, cols])
+
+
 def test_capped_radius_ties_follow_the_index_order(gpu_ctx):
     """A cap that cuts through a class of equidistant candidates (integer lattice): the admitted ones are those with the
     smallest indices, exactly as the (d2, index) order of the oracle's kd-tree search says."""

@@ -10,12 +10,12 @@ run() {  # $1 = tag, $2 = nproc, $3 = scan cfg, rest = env assignments
 import json
 try:
     d = json.loads(open("gpurun_out/bench_${tag}.json").read().strip().splitlines()[-1])
-    print({k: d.get(k) for k in ("value", "ms_per_step", "stage_ms", "outputs_match_n1", "e2e_outputs_match_n1")}, "e2e", d["e2e"]["value"], d["e2e"]["ms_per_step"], d.get("other_configs"))
+    print({k: d.get(k) for k in ("value", "ms_per_step", "stage_ms", "outputs_match_n1", "e2e_outputs_match_n1")}, "e2e", d["e2e"]["value"], d["e2e"]["ms_per_step"], d["e2e"].get("stage_ms"))
 except Exception as e:
     print("no json:", e)
 PY
 }
-run n8_pull 8 3 CCG_BENCH_REPL=pull
-run n8_bcast 8 3 CCG_BENCH_REPL=bcast
-run n4_pull 4 3 CCG_BENCH_REPL=pull
-run n8_cfg4 8 4 CCG_BENCH_REPL=pull
+run n8_pull_staged 8 3 CCG_BENCH_REPL=pull CCG_BENCH_OUT=staged
+run n8_pull_route 8 3 CCG_BENCH_REPL=pull CCG_BENCH_OUT=route
+run n8_cfg4_staged 8 4 CCG_BENCH_REPL=pull CCG_BENCH_OUT=staged
+run n8_cfg4_route 8 4 CCG_BENCH_REPL=pull CCG_BENCH_OUT=route
