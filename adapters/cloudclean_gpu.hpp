@@ -297,8 +297,29 @@ bool knnGraph(Session &s, const PointT *points, size_t n, int k, double inverse_
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// KdTreeFLANN::radiusSearch(i, radius, k_indices, k_sqr_distances, max_nn) for EVERY point of the cloud at once
+// (cv.h:98, cv.h:162, cv.cpp:273, featureeval/utils.h:50,145, markov.cpp:360-367): row i of the result is
+// indices[offsets[i] .. offsets[i+1]) / sqr_distances[...], ascending distance, the point itself first; max_nn = 0
+// means every point inside the radius, any positive cap keeps the max_nn nearest.  Returns false on failure.
+// ---------------------------------------------------------------------------------------------------------
+template <class PointT>
+bool radiusSearchAll(Session &s, const PointT *points, size_t n, double radius, unsigned max_nn, std::vector<int64_t> &offsets,
+                     std::vector<int> &indices, std::vector<float> &sqr_distances) {
+    offsets.assign(n + 1, 0);
+    indices.clear(); sqr_distances.clear();
+    if (!s.ok() || !s.setInputCloud(points, n)) return false;
+    if (n == 0) return true;
+    int64_t total = 0;
+    if (!s.check(ccg_radius_csr(s.ctx(), radius, (int)max_nn, 1, offsets.data(), nullptr, nullptr, 0, &total))) return false;
+    indices.resize((size_t)total); sqr_distances.resize((size_t)total);
+    if (total == 0) return true;
+    return s.check(ccg_radius_csr(s.ctx(), radius, (int)max_nn, 1, offsets.data(), reinterpret_cast<int32_t *>(indices.data()),
+                                  sqr_distances.data(), total, &total));
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // normal_stdev<PointT,NormalT> (cv.h:123-206) and stdev_dist (cv.cpp:166-230): one float per point, arithmetic and
-// quirks as written in the reference (include/ccgpu.h).  max_nn must be in [1, CCG_MAX_K].
+// quirks as written in the reference (include/ccgpu.h).  Any max_nn the reference accepts (0 = every point inside r).
 // ---------------------------------------------------------------------------------------------------------
 template <class PointT, class NormalT>
 std::shared_ptr<std::vector<float>> normal_stdev(Session &s, const PointT *cloud, const NormalT *normals, size_t n, double radius, int max_nn) {

@@ -464,6 +464,28 @@ int main() {
         s.setCancelFlag(nullptr);
     }
 
+    // ---- radiusSearch for every point, variable-length rows, uncapped and with a cap beyond the list kernels ----
+    {
+        for (unsigned cap : {0u, 100u}) {
+            std::vector<int64_t> off; std::vector<int> ri; std::vector<float> rd;
+            const double radius = 0.25;
+            CHECK(radiusSearchAll(s, pts.data(), n, radius, cap, off, ri, rd), "radiusSearchAll failed (%s)", s.lastError().c_str());
+            const float r2 = (float)(radius * radius);
+            int bad = 0; size_t widest = 0;
+            for (size_t i = 0; i < n && off.size() == n + 1; ++i) {
+                size_t m = 0;
+                while (m < nbrs[i].size() && nbrs[i][m].first < r2 && (cap == 0 || m < cap)) ++m;
+                const size_t got = (size_t)(off[i + 1] - off[i]);
+                widest = std::max(widest, got);
+                if (got != m) { ++bad; continue; }
+                for (size_t j = 0; j < m; ++j)
+                    if (ri[off[i] + j] != nbrs[i][j].second || rd[off[i] + j] != nbrs[i][j].first) { ++bad; break; }
+            }
+            std::printf("radiusSearchAll(max_nn=%u): %zu entries, widest row %zu, %d rows differ\n", cap, ri.size(), widest, bad);
+            CHECK(bad == 0, "radiusSearchAll(max_nn=%u) differs at %d points", cap, bad);
+        }
+    }
+
     // ---- the threading contract of NormalEstimator (normalestimation.cpp:196, :305-306): estimateNormals runs on a
     //      std::async worker with a Session of its own while the GUI thread keeps using ITS Session, and the GUI thread
     //      raises PointCloud::deleting_ at any moment.  Every outcome must be a full result or an empty one (cancelled),

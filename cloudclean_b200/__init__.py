@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libccgpu.so")
+LIB_PATH = os.environ.get("CCG_LIBRARY") or os.path.join(_HERE, "libccgpu.so")     # CCG_LIBRARY: an experiment build of the same ABI
 
 COV_SCATTER, COV_NM1, COV_N = 0, 1, 2
 MAX_K = 64

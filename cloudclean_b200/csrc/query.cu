@@ -575,7 +575,11 @@ __device__ __noinline__ unsigned prefilter_blk(const float4 *blk, const float4 &
     const float thr = __fadd_ru(__fsub_ru(bound, qq), __fmul_ru(3.0517578125e-5f, __fadd_ru(qq, bound)));
     const f32x2 AX = pack2(2.f * qx, 2.f * qx), AY = pack2(2.f * qy, 2.f * qy), AZ = pack2(2.f * qz, 2.f * qz), TH = pack2(thr, thr);
     unsigned m = 0;
-#pragma unroll
+#ifndef CCG_PF_UNROLL
+#define CCG_PF_UNROLL 16
+#endif
+    constexpr int kPfUnroll = CCG_PF_UNROLL;
+#pragma unroll kPfUnroll
     for (int p = 0; p < kLeaf / 2; ++p) {
         const float4 a = blk[1 + 2 * p], b = blk[2 + 2 * p];      // (X0 X1 Y0 Y1), (Z0 Z1 W0 W1)
         f32x2 s = add2(TH, pack2(b.z, b.w));
@@ -1262,7 +1266,10 @@ static void launch_sel3(const TreeView &T, const TileParams &P, cudaStream_t st)
 // of spills) 28.10 ms — occupancy beats registers here.  CCG_SEL_MINB=12 selects the 80-register build of K = 20 for A/B runs.
 template <int K>
 static void launch_sel(const TreeView &T, const TileParams &P, int tma, int minb, cudaStream_t st) {
-    constexpr int kDef = K > 32 ? 6 : (K > 24 ? 10 : (K == 20 ? 16 : 12));
+#ifndef CCG_MINB20
+#define CCG_MINB20 16
+#endif
+    constexpr int kDef = K > 32 ? 6 : (K > 24 ? 10 : (K == 20 ? CCG_MINB20 : 12));
     if constexpr (K == 20) {
         if (minb == 12) { if (tma) launch_sel3<K, true, 12>(T, P, st); else launch_sel3<K, false, 12>(T, P, st); return; }
     }

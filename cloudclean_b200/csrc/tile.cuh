@@ -250,7 +250,12 @@ __device__ __forceinline__ void features7(float l0, float l1, float l2, int form
 }
 
 // moments of (p - q): m = {sx sy sz sxx sxy sxz syy syz szz}, cnt points -> outputs for one row
-__device__ __forceinline__ void pca_finish(const PcaOut &o, const float4 &q, const float m[9], int cnt, size_t row) {
+#ifdef CCG_NOINLINE_FIN
+#define CCG_FIN_INLINE __noinline__
+#else
+#define CCG_FIN_INLINE __forceinline__
+#endif
+__device__ CCG_FIN_INLINE void pca_finish(const PcaOut &o, const float4 &q, const float m[9], int cnt, size_t row) {
     float *eig3 = o.eig3, *normal4 = o.normal4, *feat7 = o.feat7;
     if (o.route_world > 1) {
         const unsigned owner = (unsigned)row / o.route_rows;

@@ -1,5 +1,5 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 2400 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_gpu.log
-CCG_KEY_BITS_LIST=16,18,21 timeout 1200 python tools/keybits_probe.py 3,4 2>&1 | tee gpurun_out/keybits.log
+timeout 1500 python tools/lib_variants.py build/variants/pf4.so build/variants/pf2.so build/variants/minb14.so build/variants/finnoinl.so 2>&1 | tee gpurun_out/lib_variants.log
+CCG_SEL_CHUNKS=1 SHRINK=1 bash tools/gpu_prof.sh k_tile_sel prof_sel_r02_final

@@ -15,5 +15,6 @@ $CMD > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"^k_|Device" -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu launches rc=$?"
 python tools/launch_times.py gpurun_out/launches.csv > gpurun_out/launches.txt 2>&1; tail -22 gpurun_out/launches.txt
-CCG_SEL_CHUNKS=1 bash tools/gpu_prof.sh k_tile_sel prof_sel_r02_final
+CCG_SEL_CHUNKS=1 SHRINK=1 bash tools/gpu_prof.sh k_tile_sel prof_sel_r02_final
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
 ./adapters/test_adapters > gpurun_out/adapters.log 2>&1; echo "adapters rc=$?"

@@ -9,7 +9,7 @@ s = synth.config_scan(3, device="cuda", shrink=shrink)
 pts = s["points"]; n = pts.shape[0]
 ctx = cc.Context(0)
 ctx.set_cloud(pts)
-eig = torch.empty((n, 3), device="cuda"); nrm = torch.empty((n, 4), device="cuda")
+eig = torch.empty((n, 3), device="cuda"); nrm = torch.empty((n, 4), device="cuda"); feat = torch.empty((n, 7), device="cuda")
 for _ in range(2):
-    ctx.pca_knn_into(20, 1, eig, nrm)
+    ctx.pca_knn_features_into(20, 1, 0, eig, nrm, feat)      # the bench call
 print(n, ctx.stats())
