@@ -576,7 +576,7 @@ __device__ __noinline__ unsigned prefilter_blk(const float4 *blk, const float4 &
     const f32x2 AX = pack2(2.f * qx, 2.f * qx), AY = pack2(2.f * qy, 2.f * qy), AZ = pack2(2.f * qz, 2.f * qz), TH = pack2(thr, thr);
     unsigned m = 0;
 #ifndef CCG_PF_UNROLL
-#define CCG_PF_UNROLL 16
+#define CCG_PF_UNROLL 4        // 16 pairs in 4 rounds: the fully unrolled loop was 4.5 % slower (instruction fetch; profiles/r02_sel_v16_codesize_variants.log)
 #endif
     constexpr int kPfUnroll = CCG_PF_UNROLL;
 #pragma unroll kPfUnroll
@@ -609,13 +609,13 @@ struct ValList {
         key[0] = fminf(key[0], c);
     }
     __device__ __forceinline__ void tighten() { bound = bound < 0.f ? -1.f : fminf(rb, key[K - 1]); }
-    // Own leaf when the list has no pinned slots (k == K): the 32 exact distances of the lane are sorted in registers by a
+    // Own leaf: the 32 exact distances of the lane are sorted in registers by a
     // bitonic network (240 compare-exchanges = 480 FMNMX; the stages that only feed outputs beyond K are dead code) and the K
     // smallest become the list — against 32 ordered inserts of 2K FMNMX each (query 29.1 -> 28.2 ms on the 30 M scan).
     // Extending the idea to the two curve neighbours (sort + bitonic merge with the list, ~0.95 k instead of 1.7 k
     // instructions per leaf) cut the instruction count by another 5 % and LOST time (28.2 -> 28.7 ms): the straight-line
     // networks are fetched once per tile, stall no_instruction rose 3.4 -> 4.6 (profiles/r02_sel_v17_merge_all_*).
-    __device__ __forceinline__ void seed_sorted(const float4 &q, const float4 *pts) {
+    __device__ __forceinline__ void seed_sorted(const float4 &q, const float4 *pts, int k) {
         float d[kLeaf];
 #pragma unroll
         for (int j = 0; j < kLeaf; ++j) {
@@ -640,6 +640,16 @@ struct ValList {
         }
 #pragma unroll
         for (int i = 0; i < K; ++i) key[i] = i < kLeaf ? d[i < kLeaf ? i : 0] : INFINITY;
+        // k < K: the K - k front slots are pinned to -1 and the sorted values start behind them — a right shift by the
+        // warp-uniform amount K - k, done as log2(K) conditional shifts by constant distances (register indices stay static)
+        const int shift = K - k;
+#pragma unroll
+        for (int b = 1; b < K; b <<= 1) {
+            if (shift & b) {
+#pragma unroll
+                for (int i = K - 1; i >= 0; --i) key[i] = i >= b ? key[i - b < 0 ? 0 : i - b] : -1.f;
+            }
+        }
         tighten();
     }
     // every staged point scored exactly and inserted in turn (own leaf with pinned slots)
@@ -698,7 +708,11 @@ __device__ __forceinline__ int refine_list(const TreeView &T, SelScratch &S, int
         if (i < nlist) {
             leaf = S.w.list[i];
             const float4 lo = T.lo[0][leaf], hi = T.hi[0][leaf];
-#pragma unroll 4
+#ifndef CCG_REFINE_UNROLL
+#define CCG_REFINE_UNROLL 4
+#endif
+            constexpr int kRefUnroll = CCG_REFINE_UNROLL;
+#pragma unroll kRefUnroll
             for (int j = 0; j < kLeaf; ++j) want |= d2_point_box(S.w.ws.leaf[j], lo, hi) <= S.sbound[j];
         }
         const unsigned m = __ballot_sync(kFull, want);
@@ -764,6 +778,7 @@ __device__ __forceinline__ void drain_queue(const TreeView &T, SelScratch &S, in
 __device__ __forceinline__ int squeeze_queue(SelScratch &S, int cnt, int lane) {
     const int maxc = __reduce_max_sync(kFull, cnt);
     int w = 0;
+#pragma unroll 1
     for (int e = 0; e < maxc; ++e) {
         if (e < cnt) {
             const unsigned m = S.q.qmask[e * 32 + lane];
@@ -789,7 +804,7 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     S.w.ws.leaf[lane] = q;
     if (lane < 3) S.w.list[kSlotHome + lane] = tile + (lane == 0 ? 0 : (lane == 1 ? -1 : 1));
     __syncwarp();
-    if (P.seed_net && P.k == K) v.seed_sorted(q, S.w.ws.leaf);
+    if (P.seed_net) v.seed_sorted(q, S.w.ws.leaf, P.k);
     else v.score_direct(q, S.w.ws.leaf);
     // ---- the two neighbours along the curve, scored directly as well.  (Queueing them like the listed leaves was measured:
     //      their survivors fill half the lanes, the pooled drain needs as many rounds as the direct loop has candidates, and
@@ -809,9 +824,10 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     //      candidate list hundreds of leaves long) --------------------------------------------------------------
     {
         float b = v.bound >= 0.f ? v.bound : INFINITY;
-#pragma unroll
+        // (rolled on purpose, like the two queue loops below: the kernel is short of instruction-fetch bandwidth — 26.40 -> 25.78 ms)
+#pragma unroll 1
         for (int kk = 2; kk <= 32; kk <<= 1) {
-#pragma unroll
+#pragma unroll 1
             for (int j = kk >> 1; j > 0; j >>= 1) {
                 const float o = __shfl_xor_sync(kFull, b, j);
                 const bool up = ((lane & kk) == 0) == ((lane & j) == 0);
@@ -977,6 +993,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
     int tot = 0;
     {
         const int maxc = __reduce_max_sync(kFull, cnt);
+#pragma unroll 1
         for (int e = 0; e < maxc; ++e)
             if (e < cnt) tot += __popc(S.q.qmask[e * 32 + lane]);
     }

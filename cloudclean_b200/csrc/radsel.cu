@@ -43,14 +43,6 @@ __device__ __forceinline__ int bin_path(float d2, float scale, int lvl, const in
     return b;
 }
 
-struct CountV {                       // pass 0: how many candidates inside the radius
-    float bound; int count;
-    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
-#pragma unroll 8
-        for (int j = 0; j < kLeaf; ++j) count += d2_point(q, leaf[j]) <= bound ? 1 : 0;
-    }
-};
-
 struct HistV {                        // level pass: histogram of the candidates inside the chosen bins
     float bound, scale; int lvl; int sel[kSelLevels];
     unsigned *hist;                   // this lane's column: bin b at hist[b * 32]
@@ -124,23 +116,28 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     unsigned *hist = &s_hist[warp][lane];
     float t_out = rb; int i_out = INT_MAX;
 
-    CountV c0; c0.bound = active ? rb : -1.f; c0.count = 0;
-    traverse_tile(T, tile, q, c0, s_ws[warp]);
-    bool need = active && c0.count > max_nn;
-    if (!__any_sync(kFull, need)) { Tpos[pos] = t_out; Ipos[pos] = i_out; return; }
-
+    // The first histogram pass (level 0, every lane) also counts the neighbourhood: count = sum of the bins.
     const float scale = rb > 0.f ? __fdiv_rn((float)kSelBins, rb) : 0.f;
     int sel[kSelLevels] = {0, 0, 0, 0};
-    int lvl = 0, kprime = max_nn, nb = c0.count;          // lvl: levels THIS lane has refined; nb: candidates left in its bracket
-    while (__any_sync(kFull, need && nb > kSelKeep && lvl < kSelLevels)) {
-        const bool mine = need && nb > kSelKeep && lvl < kSelLevels;
+    int lvl = 0, kprime = max_nn, nb = 0;                 // lvl: levels THIS lane has refined; nb: candidates left in its bracket
+    bool need = active, first = true;
+    while (first || __any_sync(kFull, need && nb > kSelKeep && lvl < kSelLevels)) {
+        const bool mine = first ? active : (need && nb > kSelKeep && lvl < kSelLevels);
 #pragma unroll 8
         for (int b = 0; b < kSelBins; ++b) hist[b * 32] = 0;
         HistV h; h.bound = mine ? rb : -1.f; h.scale = scale; h.lvl = lvl; h.hist = hist;
 #pragma unroll
         for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
         traverse_tile(T, tile, q, h, s_ws[warp]);
-        if (mine) {
+        if (first) {
+            int c = 0;
+            for (int b = 0; b < kSelBins; ++b) c += (int)hist[b * 32];
+            nb = c;
+            need = active && c > max_nn;
+            first = false;
+            if (!__any_sync(kFull, need)) { Tpos[pos] = t_out; Ipos[pos] = i_out; return; }   // the cap binds nowhere in this tile
+        }
+        if (mine && need && (lvl > 0 || nb > kSelKeep)) {
             int cum = 0, b = 0;
             for (; b < kSelBins - 1; ++b) {
                 const int hb = (int)hist[b * 32];
@@ -155,6 +152,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
         }
     }
     // select pass: the candidates inside the lane's bracket, ranked exactly
+    bool tie_pass = false;                                 // does this lane need the index tie-break at T?
     {
         KeepV kv; kv.bound = need ? rb : -1.f; kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
         kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY;
@@ -163,26 +161,28 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
         traverse_tile(T, tile, q, kv, s_ws[warp]);
         if (need) {
             if (kv.cnt <= kSelKeep) {
-                // the kprime-th smallest of the kept values: v with #{< v} < kprime <= #{<= v}
+                // the kprime-th smallest of the kept values: v with #{< v} < kprime <= #{<= v}.  Every candidate AT that value
+                // lies in this bracket, so #{<= v} == kprime says the tie class fits the cap and no index decides anything.
                 for (int i = 0; i < kv.cnt; ++i) {
                     const float vi = kv.vals[i * 32];
                     int lt = 0, le = 0;
                     for (int j = 0; j < kv.cnt; ++j) { const float vj = kv.vals[j * 32]; lt += vj < vi ? 1 : 0; le += vj <= vi ? 1 : 0; }
-                    if (lt < kprime && kprime <= le) { t_out = vi; break; }
+                    if (lt < kprime && kprime <= le) { t_out = vi; tie_pass = le > kprime; break; }
                 }
             } else if (kv.vmin == kv.vmax) {
                 t_out = kv.vmin;                             // a bracket of identical values: the threshold is that value
+                tie_pass = true;
             } else {
                 atomicOr(err, 1);
             }
         }
     }
     __syncwarp();
-    // tie pass: with T known, how many candidates lie strictly below it and which indices tie AT it
-    {
-        TieV tv; tv.bound = need ? t_out : -1.f; tv.less = 0; tv.tied = 0; tv.idx = reinterpret_cast<int *>(hist);
+    // tie pass (only when some lane's tie class overflows its cap): how many candidates lie strictly below T, which indices tie AT it
+    if (__any_sync(kFull, tie_pass)) {
+        TieV tv; tv.bound = tie_pass ? t_out : -1.f; tv.less = 0; tv.tied = 0; tv.idx = reinterpret_cast<int *>(hist);
         traverse_tile(T, tile, q, tv, s_ws[warp]);
-        if (need) {
+        if (tie_pass) {
             const int m = max_nn - tv.less;                  // tied candidates the cap still admits (>= 1)
             if (tv.tied > m) {
                 if (m <= kSelKeep) {

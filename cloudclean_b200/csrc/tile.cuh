@@ -233,7 +233,9 @@ struct PcaOut {
 
 // a9: the 7 eigen features of Markov::mkFeatureVector (markov.cpp:449-475) from descending (l0, l1, l2).
 // formula_set 0 = exactly as written there (including its slips), 1 = textbook definitions.
-__device__ __forceinline__ void features7(float l0, float l1, float l2, int formula_set, float *o) {
+// out of line on purpose: logf x3 + cbrtf are ~250 instructions that every inlining site would add to a kernel that is short of
+// instruction-fetch bandwidth (k_tile_sel: 25.78 -> 25.29 ms, profiles/r02_sel_v16_codesize_variants.log)
+static __device__ __noinline__ void features7(float l0, float l1, float l2, int formula_set, float *o) {
     o[0] = __fdiv_rn(__fsub_rn(l0, l2), l0);                 // markov.cpp:451
     o[1] = __fdiv_rn(__fsub_rn(l1, l2), l0);                 // :455
     o[2] = __fdiv_rn(l2, l0);                                // :459

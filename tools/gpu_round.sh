@@ -6,7 +6,7 @@ python -m pytest tests -m gpu -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pyte
 grep -E "passed|failed|config 5:|FAILED" gpurun_out/pytest_gpu.log | tail -12
 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 cut -c1-1500 gpurun_out/bench.json
-if [ "${REF:-1}" = "1" ]; then
+if [ "${REF:-0}" = "1" ]; then
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 cut -c1-1200 gpurun_out/bench_ref.json
 fi

@@ -12,10 +12,11 @@ ctx = cc.Context(0); q = []
 for it in range(6):
     ctx.set_cloud(pts)
     ctx.pca_knn_features_into(20, cc.COV_NM1, 0, eig, nrm, feat); q.append(ctx.stats()["ms_query"])
-print(f"{os.environ.get('CCG_LIBRARY', 'default')}: query_ms min={min(q):.2f} mean={sum(q[1:])/5:.2f} checksum={int(eig.view(torch.int32).sum(dtype=torch.int64).item())}")
+print(f"{os.environ.get('CCG_LIBRARY', 'default')} minb={os.environ.get('CCG_SEL_MINB', '16')} stage={os.environ.get('CCG_SEL_STAGE', 'tma')}: query_ms min={min(q):.2f} mean={sum(q[1:])/5:.2f} checksum={int(eig.view(torch.int32).sum(dtype=torch.int64).item())}")
 '''
-for lib in [None] + sys.argv[1:] + [None]:
-    env = dict(os.environ)
+runs = [(None, {})] + [(a, {}) for a in sys.argv[1:]] + [(None, {"CCG_SEL_MINB": "12"}), (None, {"CCG_SEL_STAGE": "ldg"}), (None, {})]
+for lib, extra in runs:
+    env = dict(os.environ); env.update(extra)
     if lib:
         env["CCG_LIBRARY"] = os.path.abspath(lib)
     else:
