@@ -433,6 +433,7 @@ def main():
     bcast_ev = []
     e2e_ev = []
     build_ms = []
+    stage_ev = []
 
     def step_device():
         if world == 1:
@@ -461,17 +462,21 @@ def main():
                 dist.all_gather_into_tensor(pack, my_slice)
             eb1.record(stream)
             bcast_ev.append((eb0, eb1))
+            # the ctx is in ASYNCHRONOUS mode here (ccg_set_async): build and query are only enqueued on the shared stream, no host
+            # round trip between the NCCL broadcast and the last kernel of the step; stage times come from events on that stream
+            eq = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            eq[0].record(stream)
             ctx.set_cloud(pack[:n])
-            sb = ctx.stats()
-            launches[0] += sb["launches_build"]; build_ms.append(sb["ms_build"])
+            eq[1].record(stream)
+            launches[0] += ctx.stats()["launches_build"]
             if out_mode == "route":
                 # every rank stores each row with the rank OWNING its original index (all NVLink ports share the traffic), then
                 # rank 0 pulls the N contiguous slices with the copy engines: no un-permute pass, no single ingress port
                 # taking scattered stores
                 ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, slices.tables[0], slices.tables[1], slices.tables[2])
-                st = ctx.stats()
-                launches[0] += st["launches"]
-                kernel_ms.append(st["ms_query"])
+                eq[2].record(stream)
+                stage_ev.append(eq)
+                launches[0] += ctx.stats()["launches"]
                 dist.all_reduce(token)
                 if rank == 0:
                     for o in range(world):
@@ -483,9 +488,9 @@ def main():
             # every rank answers its interleaved share of the curve order (8192-point chunks, round robin) and stores the rows straight into rank 0's
             # arrays over NVLink from inside the query kernel; the 1-element all_reduce is the completion barrier
             ctx.pca_knn_features_shard(K, cc.COV_NM1, 0, rank, world, p_eig, p_nrm, p_feat, sorted_rows=staged)
-            st = ctx.stats()
-            launches[0] += st["launches"]
-            kernel_ms.append(st["ms_query"])
+            eq[2].record(stream)
+            stage_ev.append(eq)
+            launches[0] += ctx.stats()["launches"]
             dist.all_reduce(token)
             if staged and rank == 0:
                 ctx.unpermute(s_eig, o_eig)
@@ -609,7 +614,14 @@ def main():
     kernel_ms.clear()
     bcast_ev.clear()
     build_ms.clear()
+    stage_ev.clear()
+    if world > 1:
+        ctx.set_async(True)
     ms_dev = timed(step_device, args.steps, args.warmup)
+    if world > 1:
+        ctx.sync()                                   # deferred errors of the asynchronous steps would surface here
+        for eq in stage_ev:
+            build_ms.append(eq[0].elapsed_time(eq[1])); kernel_ms.append(eq[1].elapsed_time(eq[2]))
     stage_extra = {}
     if world > 1:
         # per-stage picture of the sharded step: NCCL broadcast of the cloud, slowest rank's query (incl. its NVLink stores)
@@ -625,6 +637,9 @@ def main():
     bms_mean = float(np.mean(build_ms[args.warmup:]))
     e2e_ev.clear()
     ms_e2e = timed(step_host, max(2, args.steps // 2), 1)
+    if world > 1:
+        ctx.sync()
+        ctx.set_async(False)
     e2e_steps = max(2, args.steps // 2)
     e2e_stages = None
     if world > 1 and e2e_ev:

@@ -56,13 +56,13 @@ typedef struct ccg_ctx ccg_ctx;
 /* Per-call statistics of the most recent query on a ctx (device time from CUDA events on the ctx stream). */
 typedef struct ccg_stats {
     float ms_upload;           /* H2D of the cloud (0 for device-resident input) */
-    float ms_build;            /* ingest + Morton keys + radix sort + reorder + bounding-box levels */
+    float ms_build;            /* ingest + curve (Hilbert) keys + radix sort + reorder + bounding-box levels */
     float ms_query;            /* the query kernels of the last call */
     float ms_download;         /* D2H of the outputs (0 for device-resident outputs) */
     int32_t launches;          /* kernels of this library launched by the last call (build counted by set_cloud) */
     int32_t launches_build;
     int64_t n_points;
-    int64_t n_leaves;          /* 32-point leaves of the Morton order */
+    int64_t n_leaves;          /* 32-point leaves of the curve order */
     int64_t leaves_scanned;    /* leaf scans summed over query tiles (0 unless CCG_COLLECT_STATS=1) */
     int64_t deferred_queries;  /* queries finished by the warp-per-query kernel */
 } ccg_stats;
@@ -98,7 +98,7 @@ int ccg_sync(ccg_ctx *ctx);
  * 12 for packed xyz.  Host or device pointer.  The data is copied before return. */
 int ccg_set_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes);
 int64_t ccg_cloud_size(const ccg_ctx *ctx);
-/* sorted position -> original index (int32[n]); the Morton order used to shard queries across GPUs */
+/* sorted position -> original index (int32[n]); the space-filling-curve order used to shard queries across GPUs */
 int ccg_get_order(ccg_ctx *ctx, int32_t *order);
 
 /* ---- a1: exact kNN -------------------------------------------------------------------------------- */
@@ -129,7 +129,8 @@ int ccg_pca_knn_features(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoi
 
 /* ---- a4 / a5 / a6: radius + PCA (getPCA / getHist) ------------------------------------------------ */
 /* Replaces the body of getPCA<PointT> (cv.h:96-113) and getHist (cv.cpp:271-295): strict radius search with
- * the max_nn cap (0 = uncapped), `<3 neighbours -> (0,0,1)` marker (cv.h:105-109), else PCA eigenvalues
+ * the max_nn cap (0 = uncapped; ANY positive cap: 20, tests.json's 1000, markov.cpp:54's 100000 — beyond CCG_MAX_K the
+ * max_nn-th distance comes from a counting select, radsel.cu), `<3 neighbours -> (0,0,1)` marker (cv.h:105-109), else PCA eigenvalues
  * descending.  normalise_hist!=0 applies getHist's L2 normalisation (cv.cpp:293).  normal4 / count optional. */
 int ccg_pca_radius(ccg_ctx *ctx, double r, int max_nn, int cov_norm, int normalise_hist, const float *viewpoint3,
                    float *eig3, float *normal4, int32_t *count);
@@ -252,8 +253,11 @@ int ccg_voxel_downsample_fetch(ccg_ctx *ctx, float *out_points);
 int ccg_knn_graph(ccg_ctx *ctx, int k, double inverse_sigma, int32_t *idx, double *weight);
 
 /* ---- f2: radius-neighbourhood reductions (same search as a2/a3, different epilogue) ------------------------
- * Both need a neighbour cap 1 <= max_nn <= CCG_MAX_K (featureeval's default is 20, featureeval.cpp:67-68): the
- * max_nn nearest inside the radius, visited in ascending (d2, index) order.  Arithmetic and quirks are kept as written.
+ * Any max_nn the reference accepts: 0 = every point inside the radius, else the max_nn nearest (featureeval's default is
+ * 20, featureeval.cpp:67-68; the GUI value reaches the calls at featureeval.cpp:816,999,1032).  With 1 <= max_nn <=
+ * CCG_MAX_K the neighbours are visited in ascending (d2, index) order and the fp32 sums are the reference's bit for bit;
+ * with 0 or a larger cap the same neighbour SET is streamed in traversal order (sums within 1e-5 of the value range;
+ * histograms and counts exact).  Arithmetic and quirks are kept as written.
  * ccg_normal_stdev — normal_stdev<PointT,NormalT> (cv.h:123-206): per point the standard deviation of the normalised
  *   angle acos(clamp(cos,0,1))/pi between its normal and its neighbours' normals (strict kd-tree radius); `normals` is an
  *   array of structs whose first three floats are the normal (pcl::Normal: stride 32), host or device, indexed like the
@@ -267,7 +271,7 @@ int ccg_normal_stdev(ccg_ctx *ctx, double r, int max_nn, const void *normals, si
 int ccg_stdev_dist(ccg_ctx *ctx, double r, int max_nn, int use_depth, const float *centre3, float *out);
 
 /* ccg_neighbour_hist — calcDistHist (featureeval/utils.h:18-110, which = 0) and calcIntensityHist (:113-195, which = 1):
- *   hist is n*bins floats; per point, over its capped strict-radius neighbourhood (1 <= max_nn <= CCG_MAX_K), every
+ *   hist is n*bins floats; per point, over its strict-radius neighbourhood (any max_nn, 0 = uncapped), every
  *   neighbour adds float(1.0/m) to bin int((sqrt(d2)/r)*(bins-1)) [which = 0] or int(attr*(bins-1)) [which = 1, attr =
  *   one float per point at attr + i*attr_stride_bytes, e.g. &points[0].intensity with stride 32]; rows of points
  *   with fewer than 3 neighbours stay 0.  Bin indices are clamped to [0, bins-1] (the reference would index out of

@@ -686,3 +686,39 @@ def test_fpfh(gpu_ctx):
     assert (l1 > 1.0).mean() < 0.01, (l1 > 1.0).mean()
     # the descriptor is informative on this scene (not all mass in one bin)
     assert (got[~lone] > 1.0).sum(1).mean() > 3.3
+
+
+# ---- the A/B switches of DESIGN.md §3.1 change speed, never results ----------------------------------------------------
+@pytest.mark.parametrize("knob", [{"CCG_SEL_STAGE": "ldg"}, {"CCG_CURVE": "morton"}, {"CCG_KEY_BITS": "13"}, {"CCG_KEY_BITS": "21"},
+                                  {"CCG_SEL_NET": "0"}, {"CCG_SEL_DRAIN_AT": "4"}, {"CCG_SEL_MINB": "12"}, {"CCG_POINT_OVERLAP": "0"},
+                                  {"CCG_SEL_CHUNKS": "1"}])
+def test_knobs_do_not_change_results(monkeypatch, knob):
+    """Every measurement switch (staging by LDG instead of TMA, Morton instead of Hilbert order, key resolution, own-leaf
+    network off, mid-list drains, 80-register build, point kernel on the main stream, one launch) must give the oracle's
+    neighbours bit for bit and the same eigenvalues / SOR mask as the default build."""
+    scan = synth.make_scan_np(220, 160, scene="room", seed=31)
+    pts = np.ascontiguousarray(scan["points"])
+    lat = SMALL["lattice_ties"]
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        ref_eig, ref_nrm = ctx.pca_knn(20, cc.COV_NM1)
+        ref_mask, ref_md = ctx.sor_mask(30, 1.0)
+    for k_, v_ in knob.items():
+        monkeypatch.setenv(k_, v_)
+    with cc.Context(0) as ctx:
+        ctx.set_cloud(pts)
+        idx, d2 = ctx.knn(20)
+        ri, rd = oracle.Tree(pts).knn(20)
+        assert np.array_equal(idx, ri) and np.array_equal(d2, rd)
+        eig, nrm = ctx.pca_knn(20, cc.COV_NM1)
+        if "CCG_CURVE" in knob or "CCG_KEY_BITS" in knob:     # another leaf order = another fp32 summation order of the moments
+            assert np.abs(eig - ref_eig).max(1).max() <= 1e-4 * ref_eig[:, 0].max()
+            check_pca(eig, nrm, oracle.pca_lists(pts, ri, cov_norm=cc.COV_NM1))
+        else:
+            assert np.array_equal(eig, ref_eig) and np.array_equal(nrm, ref_nrm, equal_nan=True)
+        mask, md = ctx.sor_mask(30, 1.0)
+        assert np.array_equal(mask, ref_mask) and np.array_equal(md, ref_md)
+        ctx.set_cloud(lat)                                   # ties and duplicates: the point kernel decides
+        idx, d2 = ctx.knn(14)
+        ri, rd = oracle.Tree(lat).knn(14)
+        assert np.array_equal(idx, ri) and np.array_equal(d2, rd)

@@ -21,6 +21,7 @@ if [ "$N" -eq 2 ]; then
   run n2 2 3
 else
   run n8 8 3
+  run n2 2 3
   run n4 4 3
   run n8_cfg4 8 4
 fi
