@@ -703,7 +703,6 @@ def main():
         md_sorted = torch.empty((world * per2,), device=dev)
         md_orig = torch.empty((n2,), device=dev) if rank == 0 else None
         mask2 = torch.empty((n2,), dtype=torch.uint8, device=dev) if rank == 0 else None
-        h_md = torch.empty((n2,), dtype=torch.float32, pin_memory=True) if rank == 0 else None
 
         def step_sor():
             dist.broadcast(p2, 0)
@@ -713,12 +712,7 @@ def main():
             dist.all_gather_into_tensor(md_sorted, md_local)
             if rank == 0:
                 ctx.unpermute(md_sorted[:n2].view(n2, 1), md_orig.view(n2, 1))
-                h_md.copy_(md_orig, non_blocking=True)
-                torch.cuda.current_stream().synchronize()
-                d_ = h_md.numpy().astype(np.float64)
-                sm = float(np.add.accumulate(d_)[-1]); sq = float(np.add.accumulate(d_ * d_)[-1])      # index order, fp64
-                thr = sm / n2 + 1.0 * np.sqrt(max(0.0, (sq - sm * sm / n2) / (n2 - 1.0)))
-                mask2.copy_(md_orig.double() > thr)
+                ctx.sor_finish(md_orig, 1.0, mask2)          # D2H + index-order fp64 sums on the host + mask (ccg_sor_finish)
         ms_sor = timed(step_sor, 3, 1)
         if rank == 0:
             with torch.cuda.stream(stream):
@@ -728,7 +722,7 @@ def main():
             sor_line = {"points": n2, "ms": ms_sor / 3, "points_per_s": n2 * 3 / (ms_sor * 1e-3), "outliers": int(mask2.sum().item()),
                         "mask_matches_n1": bool(torch.equal(m1, mask2)), "mean_distances_match_n1": bool(torch.equal(md1, md_orig)),
                         "path": "broadcast xyz(w), replicated build, ccg_sor_mean_range per rank, all-gather of the fp32 mean distances, "
-                                "un-permute + index-order fp64 sum + mask on rank 0"}
+                                "un-permute + ccg_sor_finish (index-order fp64 sum + mask) on rank 0"}
         dist.barrier()
 
     if rank == 0:

@@ -30,7 +30,7 @@ SYMBOLS = [
     "ccg_pca_knn_range", "ccg_sor_mean_range", "ccg_unpermute", "ccg_pca_knn_features", "ccg_pca_knn_features_range",
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
     "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_fpfh", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
-    "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route", "ccg_radius_csr",
+    "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route", "ccg_radius_csr", "ccg_sor_finish",
 ]
 
 
@@ -94,6 +94,7 @@ def load_library():
     L.ccg_grid_normals.argtypes = [vp, vp, i32, i32, i32, vp, vp]
     L.ccg_pca_knn_range.argtypes = [vp, i32, i32, vp, sz, sz, vp, vp]
     L.ccg_sor_mean_range.argtypes = [vp, i32, sz, sz, vp]
+    L.ccg_sor_finish.argtypes = [vp, vp, sz, f64, vp]
     L.ccg_unpermute.argtypes = [vp, vp, sz, vp]
     L.ccg_pca_knn_features.argtypes = [vp, i32, i32, vp, i32, vp, vp, vp]
     L.ccg_pca_knn_features_range.argtypes = [vp, i32, i32, vp, i32, sz, sz, vp, vp, vp]
@@ -555,6 +556,11 @@ class Context:
 
     def sor_mean_range(self, mean_k, begin, end, mean_d_sorted):
         self._check(self.L.ccg_sor_mean_range(self.h, mean_k, begin, end, _ptr(mean_d_sorted)))
+
+    def sor_finish(self, mean_d, stddev_mul, outlier):
+        """gathered mean distances (original order, host or device) -> outlier mask into `outlier` (uint8[n], host or device)"""
+        self._settle(mean_d)
+        self._check(self.L.ccg_sor_finish(self.h, _ptr(mean_d), mean_d.shape[0], float(stddev_mul), _ptr(outlier)))
 
     def unpermute(self, rows_sorted, rows_original):
         row_bytes = rows_sorted.shape[1] * 4 if rows_sorted.ndim == 2 else 4

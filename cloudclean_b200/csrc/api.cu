@@ -1134,6 +1134,39 @@ int ccg_sor_mask(ccg_ctx *ctx, int mean_k, double stddev_mul, uint8_t *outlier, 
     return finish_call(ctx);
 }
 
+/* The second half of the statistical outlier filter for SHARDED runs: the ranks computed their mean distances with
+ * ccg_sor_mean_range and gathered them (original order); one rank turns them into the mask with the contract's arithmetic —
+ * fp64 sums in index order on the host, threshold mu + stddev_mul * sigma, compare in fp64. */
+int ccg_sor_finish(ccg_ctx *ctx, const float *mean_d, size_t n, double stddev_mul, uint8_t *outlier) {
+    CCG_TRY(begin_call(ctx, false));
+    if (n == 0) return CCG_OK;
+    if (!mean_d || !outlier) return set_error(ctx, CCG_ERR_INVALID, "NULL buffer");
+    CCG_TRY(query_begin(ctx));
+    const float *h = mean_d, *d = mean_d;
+    if (is_dev(ctx, mean_d)) {
+        CCG_CUDA(ctx, ctx->hpin[0].reserve(n * 4));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->hpin[0].p, mean_d, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        h = ctx->hpin[0].as<float>();
+    } else {
+        CCG_CUDA(ctx, ctx->tmp[0].reserve(n * 4));
+        CCG_CUDA(ctx, cudaMemcpyAsync(ctx->tmp[0].p, mean_d, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        d = ctx->tmp[0].as<float>();
+    }
+    double sum = 0.0, sq = 0.0;
+    for (size_t i = 0; i < n; ++i) { sum += (double)h[i]; sq += (double)h[i] * (double)h[i]; }
+    const double mu = sum / (double)n;
+    const double var = n > 1 ? (sq - sum * sum / (double)n) / ((double)n - 1.0) : 0.0;
+    const double thr = mu + stddev_mul * sqrt(var > 0 ? var : 0.0);
+    OutBuf oo;
+    CCG_TRY(oo.open(ctx, 0, outlier, n));
+    k_sor_mask<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d, n, thr, oo.dev<uint8_t>());
+    ctx->stats.launches++;
+    CCG_TRY(query_end(ctx));
+    CCG_TRY(oo.close());
+    return finish_call(ctx);
+}
+
 int ccg_radius_count_mask(ccg_ctx *ctx, double r, int min_neighbours, int prefilter, uint8_t *outlier) {
     CCG_TRY(begin_call(ctx, true));
     if (!(r >= 0.0) || min_neighbours < 1) return set_error(ctx, CCG_ERR_INVALID, "need r >= 0 and min_neighbours >= 1");

@@ -174,6 +174,10 @@ int ccg_pca_knn_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3
 int ccg_pca_knn_features_range(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoint3, int formula_set, size_t begin, size_t end,
                                float *eig3_sorted, float *normal4_sorted, float *feat7_sorted);
 int ccg_sor_mean_range(ccg_ctx *ctx, int mean_k, size_t begin, size_t end, float *mean_d_sorted);
+/* Second half of the filter for sharded runs: mean_d = the n gathered mean distances in ORIGINAL order (host
+ * or device); index-order fp64 sums on the host, threshold mu + stddev_mul * sigma, compare in fp64 -> outlier (n bytes, host
+ * or device).  ccg_sor_mask == ccg_sor_mean_range over the whole order + un-permute + ccg_sor_finish, bit for bit. */
+int ccg_sor_finish(ccg_ctx *ctx, const float *mean_d, size_t n, double stddev_mul, uint8_t *outlier);
 /* out[order[i]] = in[i] for rows of row_bytes (multiple of 4) bytes; in/out host or device */
 int ccg_unpermute(ccg_ctx *ctx, const void *rows_sorted, size_t row_bytes, void *rows_original);
 

@@ -722,3 +722,30 @@ def test_knobs_do_not_change_results(monkeypatch, knob):
         idx, d2 = ctx.knn(14)
         ri, rd = oracle.Tree(lat).knn(14)
         assert np.array_equal(idx, ri) and np.array_equal(d2, rd)
+
+
+def test_sor_finish_reproduces_sor_mask(gpu_ctx):
+    """ccg_sor_mean_range over the whole curve order + ccg_unpermute + ccg_sor_finish (the sharded path of SURVEY §8e, here on one
+    rank in three ranges) is ccg_sor_mask bit for bit: mean distances and mask."""
+    import torch
+    scan = synth.make_scan_np(200, 150, scene="room", seed=8)
+    pts = np.ascontiguousarray(scan["points"])
+    n = pts.shape[0]
+    gpu_ctx.set_cloud(pts)
+    mask, md = gpu_ctx.sor_mask(16, 1.5, device_out=False)
+    npad = (n + 31) // 32 * 32
+    md_sorted = torch.zeros((npad,), device="cuda")
+    torch.cuda.synchronize()
+    cuts = [0, (n // 3) // 32 * 32, (2 * n // 3) // 32 * 32, n]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        gpu_ctx.sor_mean_range(16, a, b, md_sorted[a:])
+    md_orig = torch.empty((n,), device="cuda")
+    gpu_ctx.unpermute(md_sorted[:n].view(n, 1), md_orig.view(n, 1))
+    out_dev = torch.empty((n,), dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    gpu_ctx.sor_finish(md_orig, 1.5, out_dev)
+    assert np.array_equal(md_orig.cpu().numpy(), md)
+    assert np.array_equal(out_dev.cpu().numpy(), mask)
+    out_host = np.empty(n, np.uint8)
+    gpu_ctx.sor_finish(md, 1.5, out_host)                    # host in, host out
+    assert np.array_equal(out_host, mask)
