@@ -508,6 +508,14 @@ constexpr int kQCap = 20;              // queue entries per lane: listed leaves 
 constexpr int kSlotHome = 253;         // list[253] / [254] / [255] = own leaf / previous / next along the curve
 constexpr int kListMax = 252;          // listed leaves a tile may keep after the per-query refinement (u8 slots)
 
+// The rare second try of the candidate list (wide or split tiles) stays out of line: k_tile_sel is short of instruction-fetch
+// bandwidth, and this copy of the list walk is executed by a few tiles in a thousand.
+static __device__ __noinline__ int collect_leaves_split(const TreeView &T, int tile, const float4 &tlo, const float4 &thi, float rmax,
+                                                        const float4 &q, float bound, WarpScratch2 &w, int (*queue)[kQueueCap]) {
+    make_sub_boxes(q, bound, bound >= 0.f, w);
+    return collect_leaves<true>(T, tile, tlo, thi, rmax, w, queue);
+}
+
 struct alignas(16) SelScratch {
     WarpScratch2 w;                        // w.ws.leaf: the 32 queries; w.list (+ the home leaves at [253..255]); w.sub
     union {
@@ -805,19 +813,27 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     if (lane < 3) S.w.list[kSlotHome + lane] = tile + (lane == 0 ? 0 : (lane == 1 ? -1 : 1));
     __syncwarp();
     if (P.seed_net) v.seed_sorted(q, S.w.ws.leaf, P.k);
+#ifdef CCG_SCORE_TWO_SITES                 // A/B build only: the own leaf's direct scoring as a second inlined copy
     else v.score_direct(q, S.w.ws.leaf);
-    // ---- the two neighbours along the curve, scored directly as well.  (Queueing them like the listed leaves was measured:
-    //      their survivors fill half the lanes, the pooled drain needs as many rounds as the direct loop has candidates, and
-    //      pass 2 then walks 44 instead of 31 rounds per tile: 28.1 -> 32.6 ms, profiles/r02_sel_v15_*.) ---------------------
+    const int h0 = 1;
+#else
+    const int h0 = P.seed_net ? 1 : 0;
+#endif
+    // ---- the own leaf without the network, and the two neighbours along the curve, scored directly through ONE call site.
+    //      (Queueing the neighbours like the listed leaves was measured: their survivors fill half the lanes, the pooled drain
+    //      needs as many rounds as the direct loop has candidates, and pass 2 then walks 44 instead of 31 rounds per tile:
+    //      28.1 -> 32.6 ms, profiles/r02_sel_v15_*.) ---------------------------------------------------------------------
     int first = 0, pend = 0;
 #pragma unroll 1
-    for (int h = 1; h < 3; ++h) {
-        const int leaf = tile + (h == 1 ? -1 : 1);
+    for (int h = h0; h < 3; ++h) {
+        const int leaf = tile + (h == 0 ? 0 : (h == 1 ? -1 : 1));
         if (leaf < 0 || leaf >= T.count[0]) continue;
-        const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
-        __syncwarp();
-        S.w.ws.leaf[lane] = p;
-        __syncwarp();
+        if (h) {
+            const float4 p = T.pts[(size_t)leaf * kLeaf + lane];
+            __syncwarp();
+            S.w.ws.leaf[lane] = p;
+            __syncwarp();
+        }
         v.score_direct(q, S.w.ws.leaf);
     }
     // ---- isolated lanes -> point kernel (a lane whose bound is far above the warp's median would make the tile's
@@ -846,8 +862,7 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     S.sbound[lane] = v.bound;
     nlist = collect_leaves<false>(T, tile, tlo, thi, rmax, S.w, S.queue);
     if (nlist < 0) {                       // wide or split tile: describe it by 8 sub-boxes and try again
-        make_sub_boxes(q, v.bound, v.bound >= 0.f, S.w);
-        nlist = collect_leaves<true>(T, tile, tlo, thi, rmax, S.w, S.queue);
+        nlist = collect_leaves_split(T, tile, tlo, thi, rmax, q, v.bound, S.w, S.queue);
         if (nlist < 0) return -5;
     }
     if (TMA) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the BFS queues were written over the staging ring
@@ -860,19 +875,6 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
     const int drain_at = P.drain_at;
     if (nlist > 0) stg.issue(T, S, S.w.list[0], seq, lane);
     for (int i = 0; i < nlist; ++i) {
-        if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
-            // a full queue: score what is pending, drop the entries that emptied, give up only if it is still full
-            const int rounds = __reduce_max_sync(kFull, pend);
-            drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
-            cnt = squeeze_queue(S, cnt, lane);
-            first = cnt; pend = 0;
-            if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
-            if (__reduce_max_sync(kFull, cnt) >= kQCap - 3) {
-                stg.await(S, seq, lane);                 // no copy may be in flight when the block retires
-                ++seq;
-                return -3;
-            }
-        }
         const float4 *blk = stg.await(S, seq, lane);
         if (i + 1 < nlist) {
             __syncwarp();                                // every lane is done with the stage the next copy overwrites
@@ -886,12 +888,20 @@ __device__ __forceinline__ int sel_pass1(const TreeView &T, const TileParams &P,
             ++cnt;
             pend += __popc(pm);
         }
+        // ONE drain site (code size): pending survivors reached the trigger, the last leaf was filtered, or the queue is
+        // full — then score what is pending and drop the entries that emptied.
         const int rounds = __reduce_max_sync(kFull, pend);
-        if (rounds >= drain_at || (i + 1 == nlist && rounds > 0)) {
+        const bool full = __reduce_max_sync(kFull, cnt) >= kQCap - 3;
+        if (rounds >= drain_at || ((i + 1 == nlist || full) && rounds > 0)) {
             drain_queue<K>(T, S, lane, q, v, first, cnt, rounds);
             cnt = squeeze_queue(S, cnt, lane);
             first = cnt; pend = 0;
             if (st5 && lane == 0) { atomicAdd(st5 + 6, 1ull); atomicAdd(st5 + 10, (unsigned long long)rounds); }
+        }
+        if (full && i + 1 < nlist && __reduce_max_sync(kFull, cnt) >= kQCap - 3) {
+            stg.await(S, seq, lane);                     // still full after the drain: that many ties.  No copy may be in
+            ++seq;                                       // flight when the block retires
+            return -3;
         }
     }
     return nlist;
@@ -906,7 +916,9 @@ __device__ __forceinline__ void sor_finish(const float *key, int k, int mean_k, 
     mean_d[row] = (float)(s / (double)mean_k);
 }
 
-template <int K, int MODE, bool TMA, int MINB>
+// STATS: the counters behind CCG_VERBOSE_STATS live in an instantiation of their own, so that the measured kernel carries none
+// of their code (the kernel is short of instruction-fetch bandwidth: every removed instruction shows in the time).
+template <int K, int MODE, bool TMA, int MINB, bool STATS>
 __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ TreeView T, const __grid_constant__ TileParams P) {
     __shared__ SelScratch s_ws[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -921,6 +933,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
         if (tile >= T.count[0]) return;
     }
     SelScratch &S = s_ws[warp];
+    unsigned long long *const st5 = STATS ? P.stat_scanned : nullptr;
     if (TMA) {
         if (lane == 0) {
 #pragma unroll
@@ -943,7 +956,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
     unsigned seq = 0;
     int cnt = 0, nlist = 0;
     bool lone = false;
-    const int scanned = sel_pass1<K, TMA>(T, P, tile, tlo, thi, q, v, S, stg, seq, cnt, nlist, lone, P.stat_scanned);
+    const int scanned = sel_pass1<K, TMA>(T, P, tile, tlo, thi, q, v, S, stg, seq, cnt, nlist, lone, st5);
     if (scanned >= 0) {                             // isolated lanes of a dense tile -> point kernel
         const unsigned lm = __ballot_sync(kFull, lone);
         if (lm) {
@@ -962,7 +975,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
         const unsigned am = __ballot_sync(kFull, active);
         if (lane == 0) {
             base = atomicAdd(P.defer_count, __popc(am));
-            if (P.stat_scanned) { atomicAdd(P.stat_scanned + 3, 1ull); atomicAdd(P.stat_scanned + 4 - scanned, 1ull); }
+            if (st5) { atomicAdd(st5 + 3, 1ull); atomicAdd(st5 + 4 - scanned, 1ull); }
         }
         base = __shfl_sync(kFull, base, 0);
         if (active) {
@@ -972,7 +985,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
         }
         return;
     }
-    if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
+    if (st5 && lane == 0) atomicAdd(st5, (unsigned long long)scanned);
     if (MODE == MODE_SOR) {
         if (active && !lone) sor_finish<K>(v.key, k, P.mean_k, P.mean_d, row);
         return;
@@ -1019,7 +1032,7 @@ __global__ void __launch_bounds__(64, MINB) k_tile_sel(const __grid_constant__ T
     for (int i = 0; i < 9; ++i) m[i] = 0.f;
     {
         const int rounds = __reduce_max_sync(kFull, tot);
-        if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned + 1, (unsigned long long)rounds);
+        if (st5 && lane == 0) atomicAdd(st5 + 1, (unsigned long long)rounds);
         QueueWalk w;
         w.start(S, 0, cnt, lane);
         float4 fc = q; int fe; unsigned fbit = 0;
@@ -1271,12 +1284,19 @@ static void launch_topk(const TreeView &T, const TileParams &P, int blocks, cuda
     k_tile_topk<K><<<blocks, 128, 0, st>>>(T, P);
 }
 
+template <int K, bool TMA, int MINB, bool STATS>
+static void launch_sel4(const TreeView &T, const TileParams &P, cudaStream_t st) {
+    const int ntiles = P.tile_end - P.tile_begin;
+    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA, TMA, MINB, STATS><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN, TMA, MINB, STATS><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    else k_tile_sel<K, MODE_SOR, TMA, MINB, STATS><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+}
 template <int K, bool TMA, int MINB>
 static void launch_sel3(const TreeView &T, const TileParams &P, cudaStream_t st) {
-    const int ntiles = P.tile_end - P.tile_begin;
-    if (P.mode == MODE_PCA) k_tile_sel<K, MODE_PCA, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else if (P.mode == MODE_KNN) k_tile_sel<K, MODE_KNN, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
-    else k_tile_sel<K, MODE_SOR, TMA, MINB><<<(ntiles + 1) / 2, 64, 0, st>>>(T, P);
+    if (P.stat_scanned) {                   // CCG_VERBOSE_STATS runs: the counting build, TMA staging, default occupancy
+        if constexpr (TMA) { launch_sel4<K, true, MINB, true>(T, P, st); return; }
+    }
+    launch_sel4<K, TMA, MINB, false>(T, P, st);
 }
 // Resident blocks per SM the kernel is compiled for (register cap = 65536 / (64 * MINB)).  Shared memory (12.4 KB per
 // block) allows 16; measured on the 30 M scan, K = 20: 12 blocks / 80 registers 28.96 ms, 14 / 72 28.77 ms, 16 / 64 (16 bytes
