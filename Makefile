@@ -4,7 +4,7 @@ NVCC ?= /usr/local/cuda/bin/nvcc
 ARCH = -gencode arch=compute_100a,code=sm_100a
 NVFLAGS = $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Xptxas -v --expt-relaxed-constexpr
 SRC = cloudclean_b200/csrc
-OBJ = $(SRC)/build.o $(SRC)/query.o $(SRC)/radsel.o $(SRC)/gridnormals.o $(SRC)/voxel.o $(SRC)/ptx.o $(SRC)/api.o
+OBJ = $(SRC)/build.o $(SRC)/query.o $(SRC)/radsel.o $(SRC)/gridnormals.o $(SRC)/noalloc.o $(SRC)/voxel.o $(SRC)/ptx.o $(SRC)/api.o
 LIB = cloudclean_b200/libccgpu.so
 
 all: $(LIB) oracle adapters

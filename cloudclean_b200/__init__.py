@@ -31,6 +31,7 @@ SYMBOLS = [
     "ccg_pca_knn_features_scatter", "ccg_dev_alloc", "ccg_dev_free", "ccg_ipc_export", "ccg_ipc_open", "ccg_ipc_close",
     "ccg_voxel_downsample", "ccg_voxel_downsample_fetch", "ccg_pca_knn_features_shard", "ccg_knn_graph", "ccg_normal_stdev", "ccg_stdev_dist", "ccg_neighbour_hist", "ccg_don", "ccg_principal_curvatures", "ccg_fpfh", "ccg_ptx_parse", "ccg_ptx_load", "ccg_ptx_fetch", "ccg_ptx_set_cloud",
     "ccg_set_async", "ccg_sync", "ccg_pca_knn_features_route", "ccg_radius_csr", "ccg_sor_finish",
+    "ccg_grid_normals_static",
 ]
 
 
@@ -92,6 +93,7 @@ def load_library():
     L.ccg_sor_mask.argtypes = [vp, i32, f64, vp, vp]
     L.ccg_radius_count_mask.argtypes = [vp, f64, i32, i32, vp]
     L.ccg_grid_normals.argtypes = [vp, vp, i32, i32, i32, vp, vp]
+    L.ccg_grid_normals_static.argtypes = [vp, vp, vp, sz, sz, vp, i32, i32, vp, vp]
     L.ccg_pca_knn_range.argtypes = [vp, i32, i32, vp, sz, sz, vp, vp]
     L.ccg_sor_mean_range.argtypes = [vp, i32, sz, sz, vp]
     L.ccg_sor_finish.argtypes = [vp, vp, sz, f64, vp]
@@ -548,6 +550,15 @@ class Context:
         self._check(self.L.ccg_grid_normals(self.h, _ptr(cloud_to_grid), scan_w, scan_h, 1 if fallback else 0, _ptr(out),
                                             C.byref(missing)))
         return out, missing.value
+
+    def grid_normals_static(self, xyz_dev, cloud_to_grid_dev, scan_w, scan_h, normal4_dev, status2_dev=None, stream=None):
+        """ccg_grid_normals_static: stages (i) + (ii) on DEVICE tensors, nothing allocated, nothing synchronised — the
+        caller waits on `stream` (an integer cudaStream_t; None = the context's stream).  The wrapper allocates nothing either."""
+        n = int(xyz_dev.shape[0])
+        stride = int(xyz_dev.stride(0)) * xyz_dev.element_size()
+        self._check(self.L.ccg_grid_normals_static(self.h, stream, xyz_dev.data_ptr(), stride, n, cloud_to_grid_dev.data_ptr(),
+                                                   scan_w, scan_h, normal4_dev.data_ptr(),
+                                                   None if status2_dev is None else status2_dev.data_ptr()))
 
     # ---- sharding ----------------------------------------------------------------------------------
     def pca_knn_range(self, k, cov_norm, begin, end, eig_sorted, nrm_sorted, viewpoint=None):

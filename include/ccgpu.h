@@ -165,6 +165,27 @@ int ccg_radius_count_mask(ccg_ctx *ctx, double r, int min_neighbours, int prefil
 int ccg_grid_normals(ccg_ctx *ctx, const int32_t *cloud_to_grid, int scan_w, int scan_h, int do_fallback,
                      float *normal4, int32_t *n_missing);
 
+/* ---- scan-grid normals without any allocation ------------------------------------------------------ */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Stages (i) + (ii) of
+ * ccg_grid_normals — the result of ccg_grid_normals(do_fallback = 0), bit for bit — with the kernel's scratch
+ * (grid_to_cloud, int32 per grid cell) in a file-scope __device__ array of CCG_STATIC_MAX_CELLS cells instead of the
+ * context's buffers: 16 MiB that every GPU loading the library holds until exit.  The call allocates nothing (no
+ * cudaMalloc / cudaFree / allocating library routine), copies nothing to or from the host, and does NOT synchronise:
+ * the kernels are queued on cuda_stream (NULL = the context's stream) and the caller waits on that stream.
+ *   xyz_dev           DEVICE pointer, n points, x y z as float32 at the start of every stride_bytes (>= 12, multiple of 4);
+ *                     the cloud given to ccg_set_cloud is NOT used
+ *   cloud_to_grid_dev DEVICE int32[n]
+ *   normal4_dev       DEVICE float32[n * 4]: nx, ny, nz, 1; NaN x4 where the fan has no face
+ *   status2_dev       DEVICE int32[2] or NULL: [0] = normals missing (NaN rows), [1] = 1 when cloud_to_grid held an index
+ *                     outside the grid (such points are skipped; ccg_grid_normals returns CCG_ERR_INVALID for them)
+ * scan_w * scan_h > CCG_STATIC_MAX_CELLS returns CCG_ERR_UNSUPPORTED.  Every call on a GPU shares the one array and
+ * clears what it uses first: calls that overlap on the GPU (two streams, two threads, two contexts) race; calls queued on
+ * one stream do not. */
+#define CCG_STATIC_MAX_CELLS 4194304
+int ccg_grid_normals_static(ccg_ctx *ctx, void *cuda_stream, const void *xyz_dev, size_t stride_bytes, size_t n,
+                            const int32_t *cloud_to_grid_dev, int scan_w, int scan_h, float *normal4_dev, int32_t *status2_dev);
+
 /* ---- multi-GPU sharding ----------------------------------------------------------- */
 /* Every rank holds the whole cloud and builds the identical Morton order; rank g owns sorted positions
  * [begin, end) (multiples of 32 except the last end = n).  Outputs are compact, row (pos - begin), in SORTED
