@@ -189,6 +189,14 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
         ctx->side_pending = 0;
         return rc;
     };
+    // CCG_PIPELINE_TRACE=1 (measurement only): when each chunk's kernels and copies ended, relative to the first launch
+    const bool trace = getenv("CCG_PIPELINE_TRACE") != nullptr;
+    cudaEvent_t tr0 = nullptr, trk[17] = {}, trc[17] = {};
+    if (trace) {
+        cudaEventCreate(&tr0);
+        for (int c = 0; c < nch; ++c) { cudaEventCreate(&trk[c]); cudaEventCreate(&trc[c]); }
+        cudaEventRecord(tr0, st);
+    }
     for (int c = 0; c < nch; ++c) {
         if (ctx->cancel && *ctx->cancel) return bail(set_error(ctx, CCG_ERR_CANCELLED, "cancelled by caller"));
         a.begin = (size_t)slot[c] * kLeaf;
@@ -207,6 +215,20 @@ static int pipelined_query(ccg_ctx *ctx, QueryArgs a, PipeOut *outs, int nouts, 
                 CCG_CUDA(ctx, cudaMemcpyAsync((char *)outs[i].o->user + r0 * outs[i].row_bytes, (char *)outs[i].o->d + r0 * outs[i].row_bytes,
                                               (r1 - r0) * outs[i].row_bytes, cudaMemcpyDeviceToHost, cs));
         CCG_CUDA(ctx, cudaEventRecord(ctx->ev_copy[c], cs));       // rows below bound[c + 1] are on the host after this
+        if (trace) { cudaEventRecord(trk[c], st); cudaEventRecord(trc[c], cs); }
+    }
+    if (trace) {
+        cudaStreamSynchronize(st); cudaStreamSynchronize(cs);
+        size_t row_bytes = 0;
+        for (int i = 0; i < nouts; ++i) row_bytes += outs[i].row_bytes;
+        for (int c = 0; c < nch; ++c) {
+            float tk = 0.f, tc = 0.f;
+            cudaEventElapsedTime(&tk, tr0, trk[c]); cudaEventElapsedTime(&tc, tr0, trc[c]);
+            fprintf(stderr, "[ccg pipeline] chunk %2d tiles %8d..%8d kernels end %7.3f ms, rows %10zu..%10zu (%7.1f MB) on the host at %7.3f ms\n", c,
+                    slot[c], slot[c + 1], tk, bound[c], bound[c + 1], (double)(bound[c + 1] - bound[c]) * row_bytes / 1e6, tc);
+            cudaEventDestroy(trk[c]); cudaEventDestroy(trc[c]);
+        }
+        cudaEventDestroy(tr0);
     }
     if (bound_out) for (int c = 0; c <= nch; ++c) bound_out[c] = bound[c];
     if (nch_out) *nch_out = nch;

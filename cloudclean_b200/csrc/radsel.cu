@@ -7,8 +7,12 @@
 //
 //   k_tile_kth     per query the RULE of its neighbourhood: T = the max_nn-th smallest d2 inside r (r^2 bound itself when the
 //                  cap does not bind) and I = the largest original index admitted among candidates tied at T.  T is found by
-//                  a counting select over the traversal: 64-bin histograms of d2 per lane in shared memory narrow the
-//                  bracket level by level until it holds <= 64 candidates, which are then collected and ranked exactly.
+//                  a counting select over the traversal: 64-bin histograms (uniform in the distance) per lane in shared
+//                  memory narrow the bracket level by level until it holds <= 64 candidates, which are then collected and
+//                  ranked exactly.  The FIRST pass lowers its bound while it walks (as soon as the bins up to b hold max_nn
+//                  candidates nothing above bin b matters), later passes are bounded by the bracket chosen so far: a cap far
+//                  below the neighbourhood size never opens the far part of the neighbourhood.  I comes from the same kind
+//                  of select over the index bits when the cap admits more than 64 members of a tie class.
 //   k_tile_rule<V> one traversal bounded by T that feeds {d2 < T or (d2 == T and index <= I)} — exactly the
 //                  (d2, index)-ordered max_nn nearest — to a streaming visitor: PCA moments (getPCA / getHist), stdev_dist
 //                  (cv.cpp:166-230), normal_stdev (cv.h:123-206), calcDistHist / calcIntensityHist (featureeval/utils.h).
@@ -27,9 +31,12 @@ constexpr int kSelKeep = 64;          // candidates a lane can rank exactly
 constexpr int kSelLevels = 4;
 
 // bin of d2 at level `lvl` given the bins chosen at the levels above; `match` = the candidate lies inside those bins.
-// The same expression runs in every pass, so a candidate always lands in the same bin.
+// The same expression runs in every pass, so a candidate always lands in the same bin.  The bins are uniform in the DISTANCE
+// (f = 64 d / r, monotone in d2): on a surface the count grows with d2, so bin b of level 0 holds ~(2b + 1) / 4096 of the
+// neighbourhood and a cap far below the neighbourhood size (1000 of 24 k, 1000 of 570 k) still lands a few bins up, where the
+// edge above it overshoots the cap distance by a few percent instead of several times.
 __device__ __forceinline__ int bin_path(float d2, float scale, int lvl, const int sel[kSelLevels], bool &match) {
-    float f = __fmul_rn(d2, scale);
+    float f = __fmul_rn(__fsqrt_rn(d2), scale);
     int b = min(kSelBins - 1, (int)f);
     match = true;
 #pragma unroll
@@ -43,17 +50,54 @@ __device__ __forceinline__ int bin_path(float d2, float scale, int lvl, const in
     return b;
 }
 
+// Upper edge, as a d2 bound, of the bracket chosen at the first `lvl` levels: every candidate whose bins match sel[0..lvl) has
+// d2 <= the returned value.  bin_path is exact after its first multiplication (f - sel is exact, * 64 is exact), so the bracket
+// is f = sqrt(d2) * scale in [F, F + 64^-(lvl-1)) in units of level-0 bins; the margins cover the roundings of this sum, of the
+// division, of the square and of f itself (< 1e-6 together).  The top bins are clamped (f may reach 64 + 2^-18): their edge is
+// r^2 itself.
+__device__ __forceinline__ float bracket_edge(float rb, float scale, int lvl, const int sel[kSelLevels]) {
+    if (lvl == 0) return rb;
+    float F = 0.f, w = 1.f, wl = 1.f;
+#pragma unroll
+    for (int l = 0; l < kSelLevels; ++l) {
+        if (l < lvl) { F += (float)sel[l] * w; wl = w; w *= 1.f / (float)kSelBins; }
+    }
+    const float e = __fmul_rn(__fdiv_rn(F + wl, scale), 1.00001f);
+    return fminf(rb, __fmul_rn(__fmul_rn(e, e), 1.00001f));
+}
+
 struct HistV {                        // level pass: histogram of the candidates inside the chosen bins
     float bound, scale; int lvl; int sel[kSelLevels];
     unsigned *hist;                   // this lane's column: bin b at hist[b * 32]
+    // First pass only (max_nn > 0): the bound FOLLOWS the histogram down.  The traversal visits near boxes first; as soon as the
+    // bins up to b hold max_nn candidates, the max_nn-th smallest d2 cannot lie above bin b and the bound drops to that bin's
+    // edge, so the far part of a neighbourhood much larger than the cap (24 k points inside r = 0.2 m on the 30 M scan, cap
+    // 1000) is never opened.  Bins <= b stay complete: a box is only ever pruned against a bound >= the final one.
+    int max_nn, inb, limit;
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+        int add = 0;
 #pragma unroll 2
         for (int j = 0; j < kLeaf; ++j) {
             const float d2 = d2_point(q, leaf[j]);
             if (d2 <= bound) {
                 bool match;
                 const int b = bin_path(d2, scale, lvl, sel, match);
-                if (match) hist[b * 32] += 1;
+                if (match) { hist[b * 32] += 1; ++add; }
+            }
+        }
+        if (max_nn > 0) {
+            inb += add;
+            if (inb > limit) {
+                int cum = 0, b = 0;
+                for (; b < kSelBins - 1; ++b) {
+                    const int hb = (int)hist[b * 32];
+                    if (cum + hb >= max_nn) break;
+                    cum += hb;
+                }
+                const int one[kSelLevels] = {b, 0, 0, 0};
+                bound = fminf(bound, bracket_edge(bound, scale, 1, one));
+                inb = cum + (int)hist[b * 32];
+                limit = inb < (1 << 30) ? inb + (max_nn >> 2) + 32 : INT_MAX;
             }
         }
     }
@@ -102,7 +146,24 @@ struct TieV {                         // tie pass (bound = T): candidates below 
     }
 };
 
-// err bits: 1 = more than kSelKeep distinct values left after the last level, 2 = tie class too large for the cap
+// index select (a tie class AT the cap distance of which the cap admits more than kSelKeep members — piles of duplicates,
+// lattices): histogram of 6 index bits of the candidates tied at `bound` whose higher bits equal `prefix`
+struct TieIdxV {
+    float bound; int shift; unsigned prefix;
+    unsigned *hist;
+    __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
+#pragma unroll 2
+        for (int j = 0; j < kLeaf; ++j) {
+            const float4 c = leaf[j];
+            if (d2_point(q, c) == bound) {
+                const unsigned long long ci = (unsigned)__float_as_int(c.w);
+                if ((unsigned)(ci >> (shift + 6)) == prefix) hist[((unsigned)(ci >> shift) & 63u) * 32] += 1;
+            }
+        }
+    }
+};
+
+// err bit 1 = more than kSelKeep distinct values left after the last level
 __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeView T, float rb, int max_nn, float *__restrict__ Tpos,
                                                   int32_t *__restrict__ Ipos, int *__restrict__ err) {
     __shared__ WarpScratch s_ws[4];
@@ -116,8 +177,9 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     unsigned *hist = &s_hist[warp][lane];
     float t_out = rb; int i_out = INT_MAX;
 
-    // The first histogram pass (level 0, every lane) also counts the neighbourhood: count = sum of the bins.
-    const float scale = rb > 0.f ? __fdiv_rn((float)kSelBins, rb) : 0.f;
+    // The first histogram pass (level 0, every lane) also counts the neighbourhood: count = sum of the bins (a lane whose bound
+    // dropped on the way holds more than max_nn candidates below it, so "count > max_nn" reads the same either way).
+    const float scale = rb > 0.f ? __fdiv_rn((float)kSelBins, __fsqrt_rn(rb)) : 0.f;
     int sel[kSelLevels] = {0, 0, 0, 0};
     int lvl = 0, kprime = max_nn, nb = 0;                 // lvl: levels THIS lane has refined; nb: candidates left in its bracket
     bool need = active, first = true;
@@ -125,14 +187,17 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
         const bool mine = first ? active : (need && nb > kSelKeep && lvl < kSelLevels);
 #pragma unroll 8
         for (int b = 0; b < kSelBins; ++b) hist[b * 32] = 0;
-        HistV h; h.bound = mine ? rb : -1.f; h.scale = scale; h.lvl = lvl; h.hist = hist;
+        HistV h; h.scale = scale; h.lvl = lvl; h.hist = hist;
 #pragma unroll
         for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
+        // later passes only need the bracket chosen so far: everything in it lies below its upper edge
+        h.bound = mine ? bracket_edge(rb, scale, lvl, sel) : -1.f;
+        h.max_nn = first ? max_nn : 0; h.inb = 0; h.limit = max_nn < (1 << 30) ? max_nn + (max_nn >> 2) + 32 : INT_MAX;
         traverse_tile(T, tile, q, h, s_ws[warp]);
         if (first) {
             int c = 0;
             for (int b = 0; b < kSelBins; ++b) c += (int)hist[b * 32];
-            nb = c;
+            nb = h.bound < rb ? INT_MAX : c;              // a dropped bound: c undercounts, the bracket must be refined
             need = active && c > max_nn;
             first = false;
             if (!__any_sync(kFull, need)) { Tpos[pos] = t_out; Ipos[pos] = i_out; return; }   // the cap binds nowhere in this tile
@@ -154,7 +219,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     // select pass: the candidates inside the lane's bracket, ranked exactly
     bool tie_pass = false;                                 // does this lane need the index tie-break at T?
     {
-        KeepV kv; kv.bound = need ? rb : -1.f; kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
+        KeepV kv; kv.bound = need ? bracket_edge(rb, scale, lvl, sel) : -1.f; kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
         kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY;
 #pragma unroll
         for (int l = 0; l < kSelLevels; ++l) kv.sel[l] = sel[l];
@@ -179,6 +244,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     }
     __syncwarp();
     // tie pass (only when some lane's tie class overflows its cap): how many candidates lie strictly below T, which indices tie AT it
+    bool wide = false; int mleft = 0;
     if (__any_sync(kFull, tie_pass)) {
         TieV tv; tv.bound = tie_pass ? t_out : -1.f; tv.less = 0; tv.tied = 0; tv.idx = reinterpret_cast<int *>(hist);
         traverse_tile(T, tile, q, tv, s_ws[warp]);
@@ -194,10 +260,33 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
                         if (lt == m - 1) { i_out = vi; break; }
                     }
                 } else {
-                    atomicOr(err, 2);
+                    wide = true; mleft = m;
                 }
             }
         }
+    }
+    // the m-th smallest tied index for m > kSelKeep: counting select over the index bits, 6 bits per traversal (bounded by T)
+    if (__any_sync(kFull, wide)) {
+        unsigned prefix = 0;
+        for (int l = 0; l < 6; ++l) {
+            const int shift = 30 - 6 * l;
+            __syncwarp();
+#pragma unroll 8
+            for (int b = 0; b < kSelBins; ++b) hist[b * 32] = 0;
+            TieIdxV iv; iv.bound = wide ? t_out : -1.f; iv.shift = shift; iv.prefix = prefix; iv.hist = hist;
+            traverse_tile(T, tile, q, iv, s_ws[warp]);
+            if (wide) {
+                int cum = 0, b = 0;
+                for (; b < kSelBins - 1; ++b) {
+                    const int hb = (int)hist[b * 32];
+                    if (cum + hb >= mleft) break;
+                    cum += hb;
+                }
+                mleft -= cum;
+                prefix = (prefix << 6) | (unsigned)b;
+            }
+        }
+        if (wide) i_out = (int)prefix;
     }
     Tpos[pos] = t_out; Ipos[pos] = i_out;
 }
@@ -414,7 +503,7 @@ __global__ void __launch_bounds__(128) k_tile_rule(const __grid_constant__ TreeV
 // host launchers
 // ---------------------------------------------------------------------------------------------------
 // The rule arrays of a capped search: *Tpos / *Ipos stay NULL when the cap cannot bind (max_nn == 0 or >= n: FLANN caps only
-// when 0 < max_nn < n).  Synchronises once to read the two error bits.
+// when 0 < max_nn < n).  Synchronises once to read the error bit.
 int launch_radius_rule(ccg_ctx *ctx, float rb, int max_nn, const float **Tpos, const int32_t **Ipos) {
     *Tpos = nullptr; *Ipos = nullptr;
     if (ctx->n == 0 || max_nn <= 0 || (size_t)max_nn >= ctx->n) return CCG_OK;
@@ -429,7 +518,6 @@ int launch_radius_rule(ccg_ctx *ctx, float rb, int max_nn, const float **Tpos, c
     CCG_CUDA(ctx, cudaMemcpyAsync(&h, err, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CCG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (h & 1) return set_error(ctx, CCG_ERR_UNSUPPORTED, "capped radius search: more than %d distinct distances inside a 2^-24 r^2 bracket", kSelKeep);
-    if (h & 2) return set_error(ctx, CCG_ERR_UNSUPPORTED, "capped radius search: more than %d candidates tied at the cap distance of which the cap admits more than %d", kSelKeep, kSelKeep);
     *Tpos = ctx->rule_T.as<float>(); *Ipos = ctx->rule_I.as<int32_t>();
     return CCG_OK;
 }

@@ -577,6 +577,35 @@ def test_capped_radius_ties_follow_the_index_order(gpu_ctx):
         check_pca(eig, nrm, ref)
 
 
+@pytest.mark.parametrize("kind", ["surface", "volume", "lattice", "pile"])
+def test_capped_radius_far_below_the_neighbourhood_size(gpu_ctx, kind):
+    """Caps 10-300x below the neighbourhood size (the reference's pca_max_nn = 1000 inside r = 0.2 m holds 24 k points on a dense
+    scan): the counting select drops its bound while it walks (radsel.cu, HistV) — rows still bit-exact in indices and distances."""
+    rng = np.random.default_rng(77)
+    n = 24000
+    xyz = rng.random((n, 3), dtype=np.float32) - 0.5
+    if kind == "surface":
+        xyz[:, 2] *= 0.01
+    elif kind == "lattice":
+        xyz = np.round(xyz * np.float32(16)) / np.float32(16)
+    elif kind == "pile":
+        xyz[::3] = np.float32([0.01, 0.02, 0.0])
+    pts = np.zeros((n, 4), np.float32)
+    pts[:, :3] = xyz
+    T = oracle.Tree(pts)
+    gpu_ctx.set_cloud(pts)
+    for r, cap in ((0.6, 65), (0.45, 300), (0.25, 1000)):
+        off, idx, d2 = gpu_ctx.radius_csr(r, cap, strict_lt=True, device_out=False)
+        total = T.radius(r, strict_lt=True, lists=False)["total"]
+        eff = np.minimum(total, cap)
+        assert np.array_equal(np.diff(off), eff)
+        ref = T.radius(r, cap=int(max(1, eff.max())), strict_lt=True)
+        rows = np.repeat(np.arange(n), eff)
+        cols = np.arange(off[-1]) - np.repeat(off[:-1], eff)
+        assert np.array_equal(d2, ref["d2"][rows, cols])
+        assert np.array_equal(idx, ref["idx"][rows, cols])
+
+
 @pytest.mark.parametrize("r,max_nn,bins", [(0.1, 20, 20), (0.3, 64, 8), (0.05, 10, 33)])
 def test_neighbour_histograms(gpu_ctx, r, max_nn, bins):
     """calcDistHist / calcIntensityHist (featureeval/utils.h:18-195): bit-exact (same increments, same bins)."""
