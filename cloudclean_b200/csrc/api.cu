@@ -416,6 +416,8 @@ int ccg_create(ccg_ctx **out, int device_id) {
     if (sc) ctx->sel_chunks = atoi(sc);
     const char *po = getenv("CCG_POINT_OVERLAP");
     ctx->point_overlap = (po && po[0] == '0') ? 0 : 1;
+    const char *nm = getenv("CCG_NODE_MOMENTS");
+    if (nm) ctx->node_moments = atoi(nm) != 0;
     const char *kt = getenv("CCG_KNN_TOPK");
     ctx->knn_use_topk = (kt && kt[0] == '1') ? 1 : 0;
     const char *pc = getenv("CCG_PIPELINE_CHUNKS");
@@ -434,7 +436,7 @@ void ccg_destroy(ccg_ctx *ctx) {
     for (int i = 0; i < 2; ++i) { ctx->keys[i].release(); ctx->vals[i].release(); ctx->hpin[i].release(); }
     ctx->vox_out.release();
     ctx->ptx_bytes.release(); ctx->ptx_starts.release(); ctx->ptx_points.release(); ctx->ptx_c2g.release();
-    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release(); ctx->defer_b.release(); ctx->rule_T.release(); ctx->rule_I.release();
+    ctx->sort_tmp.release(); ctx->boxes_lo.release(); ctx->boxes_hi.release(); ctx->scratch.release(); ctx->defer.release(); ctx->defer_b.release(); ctx->rule_T.release(); ctx->rule_I.release(); ctx->node_mom.release();
     for (int i = 0; i < 2; ++i) if (ctx->ev_side[i]) cudaEventDestroy(ctx->ev_side[i]);
     if (ctx->ev_tile) cudaEventDestroy(ctx->ev_tile);
     if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);

@@ -286,6 +286,103 @@ __global__ void __launch_bounds__(256) k_build_level(const float4 *__restrict__ 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// per-box moments (uncapped radius sums: a box inside the radius contributes ONE aggregated term)
+//   mom[3 b + 0] = (Sx, Sy, Sz, count as int bits)   S = sum (p - c), c = the box centre 0.5 (lo + hi)
+//   mom[3 b + 1] = (Mxx, Mxy, Mxz, Myy)              M = sum (p - c)(p - c)^T
+//   mom[3 b + 2] = (Myz, Mzz, 0, 0)
+// Sums about the box's OWN centre are of the size of the box, so shifting them to a query (tile.cuh / query.cu: StreamNodes)
+// loses nothing to cancellation whatever the cloud's coordinates are.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_leaf_moments(const float4 *__restrict__ sorted, int n, int nleaf, const float4 *__restrict__ lo0,
+                                                      const float4 *__restrict__ hi0, float4 *__restrict__ mom) {
+    const int leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (leaf >= nleaf) return;
+    const int pos = leaf * kLeaf + lane;
+    const bool valid = pos < n;
+    const float4 lo = lo0[leaf], hi = hi0[leaf];
+    const float cx = __fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)), cy = __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)), cz = __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z));
+    const float4 p = sorted[pos];
+    const float X = valid ? p.x - cx : 0.f, Y = valid ? p.y - cy : 0.f, Z = valid ? p.z - cz : 0.f;
+    const float sx = warp_sum(X), sy = warp_sum(Y), sz = warp_sum(Z);
+    const float xx = warp_sum(X * X), xy = warp_sum(X * Y), xz = warp_sum(X * Z), yy = warp_sum(Y * Y), yz = warp_sum(Y * Z), zz = warp_sum(Z * Z);
+    const int cnt = __popc(__ballot_sync(kFull, valid));
+    if (lane == 0) {
+        float4 *o = mom + 3 * (size_t)leaf;
+        o[0] = make_float4(sx, sy, sz, __int_as_float(cnt));
+        o[1] = make_float4(xx, xy, xz, yy);
+        o[2] = make_float4(yz, zz, 0.f, 0.f);
+    }
+}
+
+// one warp per parent: lane c shifts child c's moments to the parent's centre, the warp adds them up
+__global__ void __launch_bounds__(256) k_level_moments(const float4 *__restrict__ clo, const float4 *__restrict__ chi, const float4 *__restrict__ cmom,
+                                                       int nchild, const float4 *__restrict__ plo, const float4 *__restrict__ phi,
+                                                       float4 *__restrict__ pmom, int nparent) {
+    const int node = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (node >= nparent) return;
+    const int c = node * kFan + lane;
+    const float4 PL = plo[node], PH = phi[node];
+    const float Cx = __fmul_rn(0.5f, __fadd_rn(PL.x, PH.x)), Cy = __fmul_rn(0.5f, __fadd_rn(PL.y, PH.y)), Cz = __fmul_rn(0.5f, __fadd_rn(PL.z, PH.z));
+    float v[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    int cnt = 0;
+    if (c < nchild) {
+        const float4 lo = clo[c], hi = chi[c];
+        const float4 a = cmom[3 * (size_t)c], b = cmom[3 * (size_t)c + 1], d = cmom[3 * (size_t)c + 2];
+        cnt = __float_as_int(a.w);
+        const float fn = (float)cnt;
+        const float ex = __fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)) - Cx, ey = __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)) - Cy,
+                    ez = __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)) - Cz;
+        const float tx = fn * ex, ty = fn * ey, tz = fn * ez;
+        v[0] = a.x + tx; v[1] = a.y + ty; v[2] = a.z + tz;
+        v[3] = b.x + ex * (2.f * a.x + tx);
+        v[4] = b.y + a.x * ey + ex * (a.y + ty);
+        v[5] = b.z + a.x * ez + ex * (a.z + tz);
+        v[6] = b.w + ey * (2.f * a.y + ty);
+        v[7] = d.x + a.y * ez + ey * (a.z + tz);
+        v[8] = d.y + ez * (2.f * a.z + tz);
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) v[i] = warp_sum(v[i]);
+    cnt = __reduce_add_sync(kFull, cnt);
+    if (lane == 0) {
+        float4 *o = pmom + 3 * (size_t)node;
+        o[0] = make_float4(v[0], v[1], v[2], __int_as_float(cnt));
+        o[1] = make_float4(v[3], v[4], v[5], v[6]);
+        o[2] = make_float4(v[7], v[8], 0.f, 0.f);
+    }
+}
+
+// Filled lazily (the kNN paths never need it): two tiny passes over the sorted cloud and the boxes, on the ctx stream.
+int ensure_node_moments(ccg_ctx *ctx) {
+    if (ctx->node_mom_valid || ctx->n == 0) return CCG_OK;
+    size_t total = 0;
+    for (int l = 0; l < ctx->nlevels; ++l) total = ctx->level_off[l] + (size_t)ctx->level_count[l];
+    CCG_CUDA(ctx, ctx->node_mom.reserve(3 * total * sizeof(float4)));
+    cudaStream_t st = ctx->stream;
+    const float4 *lo = ctx->boxes_lo.as<float4>(), *hi = ctx->boxes_hi.as<float4>();
+    float4 *mom = ctx->node_mom.as<float4>();
+    k_leaf_moments<<<(ctx->nleaf + 7) / 8, 256, 0, st>>>(ctx->sorted.as<float4>(), (int)ctx->n, ctx->nleaf, lo + ctx->level_off[0],
+                                                         hi + ctx->level_off[0], mom + 3 * ctx->level_off[0]);
+    ctx->stats.launches++;
+    for (int l = 1; l < ctx->nlevels; ++l) {
+        const int np = ctx->level_count[l];
+        k_level_moments<<<(np + 7) / 8, 256, 0, st>>>(lo + ctx->level_off[l - 1], hi + ctx->level_off[l - 1], mom + 3 * ctx->level_off[l - 1],
+                                                      ctx->level_count[l - 1], lo + ctx->level_off[l], hi + ctx->level_off[l],
+                                                      mom + 3 * ctx->level_off[l], np);
+        ctx->stats.launches++;
+    }
+    CCG_CUDA(ctx, cudaGetLastError());
+    ctx->node_mom_valid = true;
+    return CCG_OK;
+}
+
 // ccg_sync after an asynchronous build: the deferred finiteness check, bounding box and timings
 int finish_cloud_check(ccg_ctx *ctx) {
     if (!ctx->pending_cloud_check) return CCG_OK;
@@ -312,6 +409,7 @@ int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride) {
     cudaStream_t st = ctx->stream;
     ctx->n = 0;
     ctx->has_cloud = false;
+    ctx->node_mom_valid = false;
     ctx->stats = ccg_stats{};
     if (n == 0) {
         ctx->npad = 0; ctx->nleaf = 0; ctx->nlevels = 0;

@@ -98,6 +98,9 @@ struct ccg_ctx {
     int64_t vox_n = 0; int vox_nf = 0;
     ccg::DevBuf ptx_bytes, ptx_starts, ptx_points, ptx_c2g;   // last ccg_ptx_parse: file bytes, line starts, 32-byte rows, cloud_to_grid_map
     int64_t ptx_n = 0;
+    ccg::DevBuf node_mom;         // 3 float4 per box of every level (laid out like boxes_lo): count and moments of its points about the
+    bool node_mom_valid = false;  // box centre; filled on the first uncapped radius sum after a build (ensure_node_moments, build.cu)
+    int node_moments = 1;         // CCG_NODE_MOMENTS=0: the uncapped radius sums visit every point (A/B switch)
     ccg::DevBuf rule_T, rule_I;   // per sorted position: d2 threshold / tie index threshold of a capped radius search (radsel.cu)
     ccg::DevBuf defer, defer_b;   // [count | query list | output rows] of queries deferred to the exact point kernel (double buffer)
     int defer_sel = 0, side_pending = 0, last_side = 0;
@@ -162,6 +165,7 @@ int set_error(ccg_ctx *ctx, int code, const char *fmt, ...);
 // build.cu
 int build_cloud(ccg_ctx *ctx, const void *xyz, size_t n, size_t stride_bytes);
 int finish_cloud_check(ccg_ctx *ctx);
+int ensure_node_moments(ccg_ctx *ctx);
 
 // query.cu
 enum TileMode { MODE_KNN = 0, MODE_PCA = 1, MODE_SOR = 2 };

@@ -110,6 +110,33 @@ struct Stream {
     }
 };
 
+// the same sums with whole boxes taken at once (tile.cuh: visits_nodes): a box inside the radius of every lane that wants it adds
+// its count and its moments, shifted from the box centre c to the query — with d = c - q:
+//   sum (p - q) = S + n d,   sum (p - q)(p - q)^T = M + S d^T + d S^T + n d d^T        (per-box arrays: build.cu, k_leaf_moments)
+struct StreamNodes : Stream {
+    static constexpr bool kNodes = true;
+    const float4 *mom;
+    __device__ __forceinline__ void add_node(size_t node, const float4 &lo, const float4 &hi, const float4 &q) {
+        const float4 a = __ldg(mom + 3 * node);
+        const int nn = __float_as_int(a.w);
+        count += nn;
+        if (moments) {
+            const float4 b = __ldg(mom + 3 * node + 1), c = __ldg(mom + 3 * node + 2);
+            const float fn = (float)nn;
+            const float dx = __fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)) - q.x, dy = __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)) - q.y,
+                        dz = __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)) - q.z;
+            const float tx = fn * dx, ty = fn * dy, tz = fn * dz;
+            m[0] += a.x + tx; m[1] += a.y + ty; m[2] += a.z + tz;
+            m[3] += b.x + dx * (2.f * a.x + tx);
+            m[4] += b.y + a.x * dy + dx * (a.y + ty);
+            m[5] += b.z + a.x * dz + dx * (a.z + tz);
+            m[6] += b.w + dy * (2.f * a.y + ty);
+            m[7] += c.x + a.y * dz + dy * (a.z + tz);
+            m[8] += c.y + dz * (2.f * a.z + tz);
+        }
+        if (cap > 0 && count >= cap) { count = cap; bound = -1.f; }   // what the per-point count stops at
+    }
+};
 
 // streaming visitor that sums a 3-float per-point attribute (e.g. normals) over everything inside the radius;
 // the attribute is gathered by ORIGINAL index (the candidate's w), so the caller's array is used as it lies
@@ -1090,8 +1117,10 @@ struct StreamParams {
     int32_t *count;
     PcaOut pca;
     unsigned long long *stat_scanned;
+    const float4 *mom;               // per-box moments (StreamNodes) or NULL
 };
 
+template <class V>
 __global__ void __launch_bounds__(128) k_tile_stream(const __grid_constant__ TreeView T, const __grid_constant__ StreamParams P) {
     __shared__ WarpScratch s_ws[4];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1100,8 +1129,9 @@ __global__ void __launch_bounds__(128) k_tile_stream(const __grid_constant__ Tre
     const size_t pos = (size_t)tile * kLeaf + lane;
     const float4 q = T.pts[pos];
     const bool active = pos < (size_t)T.n;
-    Stream v;
+    V v;
     v.init(P.rb, P.count_cap, P.mode == 1, active);
+    if constexpr (visits_nodes<V>::value) v.mom = P.mom;
     int scanned = traverse_tile(T, tile, q, v, s_ws[warp]);
     if (P.stat_scanned && lane == 0) atomicAdd(P.stat_scanned, (unsigned long long)scanned);
     const size_t row = P.sorted_rows ? (size_t)((long long)pos - P.row_begin) : (size_t)__float_as_int(q.w);
@@ -1481,7 +1511,14 @@ int launch_tile_stream(ccg_ctx *ctx, const StreamArgs &a) {
         P.stat_scanned = (unsigned long long *)((char *)ctx->scratch.p + 1024);
     }
     const int ntiles = P.tile_end - P.tile_begin;
-    k_tile_stream<<<(ntiles + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
+    P.mom = nullptr;
+    if (ctx->node_moments) {
+        CCG_TRY(ensure_node_moments(ctx));
+        P.mom = ctx->node_mom.as<float4>();
+        k_tile_stream<StreamNodes><<<(ntiles + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
+    } else {
+        k_tile_stream<Stream><<<(ntiles + 3) / 4, 128, 0, ctx->stream>>>(ctx->view(), P);
+    }
     ctx->stats.launches++;
     CCG_CUDA(ctx, cudaGetLastError());
     if (ctx->collect_stats) {

@@ -3,6 +3,7 @@
 #pragma once
 #include "common.cuh"
 #include <cfloat>
+#include <type_traits>
 
 namespace ccg {
 
@@ -31,6 +32,14 @@ __device__ __forceinline__ float d2_point_box(const float4 &q, const float4 &lo,
     float dz = fmaxf(fmaxf(__fsub_rn(lo.z, q.z), __fsub_rn(q.z, hi.z)), 0.f);
     return sumsq3(dx, dy, dz);
 }
+// UPPER bound of d2_point(q, p) over all p inside [lo, hi]: |q.x - p.x| rounds to a value between the rounded differences to the
+// two faces (rounding is monotone), and squares and sums of non-negative terms are monotone in every rounding step
+__device__ __forceinline__ float d2_point_box_far(const float4 &q, const float4 &lo, const float4 &hi) {
+    float dx = fmaxf(fabsf(__fsub_rn(q.x, lo.x)), fabsf(__fsub_rn(q.x, hi.x)));
+    float dy = fmaxf(fabsf(__fsub_rn(q.y, lo.y)), fabsf(__fsub_rn(q.y, hi.y)));
+    float dz = fmaxf(fabsf(__fsub_rn(q.z, lo.z)), fabsf(__fsub_rn(q.z, hi.z)));
+    return sumsq3(dx, dy, dz);
+}
 // lower bound over all (q in [alo, ahi], p in [blo, bhi])
 __device__ __forceinline__ float d2_box_box(const float4 &alo, const float4 &ahi, const float4 &blo, const float4 &bhi) {
     float dx = fmaxf(fmaxf(__fsub_rn(blo.x, ahi.x), __fsub_rn(alo.x, bhi.x)), 0.f);
@@ -56,6 +65,12 @@ __device__ __forceinline__ float warp_min(float v) {
     for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o));
     return v;
 }
+
+// A visitor with `static constexpr bool kNodes = true` and add_node(node, lo, hi, q) takes a whole SUBTREE at once when its box
+// lies inside the bound of every lane that wants it (node = index into the per-node arrays laid out like the boxes: level
+// offset + node number) — the uncapped radius sums then cost one aggregated term per inner box instead of a visit per point.
+template <class V, class = void> struct visits_nodes : std::false_type {};
+template <class V> struct visits_nodes<V, std::void_t<decltype(V::kNodes)>> : std::bool_constant<V::kNodes> {};
 
 // Bottom-up, nearest-first walk of the box hierarchy for the 32 queries of one leaf ("tile").
 //   * the tile's own leaf is scanned first (it alone fills a k <= 32 list and gives a finite bound);
@@ -125,6 +140,13 @@ __device__ __forceinline__ int traverse_tile(const TreeView &T, int tile, const 
             const float4 clo = T.lo[lv][child], chi = T.hi[lv][child];
             const bool want = d2_point_box(q, clo, chi) <= v.bound;
             if (!__any_sync(kFull, want)) continue;
+            if constexpr (visits_nodes<V>::value) {
+                const bool whole = want && d2_point_box_far(q, clo, chi) <= v.bound;
+                if (__all_sync(kFull, whole || !want)) {
+                    if (whole) v.add_node((size_t)(T.lo[lv] - T.lo[0]) + (size_t)child, clo, chi, q);
+                    continue;
+                }
+            }
             if (lv == 0) {
                 // stage the leaf (a contiguous 512-byte run) and let every lane score its 32 candidates
                 const float4 p = T.pts[(size_t)child * kLeaf + lane];

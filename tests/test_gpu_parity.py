@@ -577,6 +577,72 @@ def test_capped_radius_ties_follow_the_index_order(gpu_ctx):
         check_pca(eig, nrm, ref)
 
 
+def _radius_pca_truth(pts, r):
+    """fp64 brute force over the fp32-contract membership mask d2 < float32(r*r): counts, eigenvalues (desc) of the 1/(m-1) covariance"""
+    xyz = pts[:, :3].astype(np.float32)
+    n = xyz.shape[0]
+    r2 = np.float32(r * r)
+    P = xyz.astype(np.float64)
+    cnt = np.empty(n, np.int32)
+    eig = np.zeros((n, 3))
+    for a in range(0, n, 500):
+        q = xyz[a:a + 500]
+        dx = q[:, None, 0] - xyz[None, :, 0]
+        dy = q[:, None, 1] - xyz[None, :, 1]
+        dz = q[:, None, 2] - xyz[None, :, 2]
+        mask = ((dx * dx + dy * dy) + dz * dz) < r2                     # every product and sum rounded to fp32, as the contract says
+        m = mask.sum(1)
+        cnt[a:a + 500] = m
+        w = mask.astype(np.float64)
+        for i in range(q.shape[0]):
+            if m[i] >= 3:
+                nb = P[mask[i]]
+                eig[a + i] = np.linalg.eigvalsh(np.cov(nb.T, ddof=1))[::-1]
+            else:
+                eig[a + i] = (0.0, 0.0, 1.0)
+    return cnt, eig
+
+
+@pytest.mark.parametrize("kind", ["surface", "volume", "far_from_origin"])
+def test_uncapped_radius_sums_take_whole_boxes(kind):
+    """Uncapped radius PCA / counts over neighbourhoods of thousands of points: boxes of the hierarchy that lie inside the radius
+    contribute their aggregated count and moments (StreamNodes, query.cu) — counts stay bit-exact, eigenvalues within the bar, and
+    the result agrees with the per-point walk (CCG_NODE_MOMENTS=0) to the same bar."""
+    rng = np.random.default_rng(5)
+    n = 12000
+    xyz = rng.random((n, 3)) - 0.5
+    if kind == "surface":
+        xyz[:, 2] = 0.02 * np.sin(6 * xyz[:, 0]) + 0.002 * rng.random(n)
+    if kind == "far_from_origin":
+        xyz += np.array([250.0, -80.0, 40.0])                            # cancellation test: sums must not be taken about the origin
+    pts = np.zeros((n, 4), np.float32)
+    pts[:, :3] = xyz
+    r = 0.3
+    cnt, eig64 = _radius_pca_truth(pts, r)
+    T = oracle.Tree(pts)
+    assert np.array_equal(cnt, T.radius(r, strict_lt=True, lists=False)["total"])
+    mn = int(np.median(cnt))                                             # a min-neighbour count that binds for half the points
+    ref_mask = T.radius_outliers(r, mn, False)
+    res = {}
+    for knob in ("1", "0"):
+        os.environ["CCG_NODE_MOMENTS"] = knob
+        try:
+            ctx = cc.Context(0)
+        finally:
+            del os.environ["CCG_NODE_MOMENTS"]
+        ctx.set_cloud(pts)
+        eig, nrm, count = ctx.pca_radius(r, 0, cc.COV_NM1, want_normals=True)
+        assert np.array_equal(count, cnt)
+        scale = np.maximum(eig64[:, :1], 1e-30)
+        assert (np.abs(eig - eig64) / scale).max() <= EIG_TOL
+        assert np.array_equal(ctx.radius(r, 0, strict_lt=True, lists=False)["count"], cnt)
+        assert np.array_equal(ctx.radius(r, mn, strict_lt=True, lists=False)["count"], np.minimum(cnt, mn))
+        assert np.array_equal(ctx.radius_count_mask(r, mn, prefilter=False), ref_mask)
+        res[knob] = (eig, nrm)
+        ctx.close()
+    assert (np.abs(res["1"][0] - res["0"][0]) / np.maximum(eig64[:, :1], 1e-30)).max() <= EIG_TOL
+
+
 @pytest.mark.parametrize("kind", ["surface", "volume", "lattice", "pile"])
 def test_capped_radius_far_below_the_neighbourhood_size(gpu_ctx, kind):
     """Caps 10-300x below the neighbourhood size (the reference's pca_max_nn = 1000 inside r = 0.2 m holds 24 k points on a dense
