@@ -110,30 +110,15 @@ struct Stream {
     }
 };
 
-// the same sums with whole boxes taken at once (tile.cuh: visits_nodes): a box inside the radius of every lane that wants it adds
-// its count and its moments, shifted from the box centre c to the query — with d = c - q:
-//   sum (p - q) = S + n d,   sum (p - q)(p - q)^T = M + S d^T + d S^T + n d d^T        (per-box arrays: build.cu, k_leaf_moments)
+// the same sums with whole boxes taken at once (tile.cuh: visits_nodes, add_box_moments): a box inside the radius of every lane
+// that wants it adds its count and its moments, shifted from the box centre to the query (per-box arrays: build.cu)
 struct StreamNodes : Stream {
     static constexpr bool kNodes = true;
     const float4 *mom;
+    __device__ __forceinline__ bool node_test() const { return true; }
+    __device__ __forceinline__ bool whole(float dfar) const { return dfar <= bound; }
     __device__ __forceinline__ void add_node(size_t node, const float4 &lo, const float4 &hi, const float4 &q) {
-        const float4 a = __ldg(mom + 3 * node);
-        const int nn = __float_as_int(a.w);
-        count += nn;
-        if (moments) {
-            const float4 b = __ldg(mom + 3 * node + 1), c = __ldg(mom + 3 * node + 2);
-            const float fn = (float)nn;
-            const float dx = __fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)) - q.x, dy = __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)) - q.y,
-                        dz = __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)) - q.z;
-            const float tx = fn * dx, ty = fn * dy, tz = fn * dz;
-            m[0] += a.x + tx; m[1] += a.y + ty; m[2] += a.z + tz;
-            m[3] += b.x + dx * (2.f * a.x + tx);
-            m[4] += b.y + a.x * dy + dx * (a.y + ty);
-            m[5] += b.z + a.x * dz + dx * (a.z + tz);
-            m[6] += b.w + dy * (2.f * a.y + ty);
-            m[7] += c.x + a.y * dz + dy * (a.z + tz);
-            m[8] += c.y + dz * (2.f * a.z + tz);
-        }
+        count += add_box_moments(mom, node, lo, hi, q, moments, m);
         if (cap > 0 && count >= cap) { count = cap; bound = -1.f; }   // what the per-point count stops at
     }
 };

@@ -66,6 +66,20 @@ __device__ __forceinline__ float bracket_edge(float rb, float scale, int lvl, co
     return fminf(rb, __fmul_rn(__fmul_rn(e, e), 1.00001f));
 }
 
+// Inner edge of the same bracket: every candidate with d2 below the returned value has f < F, i.e. lies below the bracket.  A box
+// whose farthest corner is nearer than this holds nothing a bracket pass is looking for (tile.cuh: visits_nodes).
+__device__ __forceinline__ float bracket_inner(float scale, int lvl, const int sel[kSelLevels]) {
+    if (lvl == 0) return 0.f;
+    float F = 0.f, w = 1.f;
+#pragma unroll
+    for (int l = 0; l < kSelLevels; ++l) {
+        if (l < lvl) { F += (float)sel[l] * w; w *= 1.f / (float)kSelBins; }
+    }
+    const float e = __fmul_rn(__fdiv_rn(F, scale), 0.99999f);
+    const float in = __fmul_rn(__fmul_rn(e, e), 0.99999f);
+    return in == in ? in : 0.f;                       // scale == 0 (r == 0): no inner edge
+}
+
 struct HistV {                        // level pass: histogram of the candidates inside the chosen bins
     float bound, scale; int lvl; int sel[kSelLevels];
     unsigned *hist;                   // this lane's column: bin b at hist[b * 32]
@@ -74,6 +88,11 @@ struct HistV {                        // level pass: histogram of the candidates
     // edge, so the far part of a neighbourhood much larger than the cap (24 k points inside r = 0.2 m on the 30 M scan, cap
     // 1000) is never opened.  Bins <= b stay complete: a box is only ever pruned against a bound >= the final one.
     int max_nn, inb, limit;
+    static constexpr bool kNodes = true;              // later passes: boxes inside the bracket's inner edge are skipped
+    float inner;
+    __device__ __forceinline__ bool node_test() const { return lvl > 0; }
+    __device__ __forceinline__ bool whole(float dfar) const { return dfar < inner; }
+    __device__ __forceinline__ void add_node(size_t, const float4 &, const float4 &, const float4 &) {}
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
         int add = 0;
 #pragma unroll 2
@@ -106,6 +125,11 @@ struct HistV {                        // level pass: histogram of the candidates
 struct KeepV {                        // select pass: the d2 values inside the chosen bins (<= kSelKeep kept), their min / max
     float bound, scale; int lvl; int sel[kSelLevels];
     float *vals; int cnt; float vmin, vmax;
+    static constexpr bool kNodes = true;
+    float inner;
+    __device__ __forceinline__ bool node_test() const { return lvl > 0; }
+    __device__ __forceinline__ bool whole(float dfar) const { return dfar < inner; }
+    __device__ __forceinline__ void add_node(size_t, const float4 &, const float4 &, const float4 &) {}
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
 #pragma unroll 2
         for (int j = 0; j < kLeaf; ++j) {
@@ -192,6 +216,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
         for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
         // later passes only need the bracket chosen so far: everything in it lies below its upper edge
         h.bound = mine ? bracket_edge(rb, scale, lvl, sel) : -1.f;
+        h.inner = bracket_inner(scale, lvl, sel);
         h.max_nn = first ? max_nn : 0; h.inb = 0; h.limit = max_nn < (1 << 30) ? max_nn + (max_nn >> 2) + 32 : INT_MAX;
         traverse_tile(T, tile, q, h, s_ws[warp]);
         if (first) {
@@ -220,7 +245,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     bool tie_pass = false;                                 // does this lane need the index tie-break at T?
     {
         KeepV kv; kv.bound = need ? bracket_edge(rb, scale, lvl, sel) : -1.f; kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
-        kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY;
+        kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel);
 #pragma unroll
         for (int l = 0; l < kSelLevels; ++l) kv.sel[l] = sel[l];
         traverse_tile(T, tile, q, kv, s_ws[warp]);
@@ -300,10 +325,18 @@ struct RuleBase {
 };
 
 struct RuleMoments : RuleBase {       // getPCA / getHist with a cap beyond the list kernels (cv.h:98-113)
-    struct Args { PcaOut pca; int32_t *count; };
+    struct Args { PcaOut pca; int32_t *count; const float4 *mom; };
     static constexpr int kSmemWords = 0;
+    static constexpr bool kNodes = true;  // a box strictly inside the cap distance is admitted whatever its indices: aggregated term
+    const float4 *mom;
     float m[9];
-    __device__ __forceinline__ void init(const Args &, const float4 &, unsigned *) {
+    __device__ __forceinline__ bool node_test() const { return mom != nullptr; }
+    __device__ __forceinline__ bool whole(float dfar) const { return dfar < bound; }
+    __device__ __forceinline__ void add_node(size_t node, const float4 &lo, const float4 &hi, const float4 &q) {
+        count += add_box_moments(mom, node, lo, hi, q, true, m);
+    }
+    __device__ __forceinline__ void init(const Args &a, const float4 &, unsigned *) {
+        mom = a.mom;
 #pragma unroll
         for (int i = 0; i < 9; ++i) m[i] = 0.f;
     }
@@ -435,9 +468,16 @@ struct RuleHist : RuleBase {          // calcDistHist / calcIntensityHist (featu
 };
 
 struct RuleCount : RuleBase {         // CSR pass 1: neighbours per point
-    struct Args { long long *count64; };
+    struct Args { long long *count64; const float4 *mom; };
     static constexpr int kSmemWords = 0;
-    __device__ __forceinline__ void init(const Args &, const float4 &, unsigned *) {}
+    static constexpr bool kNodes = true;
+    const float4 *mom;
+    __device__ __forceinline__ bool node_test() const { return mom != nullptr; }
+    __device__ __forceinline__ bool whole(float dfar) const { return dfar < bound; }
+    __device__ __forceinline__ void add_node(size_t node, const float4 &, const float4 &, const float4 &) {
+        count += __float_as_int(__ldg(mom + 3 * node).w);
+    }
+    __device__ __forceinline__ void init(const Args &a, const float4 &, unsigned *) { mom = a.mom; }
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
 #pragma unroll 8
         for (int j = 0; j < kLeaf; ++j) {
@@ -537,6 +577,8 @@ int launch_rule_pca(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ip
     for (int i = 0; i < 3; ++i) A.pca.vp[i] = a.vp[i];
     A.pca.eig3 = a.eig3; A.pca.normal4 = a.normal4; A.pca.feat7 = a.feat7; A.pca.formula_set = a.formula_set;
     A.count = a.count;
+    A.mom = nullptr;
+    if (ctx->node_moments) { CCG_TRY(ensure_node_moments(ctx)); A.mom = ctx->node_mom.as<float4>(); }
     return launch_rule<RuleMoments>(ctx, rb, Tpos, Ipos, A);
 }
 int launch_rule_stdev_dist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, int use_depth, const float centre[3], float *out) {
@@ -560,7 +602,8 @@ int launch_rule_hist(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *I
 // ascending by (d2, index) with one segmented radix sort -> idx / d2.  offsets_dev: long long[n + 1] (device).
 int launch_radius_csr_count(ccg_ctx *ctx, float rb, const float *Tpos, const int32_t *Ipos, long long *offsets_dev, long long *total_host) {
     const size_t n = ctx->n;
-    RuleCount::Args A{offsets_dev};
+    RuleCount::Args A{offsets_dev, nullptr};
+    if (ctx->node_moments) { CCG_TRY(ensure_node_moments(ctx)); A.mom = ctx->node_mom.as<float4>(); }
     CCG_TRY(launch_rule<RuleCount>(ctx, rb, Tpos, Ipos, A));
     size_t tmp_bytes = 0;
     CCG_CUDA(ctx, cudaMemsetAsync(offsets_dev + n, 0, sizeof(long long), ctx->stream));

@@ -66,11 +66,37 @@ __device__ __forceinline__ float warp_min(float v) {
     return v;
 }
 
-// A visitor with `static constexpr bool kNodes = true` and add_node(node, lo, hi, q) takes a whole SUBTREE at once when its box
-// lies inside the bound of every lane that wants it (node = index into the per-node arrays laid out like the boxes: level
-// offset + node number) — the uncapped radius sums then cost one aggregated term per inner box instead of a visit per point.
+// A visitor with `static constexpr bool kNodes = true` takes a whole SUBTREE at once: when node_test() is on, every box chosen by
+// the walk is also measured by its FARTHEST corner, and when whole(far distance) holds for every lane that wants the box, the
+// lanes call add_node(node, lo, hi, q) instead of descending (node = index into the per-node arrays laid out like the boxes:
+// level offset + node number).  Uncapped radius sums add the box's aggregated count and moments (one term per box inside the
+// radius instead of a visit per point); the bracket passes of the capped search simply skip boxes that lie inside the
+// bracket's inner edge.
 template <class V, class = void> struct visits_nodes : std::false_type {};
 template <class V> struct visits_nodes<V, std::void_t<decltype(V::kNodes)>> : std::bool_constant<V::kNodes> {};
+
+// count and moments of a box about its own centre (build.cu: k_leaf_moments / k_level_moments), shifted to the query: with
+// d = centre - q,  sum (p - q) = S + n d,  sum (p - q)(p - q)^T = M + S d^T + d S^T + n d d^T
+__device__ __forceinline__ int add_box_moments(const float4 *__restrict__ mom, size_t node, const float4 &lo, const float4 &hi, const float4 &q,
+                                               bool moments, float m[9]) {
+    const float4 a = __ldg(mom + 3 * node);
+    const int nn = __float_as_int(a.w);
+    if (moments) {
+        const float4 b = __ldg(mom + 3 * node + 1), c = __ldg(mom + 3 * node + 2);
+        const float fn = (float)nn;
+        const float dx = __fmul_rn(0.5f, __fadd_rn(lo.x, hi.x)) - q.x, dy = __fmul_rn(0.5f, __fadd_rn(lo.y, hi.y)) - q.y,
+                    dz = __fmul_rn(0.5f, __fadd_rn(lo.z, hi.z)) - q.z;
+        const float tx = fn * dx, ty = fn * dy, tz = fn * dz;
+        m[0] += a.x + tx; m[1] += a.y + ty; m[2] += a.z + tz;
+        m[3] += b.x + dx * (2.f * a.x + tx);
+        m[4] += b.y + a.x * dy + dx * (a.y + ty);
+        m[5] += b.z + a.x * dz + dx * (a.z + tz);
+        m[6] += b.w + dy * (2.f * a.y + ty);
+        m[7] += c.x + a.y * dz + dy * (a.z + tz);
+        m[8] += c.y + dz * (2.f * a.z + tz);
+    }
+    return nn;
+}
 
 // Bottom-up, nearest-first walk of the box hierarchy for the 32 queries of one leaf ("tile").
 //   * the tile's own leaf is scanned first (it alone fills a k <= 32 list and gives a finite bound);
@@ -141,10 +167,12 @@ __device__ __forceinline__ int traverse_tile(const TreeView &T, int tile, const 
             const bool want = d2_point_box(q, clo, chi) <= v.bound;
             if (!__any_sync(kFull, want)) continue;
             if constexpr (visits_nodes<V>::value) {
-                const bool whole = want && d2_point_box_far(q, clo, chi) <= v.bound;
-                if (__all_sync(kFull, whole || !want)) {
-                    if (whole) v.add_node((size_t)(T.lo[lv] - T.lo[0]) + (size_t)child, clo, chi, q);
-                    continue;
+                if (v.node_test()) {
+                    const bool whole = want && v.whole(d2_point_box_far(q, clo, chi));
+                    if (__all_sync(kFull, whole || !want)) {
+                        if (whole) v.add_node((size_t)(T.lo[lv] - T.lo[0]) + (size_t)child, clo, chi, q);
+                        continue;
+                    }
                 }
             }
             if (lv == 0) {

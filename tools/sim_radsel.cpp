@@ -9,6 +9,7 @@
 #include <vector>
 #include <algorithm>
 #include <climits>
+#include <type_traits>
 #define __device__
 #define __forceinline__ inline
 struct float4 { float x, y, z, w; };
@@ -27,12 +28,18 @@ static inline float d2_point(const float4 &q, const float4 &p) {
 }
 #include "radsel_structs.inc"
 
-struct Leaf { float4 p[kLeaf]; float lb; };
+struct Leaf { float4 p[kLeaf]; float lb, ub; };
+template <class V, class = void> struct visits_nodes : std::false_type {};
+template <class V> struct visits_nodes<V, std::void_t<decltype(V::kNodes)>> : std::bool_constant<V::kNodes> {};
 static std::vector<Leaf> leaves;
+static long skipped = 0;
 template <class V> static long walk(const float4 &q, V &v) {
     long scanned = 0;
     for (auto &L : leaves) {                       // sorted by lb: nearest first
         if (!(L.lb <= v.bound)) continue;          // pruned against the CURRENT bound
+        if constexpr (visits_nodes<V>::value) {
+            if (v.node_test() && v.whole(L.ub)) { ++skipped; continue; }   // the whole leaf lies inside the bracket's inner edge
+        }
         v.scan_leaf(q, L.p); ++scanned;
     }
     return scanned;
@@ -65,9 +72,9 @@ int main(int argc, char **argv) {
         std::sort(ord.begin(), ord.end());
         leaves.clear();
         for (int i = 0; i < n; i += kLeaf) {
-            Leaf L; L.lb = INFINITY;
+            Leaf L; L.lb = INFINITY; L.ub = 0.f;
             for (int j = 0; j < kLeaf; ++j) {
-                if (i + j < n) { L.p[j] = pts[ord[i + j].second]; L.lb = fminf(L.lb, d2_point(q, L.p[j])); }
+                if (i + j < n) { L.p[j] = pts[ord[i + j].second]; L.lb = fminf(L.lb, d2_point(q, L.p[j])); L.ub = fmaxf(L.ub, d2_point(q, L.p[j])); }
                 else L.p[j] = {INFINITY, INFINITY, INFINITY, __int_as_float(-1)};
             }
             leaves.push_back(L);
@@ -94,6 +101,7 @@ int main(int argc, char **argv) {
             HistV h; h.scale = scale; h.lvl = lvl; h.hist = hist;
             for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
             h.bound = mine ? bracket_edge(rb, scale, lvl, sel) : -1.f;
+            h.inner = bracket_inner(scale, lvl, sel);
             h.max_nn = first ? max_nn : 0; h.inb = 0; h.limit = max_nn < (1 << 30) ? max_nn + (max_nn >> 2) + 32 : INT_MAX;
             scanned += walk(q, h);
             if (first) {
@@ -114,7 +122,7 @@ int main(int argc, char **argv) {
         }
         if (need) {
             KeepV kv; kv.bound = bracket_edge(rb, scale, lvl, sel); kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
-            kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY;
+            kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel);
             for (int l = 0; l < kSelLevels; ++l) kv.sel[l] = sel[l];
             scanned += walk(q, kv);
             if (kv.cnt <= kSelKeep) {
@@ -177,7 +185,7 @@ int main(int argc, char **argv) {
         } else if (err) printf("note rep %d mode %d: err %d (bracket overflow)\n", rep, mode, err);
         (void)tie_pass;
     }
-    printf("wide tie selects %ld; ", wides);
+    printf("wide tie selects %ld; leaves skipped inside the inner edge %ld; ", wides, skipped);
     printf("cases %ld fails %ld; leaves scanned (all passes) %.0f vs one full-radius pass %.0f\n", cases, total_fail, sc_new, sc_full);
     return total_fail != 0;
 }
