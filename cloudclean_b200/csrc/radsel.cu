@@ -89,8 +89,8 @@ struct HistV {                        // level pass: histogram of the candidates
     // 1000) is never opened.  Bins <= b stay complete: a box is only ever pruned against a bound >= the final one.
     int max_nn, inb, limit;
     static constexpr bool kNodes = true;              // later passes: boxes inside the bracket's inner edge are skipped
-    float inner;
-    __device__ __forceinline__ bool node_test() const { return lvl > 0; }
+    float inner; bool nodes;                          // nodes: WARP-UNIFORM switch (the test votes with a full mask)
+    __device__ __forceinline__ bool node_test() const { return nodes; }
     __device__ __forceinline__ bool whole(float dfar) const { return dfar < inner; }
     __device__ __forceinline__ void add_node(size_t, const float4 &, const float4 &, const float4 &) {}
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
@@ -126,8 +126,8 @@ struct KeepV {                        // select pass: the d2 values inside the c
     float bound, scale; int lvl; int sel[kSelLevels];
     float *vals; int cnt; float vmin, vmax;
     static constexpr bool kNodes = true;
-    float inner;
-    __device__ __forceinline__ bool node_test() const { return lvl > 0; }
+    float inner; bool nodes;                          // nodes: WARP-UNIFORM switch (the test votes with a full mask)
+    __device__ __forceinline__ bool node_test() const { return nodes; }
     __device__ __forceinline__ bool whole(float dfar) const { return dfar < inner; }
     __device__ __forceinline__ void add_node(size_t, const float4 &, const float4 &, const float4 &) {}
     __device__ __forceinline__ void scan_leaf(const float4 &q, const float4 *leaf) {
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
         for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
         // later passes only need the bracket chosen so far: everything in it lies below its upper edge
         h.bound = mine ? bracket_edge(rb, scale, lvl, sel) : -1.f;
-        h.inner = bracket_inner(scale, lvl, sel);
+        h.inner = bracket_inner(scale, lvl, sel); h.nodes = !first;
         h.max_nn = first ? max_nn : 0; h.inb = 0; h.limit = max_nn < (1 << 30) ? max_nn + (max_nn >> 2) + 32 : INT_MAX;
         traverse_tile(T, tile, q, h, s_ws[warp]);
         if (first) {
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(128) k_tile_kth(const __grid_constant__ TreeVi
     bool tie_pass = false;                                 // does this lane need the index tie-break at T?
     {
         KeepV kv; kv.bound = need ? bracket_edge(rb, scale, lvl, sel) : -1.f; kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
-        kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel);
+        kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel); kv.nodes = true;
 #pragma unroll
         for (int l = 0; l < kSelLevels; ++l) kv.sel[l] = sel[l];
         traverse_tile(T, tile, q, kv, s_ws[warp]);

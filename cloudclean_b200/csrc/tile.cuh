@@ -66,7 +66,8 @@ __device__ __forceinline__ float warp_min(float v) {
     return v;
 }
 
-// A visitor with `static constexpr bool kNodes = true` takes a whole SUBTREE at once: when node_test() is on, every box chosen by
+// A visitor with `static constexpr bool kNodes = true` takes a whole SUBTREE at once: when node_test() is on (it must be the same
+// in every lane of the warp: the test votes with a full mask), every box chosen by
 // the walk is also measured by its FARTHEST corner, and when whole(far distance) holds for every lane that wants the box, the
 // lanes call add_node(node, lo, hi, q) instead of descending (node = index into the per-node arrays laid out like the boxes:
 // level offset + node number).  Uncapped radius sums add the box's aggregated count and moments (one term per box inside the

@@ -101,7 +101,7 @@ int main(int argc, char **argv) {
             HistV h; h.scale = scale; h.lvl = lvl; h.hist = hist;
             for (int l = 0; l < kSelLevels; ++l) h.sel[l] = sel[l];
             h.bound = mine ? bracket_edge(rb, scale, lvl, sel) : -1.f;
-            h.inner = bracket_inner(scale, lvl, sel);
+            h.inner = bracket_inner(scale, lvl, sel); h.nodes = !first;
             h.max_nn = first ? max_nn : 0; h.inb = 0; h.limit = max_nn < (1 << 30) ? max_nn + (max_nn >> 2) + 32 : INT_MAX;
             scanned += walk(q, h);
             if (first) {
@@ -122,7 +122,7 @@ int main(int argc, char **argv) {
         }
         if (need) {
             KeepV kv; kv.bound = bracket_edge(rb, scale, lvl, sel); kv.scale = scale; kv.lvl = lvl; kv.vals = reinterpret_cast<float *>(hist);
-            kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel);
+            kv.cnt = 0; kv.vmin = INFINITY; kv.vmax = -INFINITY; kv.inner = bracket_inner(scale, lvl, sel); kv.nodes = true;
             for (int l = 0; l < kSelLevels; ++l) kv.sel[l] = sel[l];
             scanned += walk(q, kv);
             if (kv.cnt <= kSelKeep) {
