@@ -559,35 +559,48 @@ def main():
         h2d = n * 32                                                # summed over the ranks
         pinned_ok = all(v.registered for v in shm.values())
 
+    class Sess:                                        # what one end-to-end session of a rank owns (N > 1)
+        pass
+
+    if world > 1:
+        S0 = Sess()
+        S0.ctx, S0.stream, S0.group, S0.pack, S0.my_slice, S0.stage32 = ctx, stream, None, pack, my_slice, stage32
+        S0.slices, S0.own, S0.token, S0.out = slices, own, token, shm
+
+    def step_host_session(S, record=True):
+        with torch.cuda.stream(S.stream):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
+            ev[0].record(S.stream)
+            if rb_ > ra:
+                S.stage32[:rb_ - ra].copy_(shm["pts"].t[ra:rb_], non_blocking=True)      # H2D of this rank's rows
+                S.my_slice[:rb_ - ra].copy_(S.stage32[:rb_ - ra, :RW])
+            ev[1].record(S.stream)
+            if repl == "pull" and S is S0:
+                in_own.copy_(S.my_slice)
+                all_gather_by_pulls()
+            else:
+                dist.all_gather_into_tensor(S.pack, S.my_slice, group=S.group)
+            ev[2].record(S.stream)
+            S.ctx.set_cloud(S.pack[:n])
+            ev[3].record(S.stream)
+            S.ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, S.slices.tables[0], S.slices.tables[1], S.slices.tables[2])
+            ev[4].record(S.stream)
+            dist.all_reduce(S.token, group=S.group)                 # every peer has stored the rows this rank owns
+            ev[5].record(S.stream)
+            if rb_ > ra:
+                S.out["eig"].t[ra:rb_].copy_(S.own[0][:rb_ - ra], non_blocking=True)       # D2H to the final host addresses
+                S.out["nrm"].t[ra:rb_].copy_(S.own[1][:rb_ - ra], non_blocking=True)
+                S.out["feat"].t[ra:rb_].copy_(S.own[2][:rb_ - ra], non_blocking=True)
+            ev[6].record(S.stream)
+            if record:
+                e2e_ev.append(ev)
+
     def step_host():
         if world == 1:
             ctx.set_cloud(np_pts)                                              # host AoS in: H2D inside the call
             ctx.pca_knn_features_into(K, cc.COV_NM1, 0, np_eig, np_nrm, np_feat)   # host outputs: D2H inside the call
         else:
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
-            ev[0].record(stream)
-            if rb_ > ra:
-                stage32[:rb_ - ra].copy_(shm["pts"].t[ra:rb_], non_blocking=True)      # H2D of this rank's rows
-                my_slice[:rb_ - ra].copy_(stage32[:rb_ - ra, :RW])
-            ev[1].record(stream)
-            if repl == "pull":
-                in_own.copy_(my_slice)
-                all_gather_by_pulls()
-            else:
-                dist.all_gather_into_tensor(pack, my_slice)
-            ev[2].record(stream)
-            ctx.set_cloud(pack[:n])
-            ev[3].record(stream)
-            ctx.pca_knn_features_route(K, cc.COV_NM1, 0, rank, world, rpr, slices.tables[0], slices.tables[1], slices.tables[2])
-            ev[4].record(stream)
-            dist.all_reduce(token)                                  # every peer has stored the rows this rank owns
-            ev[5].record(stream)
-            if rb_ > ra:
-                shm["eig"].t[ra:rb_].copy_(own[0][:rb_ - ra], non_blocking=True)       # D2H to the final host addresses
-                shm["nrm"].t[ra:rb_].copy_(own[1][:rb_ - ra], non_blocking=True)
-                shm["feat"].t[ra:rb_].copy_(own[2][:rb_ - ra], non_blocking=True)
-            ev[6].record(stream)
-            e2e_ev.append(ev)
+            step_host_session(S0)
 
     def timed(fn, steps, warmup):
         with torch.cuda.stream(stream):
@@ -643,6 +656,74 @@ def main():
     bms_mean = float(np.mean(build_ms[args.warmup:]))
     e2e_ev.clear()
     ms_e2e = timed(step_host, max(2, args.steps // 2), 1)
+    sessions = int(os.environ.get("CCG_BENCH_E2E_SESSIONS", "2"))
+    e2e_multi = None
+    if world > 1 and sessions > 1 and repl != "pull":
+        # N > 1: the same end-to-end step with TWO sessions in flight on every rank (as at N = 1): a second ctx on a second
+        # stream with its own communicator, replication buffers, owner-routed output slices and shared pinned output arrays.
+        # Steps alternate between the sessions; everything is enqueued asynchronously, so session B's upload / all-gather /
+        # build / query run under session A's download (the slow stage: the box's host-memory write rate).
+        S1 = Sess()
+        S1.stream = torch.cuda.Stream(device=dev)
+        S1.ctx = cc.Context(local)
+        S1.ctx.set_stream(S1.stream.cuda_stream)
+        S1.ctx.set_async(True)
+        S1.group = dist.new_group(backend="nccl")
+        S1.pack, S1.my_slice, S1.stage32 = torch.empty_like(pack), torch.empty_like(my_slice), torch.empty_like(stage32)
+        S1.slices = sharding.PeerSlices(S1.ctx, rpr, (3, 4, 7))
+        S1.own = [b.tensor(dev) for b in S1.slices.own]
+        S1.token = torch.zeros(1, device=dev)
+        S1.out = {}
+        for name, w in (("eig", 3), ("nrm", 4), ("feat", 7)):
+            if rank == 0:
+                S1.out[name] = sharding.SharedPinned(f"{tag}_{name}_s1", (n, w), create=True, register=False)
+        dist.barrier()
+        for name, w in (("eig", 3), ("nrm", 4), ("feat", 7)):
+            if rank != 0:
+                S1.out[name] = sharding.SharedPinned(f"{tag}_{name}_s1", (n, w), register=False)
+        if rb_ > ra:
+            for name in ("eig", "nrm", "feat"):
+                S1.out[name].t[ra:rb_].zero_()                      # first touch by the owning rank (NUMA placement)
+        dist.barrier()
+        for v in S1.out.values():
+            v.register()
+        dist.barrier()
+        both = (S0, S1)
+        per = max(2, (args.steps + 1) // 2)
+
+        def run_both(reps, record):
+            for i in range(reps * 2):
+                step_host_session(both[i % 2], record=record)
+
+        run_both(1, False)                                           # warm-up: the second session's buffers get allocated
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m0.record(S0.stream)
+        S1.stream.wait_event(m0)
+        run_both(per, False)
+        S0.stream.wait_stream(S1.stream)
+        m1.record(S0.stream)
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        tm = torch.tensor([m0.elapsed_time(m1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        S1.ctx.sync()
+        same = True
+        if rb_ > ra:
+            same = all(torch.equal(S1.out[k_].t[ra:rb_].view(torch.int32), shm[k_].t[ra:rb_].view(torch.int32)) for k_ in ("eig", "nrm", "feat"))
+        ts = torch.tensor([1 if same else 0], device=dev)
+        dist.all_reduce(ts, op=dist.ReduceOp.MIN)
+        e2e_multi = {"ms": float(tm.item()), "steps": per * 2, "sessions": 2, "outputs_identical_across_sessions": bool(ts.item())}
+        torch.cuda.synchronize()
+        dist.barrier()
+        S1.slices.close()
+        for v in S1.out.values():
+            v.close()
+        S1.ctx.close()
+        del S1
     if world > 1:
         ctx.sync()
         ctx.set_async(False)
@@ -653,8 +734,6 @@ def main():
     # the scan and its own pinned outputs.  Every step still uploads ITS cloud and downloads ITS rows inside the timed region;
     # what changes is that session B's upload (PCIe up) runs under session A's query + download (PCIe down): the link is full
     # duplex and one session alone leaves each direction idle while the other works (profiles/r02_e2e_pipeline_trace_v20.log).
-    e2e_multi = None
-    sessions = int(os.environ.get("CCG_BENCH_E2E_SESSIONS", "2"))
     if world == 1 and sessions > 1:
         import threading
         ctxs = [ctx] + [cc.Context(local) for _ in range(sessions - 1)]
@@ -817,10 +896,14 @@ def main():
             one = {"value": e2e_v, "ms_per_step": ms_e2e / e2e_steps, "steps": e2e_steps}
             line["e2e"].update({"value": n * e2e_multi["steps"] / (e2e_multi["ms"] * 1e-3), "ms_per_step": e2e_multi["ms"] / e2e_multi["steps"],
                                 "steps": e2e_multi["steps"], "sessions_in_flight": e2e_multi["sessions"],
-                                "outputs_identical_across_sessions": e2e_multi["outputs_identical_across_sessions"], "one_session": one,
-                                "path": "pinned host PointXYZI in, pinned host outputs out, through the C ABI; two worker threads with a "
-                                        "ccg_ctx, a pinned scan and pinned outputs each, every step = ccg_set_cloud (H2D) + "
-                                        "ccg_pca_knn_features (D2H); one session's upload overlaps the other's query + download"})
+                                "outputs_identical_across_sessions": e2e_multi["outputs_identical_across_sessions"], "one_session": one})
+            if world == 1:
+                line["e2e"]["path"] = ("pinned host PointXYZI in, pinned host outputs out, through the C ABI; two worker threads with a "
+                                       "ccg_ctx, a pinned scan and pinned outputs each, every step = ccg_set_cloud (H2D) + "
+                                       "ccg_pca_knn_features (D2H); one session's upload overlaps the other's query + download")
+            else:
+                line["e2e"]["path"] += ("; two sessions in flight per rank (second ctx, stream, communicator, slices and shared pinned "
+                                        "outputs), steps alternate between them; stage_ms is the one-session picture")
         elif e2e_multi is not None:
             line["e2e"]["two_sessions_error"] = e2e_multi["error"]
         if match is not None:
