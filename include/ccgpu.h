@@ -131,7 +131,9 @@ int ccg_pca_knn_features(ccg_ctx *ctx, int k, int cov_norm, const float *viewpoi
 /* Replaces the body of getPCA<PointT> (cv.h:96-113) and getHist (cv.cpp:271-295): strict radius search with
  * the max_nn cap (0 = uncapped; ANY positive cap: 20, tests.json's 1000, markov.cpp:54's 100000 — beyond CCG_MAX_K the
  * max_nn-th distance comes from a counting select, radsel.cu), `<3 neighbours -> (0,0,1)` marker (cv.h:105-109), else PCA eigenvalues
- * descending.  normalise_hist!=0 applies getHist's L2 normalisation (cv.cpp:293).  normal4 / count optional. */
+ * descending.  normalise_hist!=0 applies getHist's L2 normalisation (cv.cpp:293).  normal4 / count optional.
+ * count is exact for every cap; the moments are fp32 sums in traversal order (uncapped: boxes of the hierarchy that lie inside
+ * the radius enter as one aggregated term each), eigenvalues within 1e-4 * lambda0 of the fp64 truth. */
 int ccg_pca_radius(ccg_ctx *ctx, double r, int max_nn, int cov_norm, int normalise_hist, const float *viewpoint3,
                    float *eig3, float *normal4, int32_t *count);
 
