@@ -34,3 +34,20 @@ def test_counting_select_model_matches_brute_force(sim, seed):
     last = r.stdout.strip().splitlines()[-1]
     assert "fails 0" in last and "cases 400" in last
     assert "FAIL" not in r.stdout
+
+
+def test_box_moments_shift_matches_fp64_sums():
+    """add_box_moments (tile.cuh): a box's count and moments about its own centre, shifted to a query, against fp64 point-by-point
+    sums — boxes of 1..1024 points, extents 2 mm..20 cm, clouds up to 900 m from the origin (no cancellation)."""
+    out = os.path.join(ROOT, "build", "sim")
+    os.makedirs(out, exist_ok=True)
+    src = open(os.path.join(ROOT, "cloudclean_b200", "csrc", "tile.cuh")).read()
+    a = src.index("__device__ __forceinline__ int add_box_moments")
+    with open(os.path.join(out, "box_moments.inc"), "w") as f:
+        f.write(src[a:src.index("// Bottom-up, nearest-first walk")])
+    exe = os.path.join(out, "sim_moments")
+    subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-I" + out, os.path.join(ROOT, "tools", "sim_moments.cpp"), "-o", exe],
+                   check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-2000:]
+    assert "cases 4000 fails 0" in r.stdout
